@@ -1,0 +1,125 @@
+/*
+ * makani_b200 - C ABI of the B200-native SFNO spectral hot path.
+ *
+ * Drop-in boundary for the path  RealSHT -> SpectralConv (dhconv / diagonal) -> InverseRealSHT  of
+ * choutilin/makani.  The reference has no FFI for this path (it is pure Python over cuFFT / cuBLAS);
+ * each entry point below names the reference call it replaces (paths relative to the reference root).
+ * The Python host modules in makani_b200/ bind these with ctypes (makani_b200/_ext.py); see
+ * INTEGRATION.md for the stub a maintainer of the reference would add.
+ *
+ * Conventions
+ *   - every function returns 0 on success, non-zero on failure; sfno_last_error() gives the message
+ *     (thread local);
+ *   - all data pointers are DEVICE pointers unless the name ends in _host;
+ *   - `stream` is a cudaStream_t passed as void*; calls only enqueue work (no host sync, no allocation)
+ *     so they can be captured in a CUDA graph (reference captures fwd+bwd, makani/utils/trainer.py:84-152);
+ *   - inputs are borrowed and never modified; outputs are caller-allocated.
+ *
+ * Internal device layouts ("spectral-internal", fp32)
+ *   RS   = 2 * B * Cp,  Cp = round_up(C, 4);  row index r = (b*2 + reim)*Cp + c
+ *   Kp   = round_up(nlat, 4)
+ *   XM   : [mmax][RS][Kp]      longitude-Fourier coefficients, latitude contiguous   (DFT <-> Legendre)
+ *   SP   : [lmax][mmax][RS]    spherical-harmonic coefficients, channel contiguous    (Legendre <-> conv)
+ *          only entries with m < min(mmax, round_up(l+1,16)) are defined; those with m > l are exact zeros
+ *   WP   : [lmax][2][Coutp][Cinp]   dhconv weights, planar re/im, Cin contiguous
+ */
+#ifndef MAKANI_B200_H_
+#define MAKANI_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SFNO_ABI_VERSION 1
+
+/* element types of spatial tensors crossing the boundary */
+enum { SFNO_F32 = 0, SFNO_BF16 = 1, SFNO_F16 = 2 };
+
+typedef struct sfno_plan sfno_plan;
+
+int sfno_abi_version(void);
+const char* sfno_last_error(void);
+/* number of kernels this library has launched in this process (bench.py "gpu_launches") */
+long long sfno_launch_count(void);
+
+/* ---- plan: one Legendre table [mmax][lmax][nlat] on the device --------------------------------
+ * Replaces the `weights` / `pct` buffers that torch_harmonics.RealSHT / InverseRealSHT register
+ * (constructed at makani/models/networks/sfnonet.py:536-539).  table_host is fp64, rounded once to
+ * fp32 (the reference calls .float() on the module).  m_offset is the first global order m held by
+ * this table (azimuth-sharded DistributedRealSHT keeps only its m-slab); 0 otherwise.            */
+int sfno_plan_create(int nlat, int nlon, int lmax, int mmax, int m_offset,
+                     const double* table_host, sfno_plan** out);
+int sfno_plan_destroy(sfno_plan* plan);
+
+/* sizes (in floats) of the internal buffers for a given batch*channels */
+long long sfno_xm_elems(int nlat, int mmax, int B, int C);
+long long sfno_sp_elems(int lmax, int mmax, int B, int C);
+long long sfno_wp_elems(int lmax, int Cin, int Cout);
+
+/* ---- K1 longitude DFT:   x[B*C][nlat][nlon] -> XM     (torch.fft.rfft at RealSHT.forward; call site
+ * makani/models/common/spectral_convolution.py:131).  mscale_host[mmax] multiplies bin m
+ * (forward SHT: 2*pi/nlon for all m; adjoint of the inverse DFT: 1,2,2,..(,1 at Nyquist)).       */
+int sfno_dft_fwd(const void* x, int x_dtype, int B, int C, int nlat, int nlon, int mmax,
+                 const float* mscale_dev, float* xm, void* stream);
+
+/* ---- K5 inverse longitude DFT:   XM -> y[B*C][nlat][nlon]   (torch.fft.irfft(n=nlon, norm="forward") at
+ * InverseRealSHT.forward; call site spectral_convolution.py:133,141).  mscale_dev[mmax] pre-multiplies
+ * bin m (inverse SHT: 1; adjoint of the forward DFT: pi/nlon * {2,1,1,...}).  m_valid: bins >= m_valid
+ * are taken as zero.                                                                              */
+int sfno_dft_inv(const float* xm, int B, int C, int nlat, int nlon, int mmax, int m_valid,
+                 const float* mscale_dev, void* y, int y_dtype, void* stream);
+
+/* ---- K2 / K4 Legendre contractions on tcgen05 tensor cores (TF32 in, fp32 accumulate) ---------
+ * analysis : SP[l][m][r]  = sum_k XM[m][r][k] * table[m][l][k]   (einsum '...km,mlk->...lm')
+ * synthesis: XM[m][r][k]  = sum_l SP[l][m][r] * table[m][l][k]   (einsum '...lm,mlk->...km')
+ * The same plan serves both directions (a forward plan's synthesis is the adjoint needed by backward). */
+int sfno_legendre_analysis(const sfno_plan* plan, const float* xm, int B, int C, float* sp, void* stream);
+int sfno_legendre_synthesis(const sfno_plan* plan, const float* sp, int B, int C, float* xm, void* stream);
+
+/* ---- K3 dhconv channel contraction (makani/models/common/contractions.py:131-136,
+ * einsum "bixy,iox->boxy" on complex64) as planar-complex TF32 tcgen05 GEMMs, batched over l.   */
+int sfno_dhconv_pack_weight(const void* w_c64 /*[Cin][Cout][L] complex64*/, int Cin, int Cout, int L,
+                            float* wp, void* stream);
+int sfno_dhconv_unpack_wgrad(const float* gwp, int Cin, int Cout, int L,
+                             void* gw_c64 /*[Cin][Cout][L] complex64*/, void* stream);
+/* l_offset / m_offset: global degree / order of local index 0 (non-zero only for the h/w-sharded
+ * DistributedRealSHT layout); they place the triangular m <= l structure that the kernels skip. */
+int sfno_dhconv_fwd(const float* sp_in, const float* wp, float* sp_out, int B, int Cin, int Cout,
+                    int lmax, int mmax, int l_offset, int m_offset, void* stream);
+/* dX[b,i,l,m] = sum_o dY[b,o,l,m] * conj(w[i,o,l]) */
+int sfno_dhconv_bwd_x(const float* gsp_out, const float* wp, float* gsp_in, int B, int Cin, int Cout,
+                      int lmax, int mmax, int l_offset, int m_offset, void* stream);
+/* dW[i,o,l] = sum_{b,m} conj(x[b,i,l,m]) * dY[b,o,l,m]   (packed layout WP) */
+int sfno_dhconv_bwd_w(const float* sp_in, const float* gsp_out, float* gwp, int B, int Cin, int Cout,
+                      int lmax, int mmax, int l_offset, int m_offset, void* stream);
+
+/* ---- K3' diagonal contraction (contractions.py:121-127, einsum "bixy,ioxy->boxy"): weights are used once,
+ * so this is a bandwidth kernel.  w is complex64 [Cin][Cout][lmax][mmax].
+ *   mode 0: y  = x * w            sp_a = SP x,  w_or_spb = w,    out = SP y
+ *   mode 1: dx = dy * conj(w)     sp_a = SP dy, w_or_spb = w,    out = SP dx
+ *   mode 2: dw = conj(x) * dy     sp_a = SP x,  w_or_spb = SP dy, out = complex64 dw
+ * The separable variants (contractions.py:139-154) are not provided: the reference's own einsum strings
+ * for them ("bixy,ix->boxy") have an output index absent from the inputs and raise in torch.       */
+int sfno_diag_contract(int mode, const float* sp_a, const void* w_or_spb, void* out, int B, int Cin, int Cout,
+                       int lmax, int mmax, int l_offset, int m_offset, void* stream);
+
+/* ---- layout conversion at the module boundary ------------------------------------------------
+ * SP <-> complex64 [B][C][lmax][mmax] (what RealSHT returns / InverseRealSHT accepts).           */
+int sfno_sp_to_c64(const float* sp, int B, int C, int lmax, int mmax, int l_offset, int m_offset, void* out_c64,
+                   void* stream);
+int sfno_c64_to_sp(const void* in_c64, int B, int C, int lmax, int mmax, float* sp, void* stream);
+/* XM <-> complex64 [B][C][nlat][mmax]  (needed by the distributed SHT between its all-to-alls)   */
+int sfno_xm_to_c64(const float* xm, int B, int C, int nlat, int mmax, void* out_c64, void* stream);
+int sfno_c64_to_xm(const void* in_c64, int B, int C, int nlat, int mmax, float* xm, void* stream);
+
+/* y[b][c][h][w] (+)= bias   (spectral_convolution.py:143-144); bias_kind 0: [C], 1: [C][H][W]    */
+int sfno_add_bias(void* y, int y_dtype, const float* bias, int bias_kind, int B, int C, int H, int W,
+                  void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MAKANI_B200_H_ */

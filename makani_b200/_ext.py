@@ -1,0 +1,77 @@
+"""ctypes binding of the C-ABI library ``libmakani_b200.so`` (include/makani_b200.h).
+
+There is no fallback: if the library is missing or a call fails, this raises.  Build it in-tree with
+``python -c "import __graft_entry__ as g; g.build()"`` (or ``make -C makani_b200/csrc``).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libmakani_b200.so")
+
+F32, BF16, F16 = 0, 1, 2
+
+_vp, _i, _ll = C.c_void_p, C.c_int, C.c_longlong
+
+# name -> (restype, argtypes); mirrors include/makani_b200.h line by line
+_PROTOTYPES = {
+    "sfno_abi_version": (_i, []),
+    "sfno_last_error": (C.c_char_p, []),
+    "sfno_launch_count": (_ll, []),
+    "sfno_plan_create": (_i, [_i, _i, _i, _i, _i, _vp, C.POINTER(_vp)]),
+    "sfno_plan_destroy": (_i, [_vp]),
+    "sfno_xm_elems": (_ll, [_i, _i, _i, _i]),
+    "sfno_sp_elems": (_ll, [_i, _i, _i, _i]),
+    "sfno_wp_elems": (_ll, [_i, _i, _i]),
+    "sfno_dft_fwd": (_i, [_vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp]),
+    "sfno_dft_inv": (_i, [_vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _i, _vp]),
+    "sfno_legendre_analysis": (_i, [_vp, _vp, _i, _i, _vp, _vp]),
+    "sfno_legendre_synthesis": (_i, [_vp, _vp, _i, _i, _vp, _vp]),
+    "sfno_dhconv_pack_weight": (_i, [_vp, _i, _i, _i, _vp, _vp]),
+    "sfno_dhconv_unpack_wgrad": (_i, [_vp, _i, _i, _i, _vp, _vp]),
+    "sfno_dhconv_fwd": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
+    "sfno_dhconv_bwd_x": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
+    "sfno_dhconv_bwd_w": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
+    "sfno_diag_contract": (_i, [_i, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
+    "sfno_sp_to_c64": (_i, [_vp, _i, _i, _i, _i, _i, _i, _vp, _vp]),
+    "sfno_c64_to_sp": (_i, [_vp, _i, _i, _i, _i, _vp, _vp]),
+    "sfno_xm_to_c64": (_i, [_vp, _i, _i, _i, _i, _vp, _vp]),
+    "sfno_c64_to_xm": (_i, [_vp, _i, _i, _i, _i, _vp, _vp]),
+    "sfno_add_bias": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _i, _vp]),
+}
+
+EXPORTED_SYMBOLS = tuple(_PROTOTYPES)
+
+_lib = None
+
+
+def load():
+    """Load the shared library (once) and attach prototypes.  Raises if it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} not found: the CUDA extension has not been built and makani_b200 has no CPU fallback. "
+            "Run `python -c \"import __graft_entry__ as g; g.build()\"` from the repository root.")
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in _PROTOTYPES.items():
+        fn = getattr(lib, name)          # AttributeError if the header and the library disagree
+        fn.restype = res
+        fn.argtypes = args
+    if lib.sfno_abi_version() != 1:
+        raise ImportError(f"{LIB_PATH}: ABI version {lib.sfno_abi_version()} != 1")
+    _lib = lib
+    return lib
+
+
+def check(status: int, what: str):
+    if status != 0:
+        msg = load().sfno_last_error().decode("utf-8", "replace")
+        raise RuntimeError(f"makani_b200: {what} failed: {msg}")
+
+
+def launch_count() -> int:
+    return int(load().sfno_launch_count())

@@ -1,0 +1,506 @@
+// K1 / K5: longitude DFT kernels (real input -> first mmax bins; first mmax bins -> real output).
+//
+// Layout contract (see include/makani_b200.h):
+//   x  : [B*C][nlat][nlon]  (fp32 / bf16 / fp16, longitude contiguous)
+//   XM : [mmax][RS][Kp]     RS = 2*B*Cp, row r = (b*2+reim)*Cp + c, latitude contiguous
+// A CTA owns 16 consecutive "flat" positions f = c*Kp + lat of one batch entry b, so that for every
+// (m, reim) it reads / writes 16 consecutive floats of XM (the transpose between the longitude-major
+// field and the latitude-major Legendre operand happens in shared memory).
+//
+// Two families:
+//   * generic  - direct O(W*M) DFT with a shared-memory twiddle table; any nlon (used for odd sizes)
+//   * fft480   - register/shuffle FFT for nlon = 480*R, R in {1,3} (the SFNO grids 240x480 and 721x1440)
+#include "common.cuh"
+#include "plan.h"
+#include "fft_lane.cuh"
+
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <map>
+#include <mutex>
+#include <vector>
+#include <cmath>
+
+namespace sfno {
+
+// ------------------------------------------------------------------ twiddle tables (device cache)
+static std::map<std::pair<int, int>, float2*> g_tw_cache;
+static std::mutex g_tw_mutex;
+
+static int get_twiddles(int W, const float2** out) {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  std::lock_guard<std::mutex> lock(g_tw_mutex);
+  auto key = std::make_pair(dev, W);
+  auto it = g_tw_cache.find(key);
+  if (it != g_tw_cache.end()) {
+    *out = it->second;
+    return 0;
+  }
+  std::vector<float2> h(W);
+  for (int j = 0; j < W; ++j) {
+    double a = 2.0 * M_PI * (double)j / (double)W;
+    double c = cos(a), s = sin(a);
+    if (4 * j == W) { c = 0; s = 1; }
+    if (2 * j == W) { c = -1; s = 0; }
+    if (4 * j == 3 * W) { c = 0; s = -1; }
+    h[j] = make_float2((float)c, (float)s);
+  }
+  float2* d = nullptr;
+  SFNO_CUDA(cudaMalloc(&d, W * sizeof(float2)));
+  SFNO_CUDA(cudaMemcpy(d, h.data(), W * sizeof(float2), cudaMemcpyHostToDevice));
+  g_tw_cache[key] = d;
+  *out = d;
+  return 0;
+}
+
+template <typename T> __device__ __forceinline__ float to_f32(T v);
+template <> __device__ __forceinline__ float to_f32<float>(float v) { return v; }
+template <> __device__ __forceinline__ float to_f32<__nv_bfloat16>(__nv_bfloat16 v) { return __bfloat162float(v); }
+template <> __device__ __forceinline__ float to_f32<__half>(__half v) { return __half2float(v); }
+template <typename T> __device__ __forceinline__ T from_f32(float v);
+template <> __device__ __forceinline__ float from_f32<float>(float v) { return v; }
+template <> __device__ __forceinline__ __nv_bfloat16 from_f32<__nv_bfloat16>(float v) { return __float2bfloat16_rn(v); }
+template <> __device__ __forceinline__ __half from_f32<__half>(float v) { return __float2half_rn(v); }
+
+constexpr int kRows = 16;   // flat positions per CTA tile
+
+// ------------------------------------------------------------------ generic forward
+template <typename T>
+__global__ void __launch_bounds__(256)
+dft_fwd_generic_kernel(const T* __restrict__ x, float* __restrict__ xm, const float2* __restrict__ tw,
+                       const float* __restrict__ mscale, int B, int C, int K, int Kp, int W, int M) {
+  extern __shared__ float sm[];
+  const int Cp = (C + 3) & ~3;
+  const long long RS = 2LL * B * Cp;
+  const int flat = C * Kp;
+  const int tiles_per_b = (flat + kRows - 1) / kRows;
+  const int b = blockIdx.x / tiles_per_b;
+  const int f0 = (blockIdx.x % tiles_per_b) * kRows;
+  float* xs = sm;                                  // [kRows][W+1]
+  float2* tws = reinterpret_cast<float2*>(xs + kRows * (W + 1) + ((kRows * (W + 1)) & 1));   // [W]
+  float* outs = reinterpret_cast<float*>(tws + W);  // [2][M][kRows+1]
+
+  for (int j = threadIdx.x; j < W; j += blockDim.x) tws[j] = tw[j];
+  for (int r = 0; r < kRows; ++r) {
+    const int f = f0 + r;
+    const int c = f / Kp, lat = f % Kp;
+    const bool valid = (f < flat) && (lat < K);
+    const T* row = x + ((long long)(b * C + c) * K + lat) * W;
+    for (int w = threadIdx.x; w < W; w += blockDim.x) xs[r * (W + 1) + w] = valid ? to_f32<T>(row[w]) : 0.f;
+  }
+  __syncthreads();
+  for (int idx = threadIdx.x; idx < kRows * M; idx += blockDim.x) {
+    const int r = idx % kRows, m = idx / kRows;
+    const float* xr = xs + r * (W + 1);
+    float re = 0.f, im = 0.f;
+    int t = 0;
+    for (int w = 0; w < W; ++w) {
+      const float2 cs = tws[t];
+      const float v = xr[w];
+      re = fmaf(v, cs.x, re);
+      im = fmaf(-v, cs.y, im);
+      t += m;
+      if (t >= W) t -= W;
+    }
+    const float s = mscale[m];
+    outs[(0 * M + m) * (kRows + 1) + r] = re * s;
+    outs[(1 * M + m) * (kRows + 1) + r] = im * s;
+  }
+  __syncthreads();
+  for (int idx = threadIdx.x; idx < 2 * M * kRows; idx += blockDim.x) {
+    const int r = idx % kRows, pm = idx / kRows;
+    const int reim = pm / M, m = pm % M;
+    if (f0 + r < flat)
+      xm[((long long)m * RS + (long long)(b * 2 + reim) * Cp) * Kp + f0 + r] = outs[pm * (kRows + 1) + r];
+  }
+}
+
+// ------------------------------------------------------------------ generic inverse
+template <typename T>
+__global__ void __launch_bounds__(256)
+dft_inv_generic_kernel(const float* __restrict__ xm, T* __restrict__ y, const float2* __restrict__ tw,
+                       const float* __restrict__ mscale, int B, int C, int K, int Kp, int W, int M, int m_valid) {
+  extern __shared__ float sm[];
+  const int Cp = (C + 3) & ~3;
+  const long long RS = 2LL * B * Cp;
+  const int flat = C * Kp;
+  const int tiles_per_b = (flat + kRows - 1) / kRows;
+  const int b = blockIdx.x / tiles_per_b;
+  const int f0 = (blockIdx.x % tiles_per_b) * kRows;
+  float2* tws = reinterpret_cast<float2*>(sm);       // [W]
+  float* ins = reinterpret_cast<float*>(tws + W);    // [2][M][kRows+1]
+
+  for (int j = threadIdx.x; j < W; j += blockDim.x) tws[j] = tw[j];
+  for (int idx = threadIdx.x; idx < 2 * m_valid * kRows; idx += blockDim.x) {
+    const int r = idx % kRows, pm = idx / kRows;
+    const int reim = pm / m_valid, m = pm % m_valid;
+    float v = 0.f;
+    if (f0 + r < flat) v = xm[((long long)m * RS + (long long)(b * 2 + reim) * Cp) * Kp + f0 + r];
+    // irfft weights: the Hermitian pair of bin m doubles every bin except m = 0 and the Nyquist bin
+    const float cm = (m == 0 || 2 * m == W) ? 1.f : 2.f;
+    ins[(reim * M + m) * (kRows + 1) + r] = v * mscale[m] * cm;
+  }
+  __syncthreads();
+  for (int r = 0; r < kRows; ++r) {
+    const int f = f0 + r;
+    const int c = f / Kp, lat = f % Kp;
+    if (f >= flat || lat >= K) continue;
+    T* row = y + ((long long)(b * C + c) * K + lat) * W;
+    for (int w = threadIdx.x; w < W; w += blockDim.x) {
+      float acc = 0.f;
+      int t = 0;
+      for (int m = 0; m < m_valid; ++m) {
+        const float2 cs = tws[t];
+        acc = fmaf(ins[(0 * M + m) * (kRows + 1) + r], cs.x, acc);
+        acc = fmaf(-ins[(1 * M + m) * (kRows + 1) + r], cs.y, acc);
+        t += w;
+        if (t >= W) t -= W;
+      }
+      row[w] = from_f32<T>(acc);
+    }
+  }
+}
+
+// ------------------------------------------------------------------ fft480 family (nlon = 480 * R)
+struct DeviceWarp16 {
+  __device__ __forceinline__ int lane16() const { return threadIdx.x & 15; }
+  __device__ __forceinline__ float shfl_xor(float v, int mask) const { return __shfl_xor_sync(0xffffffffu, v, mask); }
+  __device__ __forceinline__ float shfl_idx(float v, int src) const {
+    return __shfl_sync(0xffffffffu, v, (threadIdx.x & 16) | src);
+  }
+};
+
+// device tables for the fft480 family: tw240[240] | tw480[241] | tw1440[241]   (fl::cf each)
+constexpr int kTwCount = 240 + 241 + 241;
+static std::map<int, fl::cf*> g_fft_tw_cache;
+
+static int get_fft_tables(const fl::cf** out) {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  std::lock_guard<std::mutex> lock(g_tw_mutex);
+  auto it = g_fft_tw_cache.find(dev);
+  if (it != g_fft_tw_cache.end()) {
+    *out = it->second;
+    return 0;
+  }
+  std::vector<fl::cf> h(kTwCount);
+  for (int b = 0; b < 16; ++b)
+    for (int k1 = 0; k1 < 15; ++k1) {
+      double a = -2.0 * M_PI * (double)(b * k1) / 240.0;
+      h[b * 15 + k1] = fl::mk((float)cos(a), (float)sin(a));
+    }
+  for (int k = 0; k < 241; ++k) {
+    double a = -2.0 * M_PI * (double)k / 480.0;
+    h[240 + k] = fl::mk((float)cos(a), (float)sin(a));
+    double c = -2.0 * M_PI * (double)k / 1440.0;
+    h[240 + 241 + k] = fl::mk((float)cos(c), (float)sin(c));
+  }
+  h[240 + 120] = fl::mk(0.f, -1.f);
+  h[240 + 240] = fl::mk(-1.f, 0.f);
+  fl::cf* d = nullptr;
+  SFNO_CUDA(cudaMalloc(&d, kTwCount * sizeof(fl::cf)));
+  SFNO_CUDA(cudaMemcpy(d, h.data(), kTwCount * sizeof(fl::cf), cudaMemcpyHostToDevice));
+  g_fft_tw_cache[dev] = d;
+  *out = d;
+  return 0;
+}
+
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(smem_dst)), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() {
+  asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
+}
+
+__device__ __forceinline__ void lane_butterfly_twiddles(fl::cf (&bf)[4]) {
+  const int lane = threadIdx.x & 15;
+#pragma unroll
+  for (int s = 0; s < 4; ++s) {
+    const int d = 1 << s;
+    float sn, cs;
+    sincospif(-(float)(lane & (d - 1)) / (float)d, &sn, &cs);      // e^{-2 pi i j / (2d)}
+    bf[s] = fl::mk(cs, sn);
+  }
+}
+
+template <int R, typename T>
+struct FftSmem {
+  static constexpr int W = 480 * R;
+  static constexpr int kRowStride = W + 16 / (int)sizeof(T);         // elements; keeps 16 B alignment, skews banks
+  static constexpr int kRawBytes = kRows * kRowStride * (int)sizeof(T);
+  static constexpr int kStageBytes = 2 * 241 * (kRows + 1) * 4;
+  static constexpr int kBufBytes = ((kRawBytes > kStageBytes ? kRawBytes : kStageBytes) + 15) & ~15;
+  static constexpr int kBytes = kBufBytes + kTwCount * 8 + 241 * 4 + 16;
+};
+
+// forward: x rows -> XM.  256 threads = 16 rows x 16 lanes; persistent over tiles of 16 flat positions.
+template <int R, typename T>
+__global__ void __launch_bounds__(256, 2)
+dft_fwd_fft480_kernel(const T* __restrict__ x, float* __restrict__ xm, const fl::cf* __restrict__ tables,
+                      const float* __restrict__ mscale, int B, int C, int K, int Kp, int M) {
+  using S = FftSmem<R, T>;
+  constexpr int W = S::W;
+  extern __shared__ __align__(16) uint8_t smraw[];
+  T* raw = reinterpret_cast<T*>(smraw);
+  float* stage = reinterpret_cast<float*>(smraw);                     // aliases raw (used after the FFT)
+  fl::cf* tw = reinterpret_cast<fl::cf*>(smraw + S::kBufBytes);
+  float* msc = reinterpret_cast<float*>(tw + kTwCount);
+
+  for (int j = threadIdx.x; j < kTwCount; j += blockDim.x) tw[j] = tables[j];
+  for (int j = threadIdx.x; j < 241; j += blockDim.x) msc[j] = j < M ? mscale[j] : 0.f;
+  fl::cf bf[4];
+  lane_butterfly_twiddles(bf);
+
+  const int Cp = (C + 3) & ~3;
+  const long long RS = 2LL * B * Cp;
+  const int flat = C * Kp;
+  const int tiles_per_b = (flat + kRows - 1) / kRows;
+  const int ntiles = tiles_per_b * B;
+  const int r = threadIdx.x >> 4;
+  const int lane = threadIdx.x & 15;
+  const int k2 = fl::bitrev4(lane);
+  constexpr int kChunks = W * (int)sizeof(T) / 16;                    // 16-byte chunks per row
+  DeviceWarp16 warp;
+
+  for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    const int b = tile / tiles_per_b;
+    const int f0 = (tile % tiles_per_b) * kRows;
+    // ---- 1. rows -> smem (coalesced 16 B async copies); padded / out-of-range rows are zero filled
+    for (int idx = threadIdx.x; idx < kRows * kChunks; idx += blockDim.x) {
+      const int rr = idx / kChunks, ch = idx % kChunks;
+      const int f = f0 + rr;
+      const int c = f / Kp, lat = f % Kp;
+      uint8_t* dst = reinterpret_cast<uint8_t*>(raw + rr * S::kRowStride) + ch * 16;
+      if (f < flat && lat < K) {
+        const uint8_t* src = reinterpret_cast<const uint8_t*>(x + ((long long)(b * C + c) * K + lat) * W) + ch * 16;
+        cp_async16(dst, src);
+      } else {
+        *reinterpret_cast<uint4*>(dst) = make_uint4(0, 0, 0, 0);
+      }
+    }
+    cp_async_wait_all();
+    __syncthreads();
+    // ---- 2. per-row FFT in registers / shuffles
+    fl::cf X[15], x240;
+    const T* myrow = raw + r * S::kRowStride;
+    fl::rfft_row_fwd<R>(warp, [&](int i) { return to_f32<T>(myrow[i]); }, X, x240, tw, tw + 240, tw + 481, bf);
+    __syncthreads();
+    // ---- 3. transpose through smem: stage[reim][m][row]
+#pragma unroll
+    for (int k1 = 0; k1 < 15; ++k1) {
+      const int m = k1 + 15 * k2;
+      if (m < M) {
+        const float s = msc[m];
+        stage[(0 * 241 + m) * (kRows + 1) + r] = X[k1].x * s;
+        stage[(1 * 241 + m) * (kRows + 1) + r] = X[k1].y * s;
+      }
+    }
+    if (lane == 0 && 240 < M) {
+      const float s = msc[240];
+      stage[(0 * 241 + 240) * (kRows + 1) + r] = x240.x * s;
+      stage[(1 * 241 + 240) * (kRows + 1) + r] = x240.y * s;
+    }
+    __syncthreads();
+    for (int idx = threadIdx.x; idx < 2 * M * kRows; idx += blockDim.x) {
+      const int rr = idx % kRows, pm = idx / kRows;
+      const int reim = pm / M, m = pm % M;
+      if (f0 + rr < flat)
+        xm[((long long)m * RS + (long long)(b * 2 + reim) * Cp) * Kp + f0 + rr] =
+            stage[(reim * 241 + m) * (kRows + 1) + rr];
+    }
+    __syncthreads();
+  }
+}
+
+// inverse: XM -> y rows.
+template <int R, typename T>
+__global__ void __launch_bounds__(256, 2)
+dft_inv_fft480_kernel(const float* __restrict__ xm, T* __restrict__ y, const fl::cf* __restrict__ tables,
+                      const float* __restrict__ mscale, int B, int C, int K, int Kp, int M, int m_valid) {
+  using S = FftSmem<R, T>;
+  constexpr int W = S::W;
+  extern __shared__ __align__(16) uint8_t smraw[];
+  T* raw = reinterpret_cast<T*>(smraw);
+  float* stage = reinterpret_cast<float*>(smraw);
+  fl::cf* tw = reinterpret_cast<fl::cf*>(smraw + S::kBufBytes);
+  float* msc = reinterpret_cast<float*>(tw + kTwCount);
+
+  for (int j = threadIdx.x; j < kTwCount; j += blockDim.x) tw[j] = tables[j];
+  for (int j = threadIdx.x; j < 241; j += blockDim.x) msc[j] = j < m_valid ? mscale[j] : 0.f;
+  fl::cf bf[4];
+  lane_butterfly_twiddles(bf);
+
+  const int Cp = (C + 3) & ~3;
+  const long long RS = 2LL * B * Cp;
+  const int flat = C * Kp;
+  const int tiles_per_b = (flat + kRows - 1) / kRows;
+  const int ntiles = tiles_per_b * B;
+  const int r = threadIdx.x >> 4;
+  const int lane = threadIdx.x & 15;
+  const int k2 = fl::bitrev4(lane);
+  constexpr int kChunks = W * (int)sizeof(T) / 16;
+  DeviceWarp16 warp;
+  __syncthreads();
+
+  for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    const int b = tile / tiles_per_b;
+    const int f0 = (tile % tiles_per_b) * kRows;
+    // ---- 1. XM -> stage[reim][m][row] (16 consecutive floats per (m, reim)), scaled
+    for (int idx = threadIdx.x; idx < 2 * 241 * kRows; idx += blockDim.x) {
+      const int rr = idx % kRows, pm = idx / kRows;
+      const int reim = pm / 241, m = pm % 241;
+      float v = 0.f;
+      if (m < m_valid && f0 + rr < flat)
+        v = xm[((long long)m * RS + (long long)(b * 2 + reim) * Cp) * Kp + f0 + rr] * msc[m];
+      stage[(reim * 241 + m) * (kRows + 1) + rr] = v;
+    }
+    __syncthreads();
+    // ---- 2. gather this lane's bins into registers, then the stage buffer may be overwritten
+    fl::cf H[15], HP[15];
+#pragma unroll
+    for (int k1 = 0; k1 < 15; ++k1) {
+      const int k = k1 + 15 * k2, kp = 240 - k;
+      H[k1] = fl::mk(stage[(0 * 241 + k) * (kRows + 1) + r], stage[(1 * 241 + k) * (kRows + 1) + r]);
+      HP[k1] = fl::mk(stage[(0 * 241 + kp) * (kRows + 1) + r], stage[(1 * 241 + kp) * (kRows + 1) + r]);
+    }
+    __syncthreads();
+    T* myrow = raw + r * S::kRowStride;
+    fl::irfft_row<R>(warp, H, HP, [&](int i, float v) { myrow[i] = from_f32<T>(v); }, tw, tw + 240, tw + 481, bf);
+    __syncthreads();
+    // ---- 3. rows -> global, 16 B vectors
+    for (int idx = threadIdx.x; idx < kRows * kChunks; idx += blockDim.x) {
+      const int rr = idx / kChunks, ch = idx % kChunks;
+      const int f = f0 + rr;
+      const int c = f / Kp, lat = f % Kp;
+      if (f < flat && lat < K) {
+        const uint4 v = *reinterpret_cast<const uint4*>(reinterpret_cast<const uint8_t*>(raw + rr * S::kRowStride) + ch * 16);
+        *reinterpret_cast<uint4*>(reinterpret_cast<uint8_t*>(y + ((long long)(b * C + c) * K + lat) * W) + ch * 16) = v;
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// ------------------------------------------------------------------ host dispatch
+static int sm_count() {
+  static int n = 0;
+  if (!n) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    if (n <= 0) n = 148;
+  }
+  return n;
+}
+
+template <int R, typename T>
+static int launch_fwd_fft(const void* x, int B, int C, int K, int Kp, int M, const float* mscale, float* xm,
+                          cudaStream_t stream) {
+  using S = FftSmem<R, T>;
+  const fl::cf* tables;
+  if (get_fft_tables(&tables)) return 1;
+  static bool attr = false;
+  if (!attr) {
+    SFNO_CUDA(cudaFuncSetAttribute(dft_fwd_fft480_kernel<R, T>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kBytes));
+    attr = true;
+  }
+  const int ntiles = ((C * Kp + kRows - 1) / kRows) * B;
+  const int grid = std::min(ntiles, 2 * sm_count());
+  dft_fwd_fft480_kernel<R, T><<<grid, 256, S::kBytes, stream>>>(static_cast<const T*>(x), xm, tables, mscale, B, C, K, Kp, M);
+  SFNO_LAUNCHED();
+  return 0;
+}
+template <int R, typename T>
+static int launch_inv_fft(const float* xm, int B, int C, int K, int Kp, int M, int m_valid, const float* mscale,
+                          void* y, cudaStream_t stream) {
+  using S = FftSmem<R, T>;
+  const fl::cf* tables;
+  if (get_fft_tables(&tables)) return 1;
+  static bool attr = false;
+  if (!attr) {
+    SFNO_CUDA(cudaFuncSetAttribute(dft_inv_fft480_kernel<R, T>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kBytes));
+    attr = true;
+  }
+  const int ntiles = ((C * Kp + kRows - 1) / kRows) * B;
+  const int grid = std::min(ntiles, 2 * sm_count());
+  dft_inv_fft480_kernel<R, T><<<grid, 256, S::kBytes, stream>>>(xm, static_cast<T*>(y), tables, mscale, B, C, K, Kp, M, m_valid);
+  SFNO_LAUNCHED();
+  return 0;
+}
+
+template <typename T>
+static int launch_fwd_generic(const void* x, int B, int C, int K, int Kp, int W, int M, const float* mscale, float* xm,
+                              cudaStream_t stream) {
+  const float2* tw;
+  if (get_twiddles(W, &tw)) return 1;
+  const size_t smem = (size_t)(kRows * (W + 1) + 2 * W + 2 * M * (kRows + 1)) * 4 + 16;
+  SFNO_CHECK(smem <= 200 * 1024, "generic DFT: nlon too large for the shared-memory kernel");
+  SFNO_CUDA(cudaFuncSetAttribute(dft_fwd_generic_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+  const int ntiles = ((C * Kp + kRows - 1) / kRows) * B;
+  dft_fwd_generic_kernel<T><<<ntiles, 256, smem, stream>>>(static_cast<const T*>(x), xm, tw, mscale, B, C, K, Kp, W, M);
+  SFNO_LAUNCHED();
+  return 0;
+}
+template <typename T>
+static int launch_inv_generic(const float* xm, int B, int C, int K, int Kp, int W, int M, int m_valid,
+                              const float* mscale, void* y, cudaStream_t stream) {
+  const float2* tw;
+  if (get_twiddles(W, &tw)) return 1;
+  const size_t smem = (size_t)(2 * W + 2 * M * (kRows + 1)) * 4 + 16;
+  SFNO_CHECK(smem <= 200 * 1024, "generic inverse DFT: sizes too large for the shared-memory kernel");
+  SFNO_CUDA(cudaFuncSetAttribute(dft_inv_generic_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+  const int ntiles = ((C * Kp + kRows - 1) / kRows) * B;
+  dft_inv_generic_kernel<T><<<ntiles, 256, smem, stream>>>(xm, static_cast<T*>(y), tw, mscale, B, C, K, Kp, W, M, m_valid);
+  SFNO_LAUNCHED();
+  return 0;
+}
+
+static bool use_fft480(int W, int M, const void* p) {
+  const char* env = getenv("SFNO_FORCE_GENERIC_DFT");
+  if (env && env[0] == '1') return false;
+  return (W == 480 || W == 1440) && M <= 241 && (reinterpret_cast<uintptr_t>(p) & 15) == 0;
+}
+
+int dft_fwd(const void* x, int x_dtype, int B, int C, int nlat, int nlon, int mmax, const float* mscale,
+            float* xm, cudaStream_t stream) {
+  SFNO_CHECK(mmax <= nlon / 2 + 1, "mmax exceeds nlon/2+1");
+  const int Kp = round_up(nlat, 4);
+  const bool fast = use_fft480(nlon, mmax, x);
+#define SFNO_DISPATCH_FWD(T)                                                                           \
+  do {                                                                                                 \
+    if (fast && nlon == 480) return launch_fwd_fft<1, T>(x, B, C, nlat, Kp, mmax, mscale, xm, stream); \
+    if (fast && nlon == 1440) return launch_fwd_fft<3, T>(x, B, C, nlat, Kp, mmax, mscale, xm, stream);\
+    return launch_fwd_generic<T>(x, B, C, nlat, Kp, nlon, mmax, mscale, xm, stream);                   \
+  } while (0)
+  switch (x_dtype) {
+    case SFNO_F32: SFNO_DISPATCH_FWD(float);
+    case SFNO_BF16: SFNO_DISPATCH_FWD(__nv_bfloat16);
+    case SFNO_F16: SFNO_DISPATCH_FWD(__half);
+    default: SFNO_CHECK(false, "unsupported input dtype");
+  }
+#undef SFNO_DISPATCH_FWD
+}
+
+int dft_inv(const float* xm, int B, int C, int nlat, int nlon, int mmax, int m_valid, const float* mscale,
+            void* y, int y_dtype, cudaStream_t stream) {
+  SFNO_CHECK(mmax <= nlon / 2 + 1, "mmax exceeds nlon/2+1");
+  const int Kp = round_up(nlat, 4);
+  m_valid = std::min(m_valid, mmax);
+  const bool fast = use_fft480(nlon, mmax, y);
+#define SFNO_DISPATCH_INV(T)                                                                                    \
+  do {                                                                                                          \
+    if (fast && nlon == 480) return launch_inv_fft<1, T>(xm, B, C, nlat, Kp, mmax, m_valid, mscale, y, stream); \
+    if (fast && nlon == 1440) return launch_inv_fft<3, T>(xm, B, C, nlat, Kp, mmax, m_valid, mscale, y, stream);\
+    return launch_inv_generic<T>(xm, B, C, nlat, Kp, nlon, mmax, m_valid, mscale, y, stream);                   \
+  } while (0)
+  switch (y_dtype) {
+    case SFNO_F32: SFNO_DISPATCH_INV(float);
+    case SFNO_BF16: SFNO_DISPATCH_INV(__nv_bfloat16);
+    case SFNO_F16: SFNO_DISPATCH_INV(__half);
+    default: SFNO_CHECK(false, "unsupported output dtype");
+  }
+#undef SFNO_DISPATCH_INV
+}
+
+}  // namespace sfno

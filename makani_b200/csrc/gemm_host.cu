@@ -1,0 +1,343 @@
+// Host side of the tcgen05 batched GEMM: tile-list construction (triangular skipping, cost-sorted),
+// TMA tensor-map encoding, launches.  See gemm_tc.cuh for the kernel and the five contraction modes.
+#include "gemm_tc.cuh"
+#include "plan.h"
+
+#include <algorithm>
+#include <map>
+#include <mutex>
+#include <tuple>
+#include <vector>
+
+namespace sfno {
+
+// ------------------------------------------------------------------ TMA encode through the driver entry point
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static PFN_encodeTiled get_encode_fn() {
+  static PFN_encodeTiled fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<PFN_encodeTiled>(p);
+  });
+  return fn;
+}
+
+int encode_tensor_map(CUtensorMap* map, const void* gptr, int rank, const uint64_t* dims,
+                      const uint64_t* strides_bytes, const uint32_t* box, bool swizzle128) {
+  PFN_encodeTiled fn = get_encode_fn();
+  SFNO_CHECK(fn != nullptr, "cuTensorMapEncodeTiled entry point not available (no CUDA driver?)");
+  cuuint64_t d[5];
+  cuuint64_t s[4];
+  cuuint32_t b[5], e[5];
+  for (int i = 0; i < rank; ++i) {
+    d[i] = dims[i];
+    b[i] = box[i];
+    e[i] = 1;
+  }
+  for (int i = 0; i + 1 < rank; ++i) {
+    s[i] = strides_bytes[i];
+    SFNO_CHECK(s[i] % 16 == 0, "TMA global stride must be a multiple of 16 bytes");
+  }
+  SFNO_CHECK((reinterpret_cast<uintptr_t>(gptr) & 15) == 0, "TMA global address must be 16-byte aligned");
+  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, (cuuint32_t)rank, const_cast<void*>(gptr), d, s, b, e,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  swizzle128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  SFNO_CHECK(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with code " + std::to_string((int)r));
+  return 0;
+}
+
+// ------------------------------------------------------------------ tile lists (cached on the device)
+struct TileList {
+  GemmTile* dev = nullptr;
+  int count = 0;
+};
+typedef std::tuple<int, int, int, int, int, int, int, int, int> TileKey;   // device, mode, dims...
+static std::map<TileKey, TileList> g_tile_cache;
+static std::mutex g_tile_mutex;
+
+static int floor_to(int x, int m) { return x / m * m; }
+
+// valid local-m extent of row l of an SP tensor: global m < min(M, round_up(l_glob + 1, 16))
+int sp_mhi(int l_local, int l_offset, int m_offset, int M_local) {
+  int hi = round_up(l_local + l_offset + 1, 16) - m_offset;
+  return std::max(0, std::min(M_local, hi));
+}
+
+static int upload_tiles(std::vector<GemmTile>& tiles, TileList* out) {
+  // longest-processing-time first: static round-robin over a cost-sorted list balances the triangular work
+  std::stable_sort(tiles.begin(), tiles.end(), [](const GemmTile& a, const GemmTile& b) {
+    return (long long)a.nkk * a.n_mma > (long long)b.nkk * b.n_mma;
+  });
+  out->count = (int)tiles.size();
+  if (tiles.empty()) return 0;
+  SFNO_CUDA(cudaMalloc(&out->dev, tiles.size() * sizeof(GemmTile)));
+  SFNO_CUDA(cudaMemcpy(out->dev, tiles.data(), tiles.size() * sizeof(GemmTile), cudaMemcpyHostToDevice));
+  return 0;
+}
+
+static int get_tiles(const TileKey& key, const std::function<void(std::vector<GemmTile>&)>& build, TileList* out) {
+  std::lock_guard<std::mutex> lock(g_tile_mutex);
+  auto it = g_tile_cache.find(key);
+  if (it != g_tile_cache.end()) {
+    *out = it->second;
+    return 0;
+  }
+  std::vector<GemmTile> tiles;
+  build(tiles);
+  TileList tl;
+  if (upload_tiles(tiles, &tl)) return 1;
+  g_tile_cache[key] = tl;
+  *out = tl;
+  return 0;
+}
+
+static int num_sms() {
+  static int n = 0;
+  if (!n) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    if (n <= 0) n = 148;
+  }
+  return n;
+}
+
+template <int MODE>
+static int launch(const CUtensorMap& ma, const CUtensorMap& mb, const GemmArgs& args, cudaStream_t stream) {
+  using Cfg = GemmCfg<MODE>;
+  if (args.num_tiles == 0) return 0;
+  static bool attr_set = false;
+  if (!attr_set) {
+    SFNO_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   Cfg::kSmemBytes));
+    attr_set = true;
+  }
+  int grid = std::min(args.num_tiles, num_sms());
+  gemm_tc_kernel<MODE><<<grid, kGemmThreads, Cfg::kSmemBytes, stream>>>(ma, mb, args);
+  SFNO_LAUNCHED();
+  return 0;
+}
+
+static int current_device() {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  return dev;
+}
+
+// ------------------------------------------------------------------ Legendre analysis  (K2)
+int legendre_analysis(const sfno_plan* plan, const float* xm, int B, int C, float* sp, cudaStream_t stream) {
+  const int K = plan->nlat, Kp = plan->Kp, L = plan->lmax, M = plan->mmax, moff = plan->m_offset;
+  const int RS = 2 * B * round_up(C, 4);
+  CUtensorMap ma, mb;
+  {
+    uint64_t dims[3] = {(uint64_t)K, (uint64_t)RS, (uint64_t)M};
+    uint64_t str[2] = {(uint64_t)Kp * 4, (uint64_t)RS * Kp * 4};
+    uint32_t box[3] = {32, 128, 1};
+    if (encode_tensor_map(&ma, xm, 3, dims, str, box, true)) return 1;
+  }
+  {
+    uint64_t dims[3] = {(uint64_t)K, (uint64_t)L, (uint64_t)M};
+    uint64_t str[2] = {(uint64_t)Kp * 4, (uint64_t)L * Kp * 4};
+    uint32_t box[3] = {32, 64, 1};
+    if (encode_tensor_map(&mb, plan->table, 3, dims, str, box, true)) return 1;
+  }
+  TileList tl;
+  TileKey key{current_device(), LEG_ANA, K, L, M, moff, RS, 0, 0};
+  if (get_tiles(key, [&](std::vector<GemmTile>& tiles) {
+        for (int m = 0; m < M; ++m) {
+          const int n0 = floor_to(m + moff, 16);
+          for (int c0 = n0; c0 < L; c0 += 256) {
+            const int ncols = std::min(256, L - c0);
+            for (int r0 = 0; r0 < RS; r0 += 128) {
+              GemmTile t{m, r0, c0, round_up(ncols, 16), 0, (K + 7) / 8, c0 + ncols, 0};
+              tiles.push_back(t);
+            }
+          }
+        }
+      }, &tl))
+    return 1;
+  GemmArgs args;
+  args.out = sp;
+  args.tiles = tl.dev;
+  args.num_tiles = tl.count;
+  args.row_limit = RS;
+  args.out_g_stride = RS;                       // SP[l][m][r]: g = m
+  args.out_col_stride = (long long)M * RS;      // column = l
+  args.out_im_offset = 0;
+  return launch<LEG_ANA>(ma, mb, args, stream);
+}
+
+// ------------------------------------------------------------------ Legendre synthesis  (K4)
+int legendre_synthesis(const sfno_plan* plan, const float* sp, int B, int C, float* xm, cudaStream_t stream) {
+  const int K = plan->nlat, Kp = plan->Kp, L = plan->lmax, M = plan->mmax, moff = plan->m_offset;
+  const int RS = 2 * B * round_up(C, 4);
+  CUtensorMap ma, mb;
+  {
+    uint64_t dims[3] = {(uint64_t)K, (uint64_t)L, (uint64_t)M};
+    uint64_t str[2] = {(uint64_t)Kp * 4, (uint64_t)L * Kp * 4};
+    uint32_t box[3] = {32, 32, 1};
+    if (encode_tensor_map(&ma, plan->table, 3, dims, str, box, true)) return 1;
+  }
+  {
+    uint64_t dims[3] = {(uint64_t)RS, (uint64_t)M, (uint64_t)L};
+    uint64_t str[2] = {(uint64_t)RS * 4, (uint64_t)M * RS * 4};
+    uint32_t box[3] = {32, 1, 32};
+    if (encode_tensor_map(&mb, sp, 3, dims, str, box, true)) return 1;
+  }
+  TileList tl;
+  TileKey key{current_device(), LEG_SYN, K, L, M, moff, RS, 0, 0};
+  if (get_tiles(key, [&](std::vector<GemmTile>& tiles) {
+        for (int m = 0; m < M; ++m) {
+          const int l0 = std::min(L, floor_to(m + moff, 8));
+          const int nkk = (L - l0 + 7) / 8;        // 0 => this m has no degrees: zeros are written
+          for (int c0 = 0; c0 < RS; c0 += 256) {
+            const int ncols = std::min(256, RS - c0);
+            for (int r0 = 0; r0 < K; r0 += 128) {
+              GemmTile t{m, r0, c0, round_up(ncols, 16), l0, nkk, c0 + ncols, 0};
+              tiles.push_back(t);
+            }
+          }
+        }
+      }, &tl))
+    return 1;
+  GemmArgs args;
+  args.out = xm;
+  args.tiles = tl.dev;
+  args.num_tiles = tl.count;
+  args.row_limit = K;
+  args.out_g_stride = (long long)RS * Kp;       // XM[m][r][k]: g = m
+  args.out_col_stride = Kp;                     // column = r
+  args.out_im_offset = 0;
+  return launch<LEG_SYN>(ma, mb, args, stream);
+}
+
+// ------------------------------------------------------------------ dhconv  (K3 fwd / bwd-x / bwd-w)
+// SP_in  : [L][M][B][2][Cinp]     SP_out : [L][M][B][2][Coutp]     WP : [L][2][Coutp][Cinp]
+static int sp_map_kmajor(CUtensorMap* map, const float* sp, int C, int B, int L, int M) {
+  const int Cp = round_up(C, 4);
+  uint64_t dims[4] = {(uint64_t)C, 2, (uint64_t)M * B, (uint64_t)L};
+  uint64_t str[3] = {(uint64_t)Cp * 4, (uint64_t)2 * Cp * 4, (uint64_t)M * B * 2 * Cp * 4};
+  uint32_t box[4] = {32, 1, 64, 1};
+  return encode_tensor_map(map, sp, 4, dims, str, box, true);
+}
+static int sp_map_mnmajor(CUtensorMap* map, const float* sp, int C, int B, int L, int M) {
+  const int Cp = round_up(C, 4);
+  uint64_t dims[4] = {(uint64_t)C, 2, (uint64_t)M * B, (uint64_t)L};
+  uint64_t str[3] = {(uint64_t)Cp * 4, (uint64_t)2 * Cp * 4, (uint64_t)M * B * 2 * Cp * 4};
+  uint32_t box[4] = {32, 1, 32, 1};
+  return encode_tensor_map(map, sp, 4, dims, str, box, true);
+}
+static int wp_map(CUtensorMap* map, const float* wp, int Cin, int Cout, int L, bool mn_major) {
+  const int Cinp = round_up(Cin, 4), Coutp = round_up(Cout, 4);
+  uint64_t dims[4] = {(uint64_t)Cin, (uint64_t)Cout, 2, (uint64_t)L};
+  uint64_t str[3] = {(uint64_t)Cinp * 4, (uint64_t)Coutp * Cinp * 4, (uint64_t)2 * Coutp * Cinp * 4};
+  uint32_t box_k[4] = {32, 128, 1, 1};
+  uint32_t box_mn[4] = {32, 32, 1, 1};
+  return encode_tensor_map(map, wp, 4, dims, str, mn_major ? box_mn : box_k, true);
+}
+
+int dhconv_fwd(const float* sp_in, const float* wp, float* sp_out, int B, int Cin, int Cout, int L, int M,
+               int l_offset, int m_offset, cudaStream_t stream) {
+  CUtensorMap ma, mb;
+  if (wp_map(&ma, wp, Cin, Cout, L, false)) return 1;
+  if (sp_map_kmajor(&mb, sp_in, Cin, B, L, M)) return 1;
+  TileList tl;
+  TileKey key{current_device(), DH_FWD, Cin, Cout, L, M, B, l_offset, m_offset};
+  if (get_tiles(key, [&](std::vector<GemmTile>& tiles) {
+        for (int l = 0; l < L; ++l) {
+          const int nn = sp_mhi(l, l_offset, m_offset, M) * B;
+          for (int c0 = 0; c0 < nn; c0 += 128) {
+            const int ncols = std::min(128, nn - c0);
+            for (int r0 = 0; r0 < Cout; r0 += 128) {
+              GemmTile t{l, r0, c0, round_up(ncols, 16), 0, (Cin + 7) / 8, c0 + ncols, 0};
+              tiles.push_back(t);
+            }
+          }
+        }
+      }, &tl))
+    return 1;
+  const int Coutp = round_up(Cout, 4);
+  GemmArgs args;
+  args.out = sp_out;
+  args.tiles = tl.dev;
+  args.num_tiles = tl.count;
+  args.row_limit = Cout;
+  args.out_g_stride = (long long)M * B * 2 * Coutp;
+  args.out_col_stride = 2 * Coutp;              // column = n = m*B + b
+  args.out_im_offset = Coutp;
+  return launch<DH_FWD>(ma, mb, args, stream);
+}
+
+int dhconv_bwd_x(const float* gsp_out, const float* wp, float* gsp_in, int B, int Cin, int Cout, int L, int M,
+                 int l_offset, int m_offset, cudaStream_t stream) {
+  CUtensorMap ma, mb;
+  if (wp_map(&ma, wp, Cin, Cout, L, true)) return 1;
+  if (sp_map_kmajor(&mb, gsp_out, Cout, B, L, M)) return 1;
+  TileList tl;
+  TileKey key{current_device(), DH_BWDX, Cin, Cout, L, M, B, l_offset, m_offset};
+  if (get_tiles(key, [&](std::vector<GemmTile>& tiles) {
+        for (int l = 0; l < L; ++l) {
+          const int nn = sp_mhi(l, l_offset, m_offset, M) * B;
+          for (int c0 = 0; c0 < nn; c0 += 128) {
+            const int ncols = std::min(128, nn - c0);
+            for (int r0 = 0; r0 < Cin; r0 += 128) {
+              GemmTile t{l, r0, c0, round_up(ncols, 16), 0, (Cout + 7) / 8, c0 + ncols, 0};
+              tiles.push_back(t);
+            }
+          }
+        }
+      }, &tl))
+    return 1;
+  const int Cinp = round_up(Cin, 4);
+  GemmArgs args;
+  args.out = gsp_in;
+  args.tiles = tl.dev;
+  args.num_tiles = tl.count;
+  args.row_limit = Cin;
+  args.out_g_stride = (long long)M * B * 2 * Cinp;
+  args.out_col_stride = 2 * Cinp;
+  args.out_im_offset = Cinp;
+  return launch<DH_BWDX>(ma, mb, args, stream);
+}
+
+int dhconv_bwd_w(const float* sp_in, const float* gsp_out, float* gwp, int B, int Cin, int Cout, int L, int M,
+                 int l_offset, int m_offset, cudaStream_t stream) {
+  CUtensorMap ma, mb;
+  if (sp_map_mnmajor(&ma, sp_in, Cin, B, L, M)) return 1;
+  if (sp_map_mnmajor(&mb, gsp_out, Cout, B, L, M)) return 1;
+  TileList tl;
+  TileKey key{current_device(), DH_BWDW, Cin, Cout, L, M, B, l_offset, m_offset};
+  if (get_tiles(key, [&](std::vector<GemmTile>& tiles) {
+        for (int l = 0; l < L; ++l) {
+          const int nn = sp_mhi(l, l_offset, m_offset, M) * B;      // contraction extent (multiple of 8 or clipped by M*B)
+          for (int c0 = 0; c0 < Cout; c0 += 128) {
+            const int ncols = std::min(128, Cout - c0);
+            for (int r0 = 0; r0 < Cin; r0 += 128) {
+              GemmTile t{l, r0, c0, round_up(ncols, 16), 0, (nn + 7) / 8, c0 + ncols, 0};
+              tiles.push_back(t);
+            }
+          }
+        }
+      }, &tl))
+    return 1;
+  const int Cinp = round_up(Cin, 4), Coutp = round_up(Cout, 4);
+  GemmArgs args;
+  args.out = gwp;
+  args.tiles = tl.dev;
+  args.num_tiles = tl.count;
+  args.row_limit = Cin;
+  args.out_g_stride = (long long)2 * Coutp * Cinp;   // WP[l][reim][o][i]: rows = i, columns = o
+  args.out_col_stride = Cinp;
+  args.out_im_offset = (long long)Coutp * Cinp;
+  return launch<DH_BWDW>(ma, mb, args, stream);
+}
+
+}  // namespace sfno

@@ -1,0 +1,352 @@
+// Bandwidth kernels around the tensor-core path: layout conversions at the module boundary
+// (spectral-internal <-> complex64 tensors of the reference API), dhconv weight (un)packing, bias add,
+// and the "diagonal" channel contraction (weights streamed once; no reuse, so no tensor cores).
+// All global accesses are coalesced on both sides through 32x32 shared-memory tile transposes.
+#include "common.cuh"
+#include "plan.h"
+
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <algorithm>
+
+namespace sfno {
+
+// ------------------------------------------------------------------ SP <-> complex64 [B][C][L][M]
+// grid (ceil(M/32), ceil(C/32), L*B), block (32, 8)
+__global__ void sp_to_c64_kernel(const float* __restrict__ sp, float2* __restrict__ out, int B, int C, int L, int M,
+                                 int l_off, int m_off) {
+  __shared__ float tr[32][33], ti[32][33];
+  const int Cp = (C + 3) & ~3;
+  const long long RS = 2LL * B * Cp;
+  const int l = blockIdx.z / B, b = blockIdx.z % B;
+  const int m0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
+  for (int j = threadIdx.y; j < 32; j += 8) {
+    const int m = m0 + j, c = c0 + threadIdx.x;
+    float re = 0.f, im = 0.f;
+    if (m < M && c < C && (m + m_off) <= (l + l_off)) {
+      const long long base = ((long long)l * M + m) * RS + (long long)(b * 2) * Cp + c;
+      re = sp[base];
+      im = sp[base + Cp];
+    }
+    tr[j][threadIdx.x] = re;
+    ti[j][threadIdx.x] = im;
+  }
+  __syncthreads();
+  for (int j = threadIdx.y; j < 32; j += 8) {
+    const int c = c0 + j, m = m0 + threadIdx.x;
+    if (c < C && m < M) out[((long long)(b * C + c) * L + l) * M + m] = make_float2(tr[threadIdx.x][j], ti[threadIdx.x][j]);
+  }
+}
+
+__global__ void c64_to_sp_kernel(const float2* __restrict__ in, float* __restrict__ sp, int B, int C, int L, int M) {
+  __shared__ float tr[32][33], ti[32][33];
+  const int Cp = (C + 3) & ~3;
+  const long long RS = 2LL * B * Cp;
+  const int l = blockIdx.z / B, b = blockIdx.z % B;
+  const int m0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
+  for (int j = threadIdx.y; j < 32; j += 8) {
+    const int c = c0 + j, m = m0 + threadIdx.x;
+    float2 v = make_float2(0.f, 0.f);
+    if (c < C && m < M) v = in[((long long)(b * C + c) * L + l) * M + m];
+    tr[j][threadIdx.x] = v.x;
+    ti[j][threadIdx.x] = v.y;
+  }
+  __syncthreads();
+  for (int j = threadIdx.y; j < 32; j += 8) {
+    const int m = m0 + j, c = c0 + threadIdx.x;
+    if (m < M && c < Cp) {      // pad channels are written as zeros so the whole SP tensor is defined
+      const long long base = ((long long)l * M + m) * RS + (long long)(b * 2) * Cp + c;
+      sp[base] = (c < C) ? tr[threadIdx.x][j] : 0.f;
+      sp[base + Cp] = (c < C) ? ti[threadIdx.x][j] : 0.f;
+    }
+  }
+}
+
+// ------------------------------------------------------------------ XM <-> complex64 [B][C][K][M]
+// grid (ceil(M/32), ceil(K/32), B*C), block (32, 8)
+__global__ void xm_to_c64_kernel(const float* __restrict__ xm, float2* __restrict__ out, int B, int C, int K, int Kp,
+                                 int M) {
+  __shared__ float tr[32][33], ti[32][33];
+  const int Cp = (C + 3) & ~3;
+  const long long RS = 2LL * B * Cp;
+  const int b = blockIdx.z / C, c = blockIdx.z % C;
+  const int m0 = blockIdx.x * 32, k0 = blockIdx.y * 32;
+  for (int j = threadIdx.y; j < 32; j += 8) {
+    const int m = m0 + j, k = k0 + threadIdx.x;
+    float re = 0.f, im = 0.f;
+    if (m < M && k < K) {
+      const long long base = ((long long)m * RS + (long long)(b * 2) * Cp + c) * Kp + k;
+      re = xm[base];
+      im = xm[base + (long long)Cp * Kp];
+    }
+    tr[j][threadIdx.x] = re;
+    ti[j][threadIdx.x] = im;
+  }
+  __syncthreads();
+  for (int j = threadIdx.y; j < 32; j += 8) {
+    const int k = k0 + j, m = m0 + threadIdx.x;
+    if (k < K && m < M) out[((long long)(b * C + c) * K + k) * M + m] = make_float2(tr[threadIdx.x][j], ti[threadIdx.x][j]);
+  }
+}
+
+__global__ void c64_to_xm_kernel(const float2* __restrict__ in, float* __restrict__ xm, int B, int C, int K, int Kp,
+                                 int M) {
+  __shared__ float tr[32][33], ti[32][33];
+  const int Cp = (C + 3) & ~3;
+  const long long RS = 2LL * B * Cp;
+  const int b = blockIdx.z / C, c = blockIdx.z % C;
+  const int m0 = blockIdx.x * 32, k0 = blockIdx.y * 32;
+  for (int j = threadIdx.y; j < 32; j += 8) {
+    const int k = k0 + j, m = m0 + threadIdx.x;
+    float2 v = make_float2(0.f, 0.f);
+    if (k < K && m < M) v = in[((long long)(b * C + c) * K + k) * M + m];
+    tr[j][threadIdx.x] = v.x;
+    ti[j][threadIdx.x] = v.y;
+  }
+  __syncthreads();
+  for (int j = threadIdx.y; j < 32; j += 8) {
+    const int m = m0 + j, k = k0 + threadIdx.x;
+    if (m < M && k < Kp) {
+      const long long base = ((long long)m * RS + (long long)(b * 2) * Cp + c) * Kp + k;
+      xm[base] = (k < K) ? tr[threadIdx.x][j] : 0.f;
+      xm[base + (long long)Cp * Kp] = (k < K) ? ti[threadIdx.x][j] : 0.f;
+    }
+  }
+}
+
+// ------------------------------------------------------------------ dhconv weights  w[Cin][Cout][L] c64 <-> WP[L][2][Coutp][Cinp]
+// grid (ceil(L/32), ceil(Cin/32), Cout), block (32, 8)
+__global__ void pack_weight_kernel(const float2* __restrict__ w, float* __restrict__ wp, int Cin, int Cout, int L) {
+  __shared__ float tr[32][33], ti[32][33];
+  const int Cinp = (Cin + 3) & ~3, Coutp = (Cout + 3) & ~3;
+  const int o = blockIdx.z;
+  const int l0 = blockIdx.x * 32, i0 = blockIdx.y * 32;
+  for (int j = threadIdx.y; j < 32; j += 8) {
+    const int i = i0 + j, l = l0 + threadIdx.x;
+    float2 v = make_float2(0.f, 0.f);
+    if (i < Cin && l < L) v = w[((long long)i * Cout + o) * L + l];
+    tr[j][threadIdx.x] = v.x;
+    ti[j][threadIdx.x] = v.y;
+  }
+  __syncthreads();
+  for (int j = threadIdx.y; j < 32; j += 8) {
+    const int l = l0 + j, i = i0 + threadIdx.x;
+    if (l < L && i < Cinp) {
+      const long long base = (((long long)l * 2) * Coutp + o) * Cinp + i;
+      wp[base] = (i < Cin) ? tr[threadIdx.x][j] : 0.f;
+      wp[base + (long long)Coutp * Cinp] = (i < Cin) ? ti[threadIdx.x][j] : 0.f;
+    }
+  }
+}
+
+__global__ void unpack_wgrad_kernel(const float* __restrict__ gwp, float2* __restrict__ gw, int Cin, int Cout, int L) {
+  __shared__ float tr[32][33], ti[32][33];
+  const int Cinp = (Cin + 3) & ~3, Coutp = (Cout + 3) & ~3;
+  const int o = blockIdx.z;
+  const int l0 = blockIdx.x * 32, i0 = blockIdx.y * 32;
+  for (int j = threadIdx.y; j < 32; j += 8) {
+    const int l = l0 + j, i = i0 + threadIdx.x;
+    float re = 0.f, im = 0.f;
+    if (l < L && i < Cin) {
+      const long long base = (((long long)l * 2) * Coutp + o) * Cinp + i;
+      re = gwp[base];
+      im = gwp[base + (long long)Coutp * Cinp];
+    }
+    tr[j][threadIdx.x] = re;
+    ti[j][threadIdx.x] = im;
+  }
+  __syncthreads();
+  for (int j = threadIdx.y; j < 32; j += 8) {
+    const int i = i0 + j, l = l0 + threadIdx.x;
+    if (i < Cin && l < L) gw[((long long)i * Cout + o) * L + l] = make_float2(tr[threadIdx.x][j], ti[threadIdx.x][j]);
+  }
+}
+
+// ------------------------------------------------------------------ bias
+template <typename T>
+__global__ void add_bias_kernel(T* __restrict__ y, const float* __restrict__ bias, int kind, long long n, int C,
+                                long long HW) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const long long c = (i / HW) % C;
+    const float bv = kind == 0 ? bias[c] : bias[c * HW + i % HW];
+    float v;
+    if constexpr (sizeof(T) == 4) {
+      v = (float)y[i] + bv;
+      y[i] = v;
+    } else if constexpr (std::is_same<T, __nv_bfloat16>::value) {
+      y[i] = __float2bfloat16_rn(__bfloat162float(y[i]) + bv);
+    } else {
+      y[i] = __float2half_rn(__half2float(y[i]) + bv);
+    }
+  }
+}
+
+// ------------------------------------------------------------------ diagonal contraction (contractions.py:122-127)
+//   MODE 0: y[b,o,l,m]  = sum_i x[b,i,l,m] w[i,o,l,m]          (a = SP x,  out = SP y)
+//   MODE 1: dx[b,i,l,m] = sum_o g[b,o,l,m] conj(w[i,o,l,m])    (a = SP g,  out = SP dx)
+//   MODE 2: dw[i,o,l,m] = sum_b conj(x[b,i,l,m]) g[b,o,l,m]    (a = SP x, b2 = SP g, out = complex64 dw)
+// One CTA per (l, 32 consecutive m); the SP tiles are staged in shared memory (channel-contiguous reads),
+// the weight is streamed with m across lanes (contiguous).  block (32, 8).
+template <int MODE>
+__global__ void diag_kernel(const float* __restrict__ spa, const void* __restrict__ wb, void* __restrict__ outp,
+                            int B, int Cin, int Cout, int L, int M, int l_off, int m_off) {
+  extern __shared__ float smd[];
+  const int Cinp = (Cin + 3) & ~3, Coutp = (Cout + 3) & ~3;
+  const int RSi = 2 * B * Cinp, RSo = 2 * B * Coutp;
+  const int l = blockIdx.y, m0 = blockIdx.x * 32;
+  const int mloc = threadIdx.x, m = m0 + mloc;
+  const int tid = threadIdx.y * 32 + threadIdx.x;
+  const int RSa = (MODE == 1) ? RSo : RSi;            // channel extent of the staged SP input `spa`
+  const int RSb = (MODE == 1) ? RSi : RSo;            // extent of the second tile (output staging or g)
+  float* ta = smd;                                    // [32][RSa+1]
+  float* tb = smd + 32 * (RSa + 1);                   // [32][RSb+1]
+  const int mhi_l = max(0, min(M, ((l + l_off + 16) & ~15) - m_off));   // defined extent of SP row l
+  // stage input tile(s); entries outside the defined / triangular region are zero
+  for (int idx = tid; idx < 32 * RSa; idx += 256) {
+    const int mm = idx / RSa, r = idx % RSa;
+    float v = 0.f;
+    if (m0 + mm < mhi_l && (m0 + mm + m_off) <= (l + l_off)) v = spa[((long long)l * M + m0 + mm) * RSa + r];
+    ta[mm * (RSa + 1) + r] = v;
+  }
+  if (MODE == 2) {
+    const float* spg = static_cast<const float*>(wb);
+    for (int idx = tid; idx < 32 * RSb; idx += 256) {
+      const int mm = idx / RSb, r = idx % RSb;
+      float v = 0.f;
+      if (m0 + mm < mhi_l && (m0 + mm + m_off) <= (l + l_off)) v = spg[((long long)l * M + m0 + mm) * RSb + r];
+      tb[mm * (RSb + 1) + r] = v;
+    }
+  }
+  __syncthreads();
+  const long long LM = (long long)L * M;
+  if (MODE == 0 || MODE == 1) {
+    const float2* w = static_cast<const float2*>(wb);
+    const int Cred = (MODE == 0) ? Cin : Cout, Cres = (MODE == 0) ? Cout : Cin;
+    const int Credp = (MODE == 0) ? Cinp : Coutp, Cresp = (MODE == 0) ? Coutp : Cinp;
+    for (int b = 0; b < B; ++b) {
+      for (int co = threadIdx.y; co < Cres; co += 8) {
+        float re = 0.f, im = 0.f;
+        if (m < M) {
+          for (int ci = 0; ci < Cred; ++ci) {
+            const int i = (MODE == 0) ? ci : co, o = (MODE == 0) ? co : ci;
+            const float2 wv = w[((long long)i * Cout + o) * LM + (long long)l * M + m];
+            const float xr = ta[mloc * (RSa + 1) + (b * 2) * Credp + ci];
+            const float xi = ta[mloc * (RSa + 1) + (b * 2 + 1) * Credp + ci];
+            if (MODE == 0) {
+              re += xr * wv.x - xi * wv.y;
+              im += xr * wv.y + xi * wv.x;
+            } else {
+              re += xr * wv.x + xi * wv.y;
+              im += xi * wv.x - xr * wv.y;
+            }
+          }
+        }
+        tb[mloc * (RSb + 1) + (b * 2) * Cresp + co] = re;
+        tb[mloc * (RSb + 1) + (b * 2 + 1) * Cresp + co] = im;
+      }
+    }
+    __syncthreads();
+    float* out = static_cast<float*>(outp);
+    for (int idx = tid; idx < 32 * RSb; idx += 256) {
+      const int mm = idx / RSb, r = idx % RSb;
+      const int c = r % Cresp;
+      if (m0 + mm < mhi_l) out[((long long)l * M + m0 + mm) * RSb + r] = (c < Cres) ? tb[mm * (RSb + 1) + r] : 0.f;
+    }
+  } else {
+    float2* gw = static_cast<float2*>(outp);
+    for (int idx = threadIdx.y; idx < Cin * Cout; idx += 8) {
+      const int i = idx / Cout, o = idx % Cout;
+      float re = 0.f, im = 0.f;
+      for (int b = 0; b < B; ++b) {
+        const float xr = ta[mloc * (RSa + 1) + (b * 2) * Cinp + i], xi = ta[mloc * (RSa + 1) + (b * 2 + 1) * Cinp + i];
+        const float gr = tb[mloc * (RSb + 1) + (b * 2) * Coutp + o], gi = tb[mloc * (RSb + 1) + (b * 2 + 1) * Coutp + o];
+        re += xr * gr + xi * gi;
+        im += xr * gi - xi * gr;
+      }
+      if (m < M) gw[((long long)i * Cout + o) * LM + (long long)l * M + m] = make_float2(re, im);
+    }
+  }
+}
+
+}  // namespace sfno
+
+// ====================================================================== C ABI
+using namespace sfno;
+
+extern "C" {
+
+int sfno_sp_to_c64(const float* sp, int B, int C, int lmax, int mmax, int l_offset, int m_offset, void* out_c64,
+                   void* stream) {
+  dim3 grid((mmax + 31) / 32, (C + 31) / 32, lmax * B), block(32, 8);
+  sp_to_c64_kernel<<<grid, block, 0, (cudaStream_t)stream>>>(sp, (float2*)out_c64, B, C, lmax, mmax, l_offset, m_offset);
+  SFNO_LAUNCHED();
+  return 0;
+}
+int sfno_c64_to_sp(const void* in_c64, int B, int C, int lmax, int mmax, float* sp, void* stream) {
+  const int Cp = (C + 3) & ~3;
+  dim3 grid((mmax + 31) / 32, (Cp + 31) / 32, lmax * B), block(32, 8);
+  c64_to_sp_kernel<<<grid, block, 0, (cudaStream_t)stream>>>((const float2*)in_c64, sp, B, C, lmax, mmax);
+  SFNO_LAUNCHED();
+  return 0;
+}
+int sfno_xm_to_c64(const float* xm, int B, int C, int nlat, int mmax, void* out_c64, void* stream) {
+  const int Kp = round_up(nlat, 4);
+  dim3 grid((mmax + 31) / 32, (nlat + 31) / 32, B * C), block(32, 8);
+  xm_to_c64_kernel<<<grid, block, 0, (cudaStream_t)stream>>>(xm, (float2*)out_c64, B, C, nlat, Kp, mmax);
+  SFNO_LAUNCHED();
+  return 0;
+}
+int sfno_c64_to_xm(const void* in_c64, int B, int C, int nlat, int mmax, float* xm, void* stream) {
+  const int Kp = round_up(nlat, 4);
+  dim3 grid((mmax + 31) / 32, (Kp + 31) / 32, B * C), block(32, 8);
+  c64_to_xm_kernel<<<grid, block, 0, (cudaStream_t)stream>>>((const float2*)in_c64, xm, B, C, nlat, Kp, mmax);
+  SFNO_LAUNCHED();
+  return 0;
+}
+int sfno_dhconv_pack_weight(const void* w_c64, int Cin, int Cout, int L, float* wp, void* stream) {
+  const int Cinp = (Cin + 3) & ~3;
+  dim3 grid((L + 31) / 32, (Cinp + 31) / 32, Cout), block(32, 8);
+  pack_weight_kernel<<<grid, block, 0, (cudaStream_t)stream>>>((const float2*)w_c64, wp, Cin, Cout, L);
+  SFNO_LAUNCHED();
+  return 0;
+}
+int sfno_dhconv_unpack_wgrad(const float* gwp, int Cin, int Cout, int L, void* gw_c64, void* stream) {
+  dim3 grid((L + 31) / 32, (Cin + 31) / 32, Cout), block(32, 8);
+  unpack_wgrad_kernel<<<grid, block, 0, (cudaStream_t)stream>>>(gwp, (float2*)gw_c64, Cin, Cout, L);
+  SFNO_LAUNCHED();
+  return 0;
+}
+int sfno_add_bias(void* y, int y_dtype, const float* bias, int bias_kind, int B, int C, int H, int W, void* stream) {
+  const long long HW = (long long)H * W, n = (long long)B * C * HW;
+  const int grid = (int)std::min<long long>((n + 255) / 256, 148 * 16);
+  cudaStream_t s = (cudaStream_t)stream;
+  switch (y_dtype) {
+    case SFNO_F32: add_bias_kernel<float><<<grid, 256, 0, s>>>((float*)y, bias, bias_kind, n, C, HW); break;
+    case SFNO_BF16: add_bias_kernel<__nv_bfloat16><<<grid, 256, 0, s>>>((__nv_bfloat16*)y, bias, bias_kind, n, C, HW); break;
+    case SFNO_F16: add_bias_kernel<__half><<<grid, 256, 0, s>>>((__half*)y, bias, bias_kind, n, C, HW); break;
+    default: SFNO_CHECK(false, "unsupported dtype");
+  }
+  SFNO_LAUNCHED();
+  return 0;
+}
+
+int sfno_diag_contract(int mode, const float* sp_a, const void* w_or_spb, void* out, int B, int Cin, int Cout,
+                       int lmax, int mmax, int l_offset, int m_offset, void* stream) {
+  const int Cinp = (Cin + 3) & ~3, Coutp = (Cout + 3) & ~3;
+  const size_t smem = (size_t)32 * (2 * B * Cinp + 2 * B * Coutp + 2) * 4;
+  SFNO_CHECK(smem <= 200 * 1024, "diagonal contraction: B*(Cin+Cout) too large for the shared-memory tile");
+  dim3 grid((mmax + 31) / 32, lmax), block(32, 8);
+  cudaStream_t s = (cudaStream_t)stream;
+#define SFNO_DIAG(MODE)                                                                                     \
+  SFNO_CUDA(cudaFuncSetAttribute(diag_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024)); \
+  diag_kernel<MODE><<<grid, block, smem, s>>>(sp_a, w_or_spb, out, B, Cin, Cout, lmax, mmax, l_offset, m_offset)
+  if (mode == 0) { SFNO_DIAG(0); }
+  else if (mode == 1) { SFNO_DIAG(1); }
+  else if (mode == 2) { SFNO_DIAG(2); }
+  else SFNO_CHECK(false, "bad mode");
+#undef SFNO_DIAG
+  SFNO_LAUNCHED();
+  return 0;
+}
+
+}  // extern "C"

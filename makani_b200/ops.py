@@ -1,0 +1,254 @@
+"""Thin torch-tensor wrappers over the C ABI (one function per kernel family).
+
+Device memory, streams and dtypes come from torch; the arithmetic is all in libmakani_b200.so.
+Every wrapper allocates its output with ``torch.empty`` on the input's device and enqueues on
+``torch.cuda.current_stream()`` - no host synchronisation, so calls are CUDA-graph capturable
+after one warm-up call per shape (tile schedules / twiddle tables are built on first use).
+
+Internal tensors (see include/makani_b200.h):
+    XM  flat fp32  [mmax][RS][Kp]      SP  flat fp32  [lmax][mmax][RS]      WP  flat fp32 [lmax][2][Coutp][Cinp]
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+
+import numpy as np
+import torch
+
+from . import _ext
+
+_DTYPES = {torch.float32: _ext.F32, torch.bfloat16: _ext.BF16, torch.float16: _ext.F16}
+
+
+def _rup(x, m):
+    return (x + m - 1) // m * m
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _ptr(t: torch.Tensor):
+    return C.c_void_p(t.data_ptr())
+
+
+def _need_cuda(t: torch.Tensor, name: str):
+    if not t.is_cuda:
+        raise RuntimeError(f"makani_b200: {name} must be a CUDA tensor (got {t.device}); this package has no CPU path")
+
+
+def dtype_code(dt: torch.dtype) -> int:
+    try:
+        return _DTYPES[dt]
+    except KeyError:
+        raise TypeError(f"makani_b200: unsupported dtype {dt}; supported: float32, bfloat16, float16") from None
+
+
+class Plan:
+    """Owns one device Legendre table [mmax][lmax][nlat] (``sfno_plan_create``)."""
+
+    def __init__(self, nlat, nlon, lmax, mmax, table64: np.ndarray, m_offset: int = 0, device=None):
+        lib = _ext.load()
+        table64 = np.ascontiguousarray(table64, dtype=np.float64)
+        assert table64.shape == (mmax, lmax, nlat), (table64.shape, (mmax, lmax, nlat))
+        self.nlat, self.nlon, self.lmax, self.mmax, self.m_offset = nlat, nlon, lmax, mmax, m_offset
+        self.device = torch.device(device if device is not None else torch.cuda.current_device())
+        self._h = C.c_void_p()
+        with torch.cuda.device(self.device):
+            _ext.check(lib.sfno_plan_create(nlat, nlon, lmax, mmax, m_offset,
+                                            table64.ctypes.data_as(C.c_void_p), C.byref(self._h)), "sfno_plan_create")
+
+    @property
+    def handle(self):
+        return self._h
+
+    def __del__(self):
+        h = getattr(self, "_h", None)
+        if h is not None and h.value:
+            try:
+                _ext.load().sfno_plan_destroy(h)
+            except Exception:
+                pass
+            self._h = C.c_void_p()
+
+
+def xm_elems(nlat, mmax, B, Cn):
+    return mmax * 2 * B * _rup(Cn, 4) * _rup(nlat, 4)
+
+
+def sp_elems(lmax, mmax, B, Cn):
+    return lmax * mmax * 2 * B * _rup(Cn, 4)
+
+
+def wp_elems(lmax, Cin, Cout):
+    return lmax * 2 * _rup(Cout, 4) * _rup(Cin, 4)
+
+
+# ------------------------------------------------------------------------------------------ DFT
+def fwd_scale(nlon: int, mmax: int) -> torch.Tensor:
+    """RealSHT: X = 2*pi * rfft(x, norm="forward")  ->  2*pi/nlon on every bin."""
+    return torch.full((mmax,), 2.0 * math.pi / nlon, dtype=torch.float32)
+
+
+def irfft_adjoint_scale(nlon: int, mmax: int) -> torch.Tensor:
+    """Adjoint of irfft(n=nlon, norm="forward"): bins are doubled except m = 0 and Nyquist."""
+    s = torch.full((mmax,), 2.0, dtype=torch.float32)
+    s[0] = 1.0
+    if nlon % 2 == 0 and mmax > nlon // 2:
+        s[nlon // 2] = 1.0
+    return s
+
+
+def rfft_adjoint_scale(nlon: int, mmax: int) -> torch.Tensor:
+    """Adjoint of 2*pi*rfft(norm="forward") expressed through the irfft kernel (which doubles bins 0<m<Nyq)."""
+    s = torch.full((mmax,), 0.5, dtype=torch.float32)
+    s[0] = 1.0
+    if nlon % 2 == 0 and mmax > nlon // 2:
+        s[nlon // 2] = 1.0
+    return s * (2.0 * math.pi / nlon)
+
+
+def dft_fwd(x: torch.Tensor, mmax: int, mscale: torch.Tensor) -> torch.Tensor:
+    """x [B, C, nlat, nlon] (f32/bf16/f16, contiguous) -> XM."""
+    _need_cuda(x, "x")
+    B, Cn, K, W = x.shape
+    x = x.contiguous()
+    xm = torch.empty(xm_elems(K, mmax, B, Cn), dtype=torch.float32, device=x.device)
+    _ext.check(_ext.load().sfno_dft_fwd(_ptr(x), dtype_code(x.dtype), B, Cn, K, W, mmax, _ptr(mscale), _ptr(xm),
+                                        _stream()), "sfno_dft_fwd")
+    return xm
+
+
+def dft_inv(xm: torch.Tensor, B: int, Cn: int, nlat: int, nlon: int, mmax: int, mscale: torch.Tensor,
+            dtype: torch.dtype, m_valid=None) -> torch.Tensor:
+    _need_cuda(xm, "xm")
+    y = torch.empty((B, Cn, nlat, nlon), dtype=dtype, device=xm.device)
+    _ext.check(_ext.load().sfno_dft_inv(_ptr(xm), B, Cn, nlat, nlon, mmax, mmax if m_valid is None else m_valid,
+                                        _ptr(mscale), _ptr(y), dtype_code(dtype), _stream()), "sfno_dft_inv")
+    return y
+
+
+# ------------------------------------------------------------------------------------------ Legendre
+def legendre_analysis(plan: Plan, xm: torch.Tensor, B: int, Cn: int) -> torch.Tensor:
+    sp = torch.empty(sp_elems(plan.lmax, plan.mmax, B, Cn), dtype=torch.float32, device=xm.device)
+    _ext.check(_ext.load().sfno_legendre_analysis(plan.handle, _ptr(xm), B, Cn, _ptr(sp), _stream()),
+               "sfno_legendre_analysis")
+    return sp
+
+
+def legendre_synthesis(plan: Plan, sp: torch.Tensor, B: int, Cn: int) -> torch.Tensor:
+    xm = torch.empty(xm_elems(plan.nlat, plan.mmax, B, Cn), dtype=torch.float32, device=sp.device)
+    _ext.check(_ext.load().sfno_legendre_synthesis(plan.handle, _ptr(sp), B, Cn, _ptr(xm), _stream()),
+               "sfno_legendre_synthesis")
+    return xm
+
+
+# ------------------------------------------------------------------------------------------ layout
+def sp_to_c64(sp, B, Cn, lmax, mmax, l_offset=0, m_offset=0) -> torch.Tensor:
+    out = torch.empty((B, Cn, lmax, mmax), dtype=torch.complex64, device=sp.device)
+    _ext.check(_ext.load().sfno_sp_to_c64(_ptr(sp), B, Cn, lmax, mmax, l_offset, m_offset, _ptr(out), _stream()),
+               "sfno_sp_to_c64")
+    return out
+
+
+def c64_to_sp(c: torch.Tensor) -> torch.Tensor:
+    _need_cuda(c, "coefficients")
+    B, Cn, L, M = c.shape
+    c = c.contiguous()
+    if c.dtype != torch.complex64:
+        raise TypeError(f"makani_b200: spectral coefficients must be complex64, got {c.dtype}")
+    sp = torch.empty(sp_elems(L, M, B, Cn), dtype=torch.float32, device=c.device)
+    _ext.check(_ext.load().sfno_c64_to_sp(_ptr(c), B, Cn, L, M, _ptr(sp), _stream()), "sfno_c64_to_sp")
+    return sp
+
+
+def xm_to_c64(xm, B, Cn, nlat, mmax) -> torch.Tensor:
+    out = torch.empty((B, Cn, nlat, mmax), dtype=torch.complex64, device=xm.device)
+    _ext.check(_ext.load().sfno_xm_to_c64(_ptr(xm), B, Cn, nlat, mmax, _ptr(out), _stream()), "sfno_xm_to_c64")
+    return out
+
+
+def c64_to_xm(c: torch.Tensor) -> torch.Tensor:
+    _need_cuda(c, "coefficients")
+    B, Cn, K, M = c.shape
+    c = c.contiguous()
+    if c.dtype != torch.complex64:
+        raise TypeError(f"makani_b200: Fourier coefficients must be complex64, got {c.dtype}")
+    xm = torch.empty(xm_elems(K, M, B, Cn), dtype=torch.float32, device=c.device)
+    _ext.check(_ext.load().sfno_c64_to_xm(_ptr(c), B, Cn, K, M, _ptr(xm), _stream()), "sfno_c64_to_xm")
+    return xm
+
+
+def add_bias_(y: torch.Tensor, bias: torch.Tensor) -> torch.Tensor:
+    """In-place y[b,c,h,w] += bias, bias [1,C,1,1] or [1,C,H,W] (fp32)."""
+    B, Cn, H, W = y.shape
+    kind = 0 if bias.numel() == Cn else 1
+    bias = bias.detach().to(torch.float32).contiguous()
+    _ext.check(_ext.load().sfno_add_bias(_ptr(y), dtype_code(y.dtype), _ptr(bias), kind, B, Cn, H, W, _stream()),
+               "sfno_add_bias")
+    return y
+
+
+# ------------------------------------------------------------------------------------------ dhconv
+def pack_weight(w: torch.Tensor) -> torch.Tensor:
+    """complex64 [Cin, Cout, L] -> WP."""
+    _need_cuda(w, "weight")
+    Cin, Cout, L = w.shape
+    w = w.detach().contiguous()
+    wp = torch.empty(wp_elems(L, Cin, Cout), dtype=torch.float32, device=w.device)
+    _ext.check(_ext.load().sfno_dhconv_pack_weight(_ptr(w), Cin, Cout, L, _ptr(wp), _stream()),
+               "sfno_dhconv_pack_weight")
+    return wp
+
+
+def unpack_wgrad(gwp: torch.Tensor, Cin, Cout, L) -> torch.Tensor:
+    gw = torch.empty((Cin, Cout, L), dtype=torch.complex64, device=gwp.device)
+    _ext.check(_ext.load().sfno_dhconv_unpack_wgrad(_ptr(gwp), Cin, Cout, L, _ptr(gw), _stream()),
+               "sfno_dhconv_unpack_wgrad")
+    return gw
+
+
+def dhconv_fwd(sp_in, wp, B, Cin, Cout, lmax, mmax, l_offset=0, m_offset=0) -> torch.Tensor:
+    sp_out = torch.empty(sp_elems(lmax, mmax, B, Cout), dtype=torch.float32, device=sp_in.device)
+    _ext.check(_ext.load().sfno_dhconv_fwd(_ptr(sp_in), _ptr(wp), _ptr(sp_out), B, Cin, Cout, lmax, mmax,
+                                           l_offset, m_offset, _stream()), "sfno_dhconv_fwd")
+    return sp_out
+
+
+def dhconv_bwd_x(gsp_out, wp, B, Cin, Cout, lmax, mmax, l_offset=0, m_offset=0) -> torch.Tensor:
+    gsp_in = torch.empty(sp_elems(lmax, mmax, B, Cin), dtype=torch.float32, device=gsp_out.device)
+    _ext.check(_ext.load().sfno_dhconv_bwd_x(_ptr(gsp_out), _ptr(wp), _ptr(gsp_in), B, Cin, Cout, lmax, mmax,
+                                             l_offset, m_offset, _stream()), "sfno_dhconv_bwd_x")
+    return gsp_in
+
+
+def dhconv_bwd_w(sp_in, gsp_out, B, Cin, Cout, lmax, mmax, l_offset=0, m_offset=0) -> torch.Tensor:
+    gwp = torch.empty(wp_elems(lmax, Cin, Cout), dtype=torch.float32, device=sp_in.device)
+    _ext.check(_ext.load().sfno_dhconv_bwd_w(_ptr(sp_in), _ptr(gsp_out), _ptr(gwp), B, Cin, Cout, lmax, mmax,
+                                             l_offset, m_offset, _stream()), "sfno_dhconv_bwd_w")
+    return gwp
+
+
+# ------------------------------------------------------------------------------------------ diagonal
+def diag_fwd(sp_in, w, B, Cin, Cout, lmax, mmax, l_offset=0, m_offset=0) -> torch.Tensor:
+    w = w.detach().contiguous()
+    sp_out = torch.empty(sp_elems(lmax, mmax, B, Cout), dtype=torch.float32, device=sp_in.device)
+    _ext.check(_ext.load().sfno_diag_contract(0, _ptr(sp_in), _ptr(w), _ptr(sp_out), B, Cin, Cout, lmax, mmax,
+                                              l_offset, m_offset, _stream()), "sfno_diag_contract(fwd)")
+    return sp_out
+
+
+def diag_bwd_x(gsp_out, w, B, Cin, Cout, lmax, mmax, l_offset=0, m_offset=0) -> torch.Tensor:
+    w = w.detach().contiguous()
+    gsp_in = torch.empty(sp_elems(lmax, mmax, B, Cin), dtype=torch.float32, device=gsp_out.device)
+    _ext.check(_ext.load().sfno_diag_contract(1, _ptr(gsp_out), _ptr(w), _ptr(gsp_in), B, Cin, Cout, lmax, mmax,
+                                              l_offset, m_offset, _stream()), "sfno_diag_contract(bwd_x)")
+    return gsp_in
+
+
+def diag_bwd_w(sp_in, gsp_out, B, Cin, Cout, lmax, mmax, l_offset=0, m_offset=0) -> torch.Tensor:
+    gw = torch.empty((Cin, Cout, lmax, mmax), dtype=torch.complex64, device=sp_in.device)
+    _ext.check(_ext.load().sfno_diag_contract(2, _ptr(sp_in), _ptr(gsp_out), _ptr(gw), B, Cin, Cout, lmax, mmax,
+                                              l_offset, m_offset, _stream()), "sfno_diag_contract(bwd_w)")
+    return gw

@@ -1,0 +1,238 @@
+"""SpectralConv: drop-in for ``makani.models.common.spectral_convolution.SpectralConv``
+(makani/models/common/spectral_convolution.py:43-148), with the alias ``SpectralConvS2``.
+
+Same constructor signature, same parameter (``weight`` complex64 ``[Cin, Cout, L]`` for dhconv /
+``[Cin, Cout, L, M]`` for diagonal, with the ``is_shared_mp`` / ``sharded_dims_mp`` annotations the
+reference's checkpointing reads), optional ``bias``, same ``forward(x) -> (y, residual)``.
+
+Unlike the reference, the whole chain  DFT -> Legendre -> channel contraction -> Legendre -> inverse DFT  runs
+on spectral-internal device layouts without materialising a complex64 ``[B,C,L,M]`` tensor between the
+stages, and its backward is a single hand-written adjoint chain (one autograd node).
+"""
+from __future__ import annotations
+
+import math
+
+import torch
+import torch.nn as nn
+
+from . import ops
+from .sht import InverseRealSHT, RealSHT, _TransformBase
+
+__all__ = ["SpectralConv", "SpectralConvS2"]
+
+
+def _distributed_classes():
+    from .distributed import DistributedInverseRealSHT, DistributedRealSHT
+    return DistributedRealSHT, DistributedInverseRealSHT
+
+
+class _SpectralConvFunction(torch.autograd.Function):
+    """(x, weight) -> (y, residual_or_None); single-device transforms only."""
+
+    @staticmethod
+    def forward(ctx, x, weight, mod):
+        fwd, inv = mod.forward_transform, mod.inverse_transform
+        dev = x.device
+        B, Cin = x.shape[0], x.shape[1]
+        Cout, L, M = mod.out_channels, mod.modes_lat, mod.modes_lon
+        pf, pi = fwd._plan(dev), inv._plan(dev)
+
+        xm = ops.dft_fwd(x, M, fwd._scale(dev, "fwd"))
+        sp = ops.legendre_analysis(pf, xm, B, Cin)
+        del xm
+        residual = None
+        if mod.scale_residual:
+            rxm = ops.legendre_synthesis(pi, sp, B, Cin)
+            residual = ops.dft_inv(rxm, B, Cin, inv.nlat, inv.nlon, M, inv._scale(dev, "one"), x.dtype)
+            del rxm
+        if mod.operator_type == "dhconv":
+            wp = mod._packed_weight(weight)
+            sp2 = ops.dhconv_fwd(sp, wp, B, Cin, Cout, L, M)
+        else:
+            wp = None
+            sp2 = ops.diag_fwd(sp, weight, B, Cin, Cout, L, M)
+        xm2 = ops.legendre_synthesis(pi, sp2, B, Cout)
+        del sp2
+        y = ops.dft_inv(xm2, B, Cout, inv.nlat, inv.nlon, M, inv._scale(dev, "one"), x.dtype)
+
+        ctx.mod = mod
+        ctx.in_dtype = x.dtype
+        ctx.shape = (B, Cin, Cout, L, M)
+        ctx.has_residual = residual is not None
+        if wp is not None:
+            ctx.save_for_backward(sp, wp)
+        else:
+            ctx.save_for_backward(sp, weight)
+        if residual is None:
+            return y, None
+        return y, residual
+
+    @staticmethod
+    def backward(ctx, gy, gres):
+        mod = ctx.mod
+        fwd, inv = mod.forward_transform, mod.inverse_transform
+        B, Cin, Cout, L, M = ctx.shape
+        sp, wsaved = ctx.saved_tensors
+        dev = gy.device
+        pf, pi = fwd._plan(dev), inv._plan(dev)
+        adj = inv._scale(dev, "irfft_adj")
+
+        gxm2 = ops.dft_fwd(gy.contiguous(), M, adj)
+        gsp2 = ops.legendre_analysis(pi, gxm2, B, Cout)
+        del gxm2
+        gw = None
+        if mod.operator_type == "dhconv":
+            if ctx.needs_input_grad[1]:
+                gw = ops.unpack_wgrad(ops.dhconv_bwd_w(sp, gsp2, B, Cin, Cout, L, M), Cin, Cout, L)
+            gsp = ops.dhconv_bwd_x(gsp2, wsaved, B, Cin, Cout, L, M) if ctx.needs_input_grad[0] else None
+        else:
+            if ctx.needs_input_grad[1]:
+                gw = ops.diag_bwd_w(sp, gsp2, B, Cin, Cout, L, M)
+            gsp = ops.diag_bwd_x(gsp2, wsaved, B, Cin, Cout, L, M) if ctx.needs_input_grad[0] else None
+        del gsp2
+        gx = None
+        if ctx.needs_input_grad[0]:
+            if ctx.has_residual and gres is not None:
+                grxm = ops.dft_fwd(gres.contiguous(), M, adj)
+                gsp = gsp + ops.legendre_analysis(pi, grxm, B, Cin)     # both zero outside the defined region
+                del grxm
+            gxm = ops.legendre_synthesis(pf, gsp, B, Cin)
+            gx = ops.dft_inv(gxm, B, Cin, fwd.nlat, fwd.nlon, M, fwd._scale(dev, "rfft_adj"), ctx.in_dtype)
+        return gx, gw, None
+
+
+class SpectralConv(nn.Module):
+    """
+    Spectral convolution on the two-sphere: SHT -> per-mode channel contraction -> inverse SHT.
+    Mirrors the reference module (spectral_convolution.py:43-148).
+    """
+
+    def __init__(self, forward_transform, inverse_transform, in_channels, out_channels, operator_type="diagonal",
+                 separable=False, bias=False, gain=1.0):
+        super().__init__()
+
+        self.forward_transform = forward_transform
+        self.inverse_transform = inverse_transform
+
+        self.in_channels = in_channels
+        self.out_channels = out_channels
+
+        self.modes_lat = self.inverse_transform.lmax
+        self.modes_lon = self.inverse_transform.mmax
+
+        self.scale_residual = (self.forward_transform.nlat != self.inverse_transform.nlat) or (
+            self.forward_transform.nlon != self.inverse_transform.nlon)
+        if hasattr(self.forward_transform, "grid"):
+            self.scale_residual = self.scale_residual or (self.forward_transform.grid != self.inverse_transform.grid)
+
+        self.operator_type = operator_type
+        self.separable = separable
+
+        assert self.inverse_transform.lmax == self.modes_lat
+        assert self.inverse_transform.mmax == self.modes_lon
+
+        weight_shape = [in_channels]
+        if not self.separable:
+            weight_shape += [out_channels]
+
+        DistSHT, DistISHT = _distributed_classes()
+        self._distributed = isinstance(self.inverse_transform, DistISHT)
+        if self._distributed:
+            it = self.inverse_transform
+            self.modes_lat_local = it.l_shapes[it.comm_rank_polar]
+            self.modes_lon_local = it.m_shapes[it.comm_rank_azimuth]
+            self.nlat_local = it.lat_shapes[it.comm_rank_polar]
+            self.nlon_local = it.lon_shapes[it.comm_rank_azimuth]
+            self._l_offset = sum(it.l_shapes[: it.comm_rank_polar])
+            self._m_offset = sum(it.m_shapes[: it.comm_rank_azimuth])
+        else:
+            self.modes_lat_local = self.modes_lat
+            self.modes_lon_local = self.modes_lon
+            self.nlat_local = self.inverse_transform.nlat
+            self.nlon_local = self.inverse_transform.nlon
+            self._l_offset = 0
+            self._m_offset = 0
+
+        if self.operator_type == "diagonal":
+            weight_shape += [self.modes_lat_local, self.modes_lon_local]
+        elif self.operator_type == "dhconv":
+            weight_shape += [self.modes_lat_local]
+        else:
+            raise ValueError(f"Unsupported operator type f{self.operator_type}")
+
+        if self.separable:
+            # the reference's separable contractions ("bixy,ix->boxy", contractions.py:139-154) name an output
+            # index that no operand carries; torch.einsum rejects them, so there is no behaviour to reproduce.
+            raise NotImplementedError("separable SpectralConv is not supported (the reference einsum is ill-formed)")
+
+        # initialisation of spectral_convolution.py:97-102
+        scale = math.sqrt(gain / in_channels) * torch.ones(self.modes_lat_local, dtype=torch.complex64)
+        scale[0] *= math.sqrt(2.0)
+        if self.operator_type == "diagonal":
+            scale = scale.reshape(-1, 1)
+        init = scale * torch.randn(*weight_shape, dtype=torch.complex64)
+        self.weight = nn.Parameter(init)
+
+        if self.operator_type == "dhconv":
+            self.weight.is_shared_mp = ["matmul", "w"]
+            self.weight.sharded_dims_mp = [None for _ in weight_shape]
+            self.weight.sharded_dims_mp[-1] = "h"
+        else:
+            self.weight.is_shared_mp = ["matmul"]
+            self.weight.sharded_dims_mp = [None for _ in weight_shape]
+            self.weight.sharded_dims_mp[-1] = "w"
+            self.weight.sharded_dims_mp[-2] = "h"
+
+        if bias == "constant":
+            self.bias = nn.Parameter(torch.zeros(1, self.out_channels, 1, 1))
+        elif bias == "position":
+            self.bias = nn.Parameter(torch.zeros(1, self.out_channels, self.nlat_local, self.nlon_local))
+            self.bias.is_shared_mp = ["matmul"]
+            self.bias.sharded_dims_mp = [None, None, "h", "w"]
+
+        self._wp_cache = None     # (weight version, data_ptr, packed tensor)
+
+    # packed planar copy of the dhconv weight, refreshed when the parameter changes (optimizer step / load)
+    def _packed_weight(self, weight: torch.Tensor) -> torch.Tensor:
+        key = (weight._version, weight.data_ptr(), weight.device)
+        cache = self._wp_cache
+        if cache is not None and cache[0] == key and not torch.cuda.is_current_stream_capturing():
+            return cache[1]
+        wp = ops.pack_weight(weight)
+        self._wp_cache = (key, wp)
+        return wp
+
+    def _fused_ok(self):
+        return (isinstance(self.forward_transform, _TransformBase) and isinstance(self.inverse_transform, _TransformBase)
+                and type(self.forward_transform) is RealSHT and type(self.inverse_transform) is InverseRealSHT
+                and self.forward_transform.lmax == self.modes_lat and self.forward_transform.mmax == self.modes_lon)
+
+    def forward(self, x):
+        dtype = x.dtype
+        ops._need_cuda(x, "SpectralConv input")
+        ops.dtype_code(dtype)
+        if self._fused_ok():
+            y, residual = _SpectralConvFunction.apply(x.contiguous(), self.weight, self)
+            if residual is None:
+                residual = x
+        else:
+            y, residual = self._forward_composed(x)
+        if hasattr(self, "bias"):
+            y = y + self.bias.to(y.dtype)
+        return y, residual
+
+    # distributed (or foreign) transforms: same arithmetic, stage by stage through the module API
+    def _forward_composed(self, x):
+        dtype = x.dtype
+        residual = x
+        xs = self.forward_transform(x.float()).contiguous()
+        if self.scale_residual:
+            residual = self.inverse_transform(xs).to(dtype)
+        from .contraction import contract_complex
+        xs = contract_complex(xs, self.weight, self.operator_type, self._l_offset, self._m_offset)
+        y = self.inverse_transform(xs).to(dtype)
+        return y, residual
+
+
+SpectralConvS2 = SpectralConv

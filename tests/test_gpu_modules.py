@@ -1,0 +1,187 @@
+"""GPU parity tests of the drop-in modules (RealSHT, InverseRealSHT, SpectralConv) against the CPU oracle
+(oracle/sht_oracle.py, fp64) on the same seeded inputs, forward and backward, plus size-independent
+properties at the full BASELINE.json sizes (240x480 / 721x1440, C = 384).
+
+Metric: the reference's own (tests/distributed/tests_fft.py:231): mean over leading dims of
+||a-b||_2 / ||b||_2 over the last two dims.  Stated tolerances vs the fp64 oracle:
+   transforms (one TF32 contraction)            1e-3
+   SpectralConv block (three TF32 contractions) 2e-3      gradients: same
+   bf16 in/out                                  2e-2      (bf16 rounding of the output dominates)
+"""
+import pytest
+import torch
+
+from oracle import sht_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+TOL_T = 1e-3
+TOL_BLOCK = 2e-3
+
+
+@pytest.fixture(scope="module")
+def mk(built_lib):
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    import makani_b200
+    return makani_b200
+
+
+DEV = "cuda:0"
+
+GRIDS = [
+    (32, 64, None, None, "legendre-gauss"),
+    (33, 64, None, None, "equiangular"),        # odd nlat (latitude padding), poles included
+    (17, 40, None, None, "lobatto"),
+    (24, 48, 16, 12, "legendre-gauss"),         # truncated lmax / mmax
+    (60, 480, 60, 61, "legendre-gauss"),        # fft480 path, R = 1
+    (45, 1440, 40, 41, "equiangular"),          # fft480 path, R = 3
+]
+
+
+@pytest.mark.parametrize("nlat,nlon,lmax,mmax,grid", GRIDS)
+def test_real_sht_forward_backward(mk, nlat, nlon, lmax, mmax, grid):
+    torch.manual_seed(0)
+    sht = mk.RealSHT(nlat, nlon, lmax=lmax, mmax=mmax, grid=grid).to(DEV)
+    ref = O.RealSHT(nlat, nlon, lmax=lmax, mmax=mmax, grid=grid)
+    x = torch.randn(2, 3, nlat, nlon, device=DEV, requires_grad=True)
+    c = sht(x)
+    assert c.shape == (2, 3, sht.lmax, sht.mmax) and c.dtype == torch.complex64
+    xr = x.detach().double().cpu().requires_grad_(True)
+    cr = ref(xr)
+    assert O.rel_l2(c.detach().cpu(), cr.detach()) < TOL_T
+    g = torch.randn_like(cr)
+    (c * g.to(DEV).to(torch.complex64).conj()).real.sum().backward()
+    (cr * g.conj()).real.sum().backward()
+    assert O.rel_l2(x.grad.cpu(), xr.grad) < TOL_T
+
+
+@pytest.mark.parametrize("nlat,nlon,lmax,mmax,grid", GRIDS)
+def test_inverse_sht_forward_backward(mk, nlat, nlon, lmax, mmax, grid):
+    torch.manual_seed(1)
+    isht = mk.InverseRealSHT(nlat, nlon, lmax=lmax, mmax=mmax, grid=grid).to(DEV)
+    ref = O.InverseRealSHT(nlat, nlon, lmax=lmax, mmax=mmax, grid=grid)
+    L, M = isht.lmax, isht.mmax
+    c0 = torch.randn(2, 3, L, M, dtype=torch.complex128) * torch.tril(torch.ones(L, M))
+    c = c0.to(torch.complex64).to(DEV).requires_grad_(True)
+    cr = c0.clone().requires_grad_(True)
+    y, yr = isht(c), ref(cr)
+    assert y.shape == (2, 3, nlat, nlon) and y.dtype == torch.float32
+    assert O.rel_l2(y.detach().cpu(), yr.detach()) < TOL_T
+    g = torch.randn_like(yr)
+    (y * g.float().to(DEV)).sum().backward()
+    (yr * g).sum().backward()
+    mask = torch.tril(torch.ones(L, M))
+    assert O.rel_l2(c.grad.cpu(), cr.grad * mask) < TOL_T
+
+
+def _block(mk, nlat_in, nlon_in, grid_in, nlat_out, nlon_out, grid_out, L, M, Cin, Cout, op, B, dtype, bias=False):
+    torch.manual_seed(2)
+    fwd = mk.RealSHT(nlat_in, nlon_in, lmax=L, mmax=M, grid=grid_in).to(DEV)
+    inv = mk.InverseRealSHT(nlat_out, nlon_out, lmax=L, mmax=M, grid=grid_out).to(DEV)
+    conv = mk.SpectralConv(fwd, inv, Cin, Cout, operator_type=op, bias=bias).to(DEV)
+    if bias:
+        with torch.no_grad():
+            conv.bias.normal_()
+    ofwd = O.RealSHT(nlat_in, nlon_in, lmax=L, mmax=M, grid=grid_in)
+    oinv = O.InverseRealSHT(nlat_out, nlon_out, lmax=L, mmax=M, grid=grid_out)
+    x = torch.randn(B, Cin, nlat_in, nlon_in, device=DEV).to(dtype).requires_grad_(True)
+    y, res = conv(x)
+    xr = x.detach().double().cpu().requires_grad_(True)
+    wr = conv.weight.detach().cpu().to(torch.complex128).requires_grad_(True)
+    br = conv.bias.detach().double().cpu() if bias else None
+    yr, resr = O.spectral_conv_forward(xr, ofwd, oinv, wr, op, bias=br, compute_dtype=torch.float64)
+    tol = TOL_BLOCK if dtype == torch.float32 else 2e-2
+    assert y.dtype == dtype and y.shape == yr.shape
+    e_y = O.rel_l2(y.detach().float().cpu(), yr.detach())
+    assert e_y < tol, ("y", e_y)
+    if conv.scale_residual:
+        e_r = O.rel_l2(res.detach().float().cpu(), resr.detach())
+        assert e_r < tol, ("residual", e_r)
+    else:
+        assert res is x
+    gy = torch.randn_like(yr)
+    loss = (y.float() * gy.float().to(DEV)).sum()
+    lossr = (yr * gy).sum()
+    if conv.scale_residual:
+        gr = torch.randn_like(resr)
+        loss = loss + (res.float() * gr.float().to(DEV)).sum()
+        lossr = lossr + (resr * gr).sum()
+    loss.backward()
+    lossr.backward()
+    e_gx = O.rel_l2(x.grad.float().cpu(), xr.grad)
+    e_gw = float((conv.weight.grad.cpu().to(torch.complex128) - wr.grad).norm() / wr.grad.norm())
+    assert e_gx < tol, ("dx", e_gx)
+    assert e_gw < tol, ("dw", e_gw)
+    return e_y, e_gx, e_gw
+
+
+@pytest.mark.parametrize("op", ["dhconv", "diagonal"])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_spectral_conv_same_grid(mk, op, dtype):
+    _block(mk, 32, 64, "legendre-gauss", 32, 64, "legendre-gauss", 32, 33, 12, 20, op, 2, dtype)
+
+
+def test_spectral_conv_bias_and_residual_rescale(mk):
+    # block-0 like: equiangular fine grid in, Gauss coarse grid out -> residual is re-projected
+    _block(mk, 49, 96, "equiangular", 16, 32, "legendre-gauss", 16, 17, 8, 8, "dhconv", 2, torch.float32, bias="constant")
+    # block-7 like: coarse in, fine out, position bias
+    _block(mk, 16, 32, "legendre-gauss", 49, 96, "equiangular", 16, 17, 8, 8, "dhconv", 1, torch.float32, bias="position")
+
+
+def test_spectral_conv_sfno_internal_shapes_small_channels(mk):
+    # the internal SFNO grid (240x480 Gauss, L=240, M=241) with few channels so the fp64 oracle stays cheap
+    _block(mk, 240, 480, "legendre-gauss", 240, 480, "legendre-gauss", 240, 241, 8, 8, "dhconv", 1, torch.float32)
+
+
+def test_state_dict_and_annotations(mk):
+    fwd = mk.RealSHT(16, 32, grid="legendre-gauss")
+    inv = mk.InverseRealSHT(16, 32, grid="legendre-gauss")
+    conv = mk.SpectralConv(fwd, inv, 4, 6, operator_type="dhconv", bias="constant")
+    sd = conv.state_dict()
+    assert set(sd) == {"weight", "bias"}                       # tables are non-persistent buffers
+    assert sd["weight"].dtype == torch.complex64 and tuple(sd["weight"].shape) == (4, 6, 16)
+    assert conv.weight.is_shared_mp == ["matmul", "w"] and conv.weight.sharded_dims_mp == [None, None, "h"]
+    assert mk.SpectralConvS2 is mk.SpectralConv
+    d = mk.SpectralConv(fwd, inv, 4, 6, operator_type="diagonal")
+    assert tuple(d.weight.shape) == (4, 6, 16, 17) and d.weight.sharded_dims_mp == [None, None, "h", "w"]
+    with pytest.raises(ValueError):
+        mk.SpectralConv(fwd, inv, 4, 6, operator_type="nope")
+
+
+# ---------------------------------------------------------------- full BASELINE sizes: properties only
+def test_full_size_roundtrip_and_linearity_internal_grid(mk):
+    torch.manual_seed(3)
+    nlat, nlon, L, M, C = 240, 480, 240, 241, 384
+    sht = mk.RealSHT(nlat, nlon, lmax=L, mmax=M, grid="legendre-gauss").to(DEV)
+    isht = mk.InverseRealSHT(nlat, nlon, lmax=L, mmax=M, grid="legendre-gauss").to(DEV)
+    c = torch.randn(1, C, L, M, dtype=torch.complex64, device=DEV) * torch.tril(torch.ones(L, M, device=DEV))
+    c[..., 0] = c[..., 0].real.to(torch.complex64)
+    c[..., M - 1] = 0                                      # m = 240 has no degree l >= m when L = 240
+    x = isht(c)
+    c2 = sht(x)
+    assert O.rel_l2(c2.cpu(), c.cpu()) < 2 * TOL_T          # sht(isht(c)) = c for band-limited c
+    x2 = isht(c2)
+    assert O.rel_l2(x2.cpu(), x.cpu()) < 2 * TOL_T          # isht o sht is a projection
+    a, b = torch.randn_like(x), torch.randn_like(x)
+    lin = sht(2.0 * a - 3.0 * b)
+    assert O.rel_l2(lin.cpu(), (2.0 * sht(a) - 3.0 * sht(b)).cpu()) < 2 * TOL_T
+
+
+def test_full_size_block0_shapes(mk):
+    """721x1440 equiangular in -> 240x480 Gauss out at C = 384 (SFNO block 0): adjoint identity
+    <conv(x), g> = <x, conv^T g> ties forward and backward together without an oracle at this size."""
+    torch.manual_seed(4)
+    C, L, M = 384, 240, 241
+    fwd = mk.RealSHT(721, 1440, lmax=L, mmax=M, grid="equiangular").to(DEV)
+    inv = mk.InverseRealSHT(240, 480, lmax=L, mmax=M, grid="legendre-gauss").to(DEV)
+    conv = mk.SpectralConv(fwd, inv, C, C, operator_type="dhconv").to(DEV)
+    x = torch.randn(1, C, 721, 1440, device=DEV, requires_grad=True)
+    y, res = conv(x)
+    assert y.shape == (1, C, 240, 480) and res.shape == (1, C, 240, 480)
+    g, gr = torch.randn_like(y), torch.randn_like(res)
+    ((y * g).sum() + (res * gr).sum()).backward()
+    lhs = float((y.double() * g.double()).sum() + (res.double() * gr.double()).sum())
+    rhs = float((x.detach().double() * x.grad.double()).sum())
+    assert abs(lhs - rhs) / abs(lhs) < 5e-3, (lhs, rhs)
+    assert torch.isfinite(conv.weight.grad.abs()).all()

@@ -60,10 +60,10 @@ long long sfno_sp_elems(int lmax, int mmax, int B, int C);
 long long sfno_wp_elems(int lmax, int Cin, int Cout);
 
 /* ---- K1 longitude DFT:   x[B*C][nlat][nlon] -> XM     (torch.fft.rfft at RealSHT.forward; call site
- * makani/models/common/spectral_convolution.py:131).  mscale_host[mmax] multiplies bin m
+ * makani/models/common/spectral_convolution.py:131).  mscale_dev[mmax] multiplies bin m
  * (forward SHT: 2*pi/nlon for all m; adjoint of the inverse DFT: 1,2,2,..(,1 at Nyquist)).       */
 int sfno_dft_fwd(const void* x, int x_dtype, int B, int C, int nlat, int nlon, int mmax,
-                 const float* mscale_dev, float* xm, void* stream);
+                 const float* mscale_dev, float* xm, int round_tf32, void* stream);
 
 /* ---- K5 inverse longitude DFT:   XM -> y[B*C][nlat][nlon]   (torch.fft.irfft(n=nlon, norm="forward") at
  * InverseRealSHT.forward; call site spectral_convolution.py:133,141).  mscale_dev[mmax] pre-multiplies
@@ -76,7 +76,10 @@ int sfno_dft_inv(const float* xm, int B, int C, int nlat, int nlon, int mmax, in
  * analysis : SP[l][m][r]  = sum_k XM[m][r][k] * table[m][l][k]   (einsum '...km,mlk->...lm')
  * synthesis: XM[m][r][k]  = sum_l SP[l][m][r] * table[m][l][k]   (einsum '...lm,mlk->...km')
  * The same plan serves both directions (a forward plan's synthesis is the adjoint needed by backward). */
-int sfno_legendre_analysis(const sfno_plan* plan, const float* xm, int B, int C, float* sp, void* stream);
+/* round_tf32 = 1 stores round-to-nearest TF32 values (set it when the output feeds another TF32 contraction:
+ * the tensor core otherwise truncates, a one-sided ~1e-3 bias); 0 keeps full fp32 (output leaves the path). */
+int sfno_legendre_analysis(const sfno_plan* plan, const float* xm, int B, int C, float* sp, int round_tf32,
+                           void* stream);
 int sfno_legendre_synthesis(const sfno_plan* plan, const float* sp, int B, int C, float* xm, void* stream);
 
 /* ---- K3 dhconv channel contraction (makani/models/common/contractions.py:131-136,
@@ -88,10 +91,10 @@ int sfno_dhconv_unpack_wgrad(const float* gwp, int Cin, int Cout, int L,
 /* l_offset / m_offset: global degree / order of local index 0 (non-zero only for the h/w-sharded
  * DistributedRealSHT layout); they place the triangular m <= l structure that the kernels skip. */
 int sfno_dhconv_fwd(const float* sp_in, const float* wp, float* sp_out, int B, int Cin, int Cout,
-                    int lmax, int mmax, int l_offset, int m_offset, void* stream);
+                    int lmax, int mmax, int l_offset, int m_offset, int round_tf32, void* stream);
 /* dX[b,i,l,m] = sum_o dY[b,o,l,m] * conj(w[i,o,l]) */
 int sfno_dhconv_bwd_x(const float* gsp_out, const float* wp, float* gsp_in, int B, int Cin, int Cout,
-                      int lmax, int mmax, int l_offset, int m_offset, void* stream);
+                      int lmax, int mmax, int l_offset, int m_offset, int round_tf32, void* stream);
 /* dW[i,o,l] = sum_{b,m} conj(x[b,i,l,m]) * dY[b,o,l,m]   (packed layout WP) */
 int sfno_dhconv_bwd_w(const float* sp_in, const float* gsp_out, float* gwp, int B, int Cin, int Cout,
                       int lmax, int mmax, int l_offset, int m_offset, void* stream);

@@ -25,14 +25,14 @@ _PROTOTYPES = {
     "sfno_xm_elems": (_ll, [_i, _i, _i, _i]),
     "sfno_sp_elems": (_ll, [_i, _i, _i, _i]),
     "sfno_wp_elems": (_ll, [_i, _i, _i]),
-    "sfno_dft_fwd": (_i, [_vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp]),
+    "sfno_dft_fwd": (_i, [_vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _i, _vp]),
     "sfno_dft_inv": (_i, [_vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _i, _vp]),
-    "sfno_legendre_analysis": (_i, [_vp, _vp, _i, _i, _vp, _vp]),
+    "sfno_legendre_analysis": (_i, [_vp, _vp, _i, _i, _vp, _i, _vp]),
     "sfno_legendre_synthesis": (_i, [_vp, _vp, _i, _i, _vp, _vp]),
     "sfno_dhconv_pack_weight": (_i, [_vp, _i, _i, _i, _vp, _vp]),
     "sfno_dhconv_unpack_wgrad": (_i, [_vp, _i, _i, _i, _vp, _vp]),
-    "sfno_dhconv_fwd": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
-    "sfno_dhconv_bwd_x": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
+    "sfno_dhconv_fwd": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
+    "sfno_dhconv_bwd_x": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "sfno_dhconv_bwd_w": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "sfno_diag_contract": (_i, [_i, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "sfno_sp_to_c64": (_i, [_vp, _i, _i, _i, _i, _i, _i, _vp, _vp]),

@@ -10,6 +10,16 @@
 namespace sfno {
 
 static thread_local std::string t_last_error;
+
+// round-to-nearest (ties away) to TF32 on the host, same result as cvt.rna.tf32.f32 for finite values
+static float tf32_rn_host(float x) {
+  uint32_t u;
+  memcpy(&u, &x, 4);
+  if ((u & 0x7f800000u) == 0x7f800000u) return x;
+  u = (u + 0x1000u) & 0xffffe000u;
+  memcpy(&x, &u, 4);
+  return x;
+}
 std::atomic<long long> g_launch_count{0};
 
 void set_error(const std::string& msg) { t_last_error = msg; }
@@ -53,7 +63,7 @@ int sfno_plan_create(int nlat, int nlon, int lmax, int mmax, int m_offset, const
     for (int l = 0; l < lmax; ++l) {
       const double* src = table_host + ((size_t)m * lmax + l) * nlat;
       float* dst = h.data() + ((size_t)m * lmax + l) * p->Kp;
-      for (int k = 0; k < nlat; ++k) dst[k] = (float)src[k];
+      for (int k = 0; k < nlat; ++k) dst[k] = tf32_rn_host((float)src[k]);
     }
   cudaError_t e = cudaMalloc(&p->table, n * sizeof(float));
   if (e == cudaSuccess) e = cudaMemcpy(p->table, h.data(), n * sizeof(float), cudaMemcpyHostToDevice);
@@ -75,32 +85,34 @@ int sfno_plan_destroy(sfno_plan* plan) {
 }
 
 int sfno_dft_fwd(const void* x, int x_dtype, int B, int C, int nlat, int nlon, int mmax, const float* mscale_dev,
-                 float* xm, void* stream) {
+                 float* xm, int round_tf32, void* stream) {
   SFNO_CHECK(x && xm && mscale_dev, "null argument");
-  return dft_fwd(x, x_dtype, B, C, nlat, nlon, mmax, mscale_dev, xm, (cudaStream_t)stream);
+  return dft_fwd(x, x_dtype, B, C, nlat, nlon, mmax, mscale_dev, xm, round_tf32, (cudaStream_t)stream);
 }
 int sfno_dft_inv(const float* xm, int B, int C, int nlat, int nlon, int mmax, int m_valid, const float* mscale_dev,
                  void* y, int y_dtype, void* stream) {
   SFNO_CHECK(xm && y && mscale_dev, "null argument");
   return dft_inv(xm, B, C, nlat, nlon, mmax, m_valid, mscale_dev, y, y_dtype, (cudaStream_t)stream);
 }
-int sfno_legendre_analysis(const sfno_plan* plan, const float* xm, int B, int C, float* sp, void* stream) {
+int sfno_legendre_analysis(const sfno_plan* plan, const float* xm, int B, int C, float* sp, int round_tf32,
+                           void* stream) {
   SFNO_CHECK(plan && xm && sp, "null argument");
-  return legendre_analysis(plan, xm, B, C, sp, (cudaStream_t)stream);
+  return legendre_analysis(plan, xm, B, C, sp, round_tf32, (cudaStream_t)stream);
 }
 int sfno_legendre_synthesis(const sfno_plan* plan, const float* sp, int B, int C, float* xm, void* stream) {
   SFNO_CHECK(plan && xm && sp, "null argument");
   return legendre_synthesis(plan, sp, B, C, xm, (cudaStream_t)stream);
 }
 int sfno_dhconv_fwd(const float* sp_in, const float* wp, float* sp_out, int B, int Cin, int Cout, int lmax, int mmax,
-                    int l_offset, int m_offset, void* stream) {
+                    int l_offset, int m_offset, int round_tf32, void* stream) {
   SFNO_CHECK(sp_in && wp && sp_out, "null argument");
-  return dhconv_fwd(sp_in, wp, sp_out, B, Cin, Cout, lmax, mmax, l_offset, m_offset, (cudaStream_t)stream);
+  return dhconv_fwd(sp_in, wp, sp_out, B, Cin, Cout, lmax, mmax, l_offset, m_offset, round_tf32, (cudaStream_t)stream);
 }
 int sfno_dhconv_bwd_x(const float* gsp_out, const float* wp, float* gsp_in, int B, int Cin, int Cout, int lmax,
-                      int mmax, int l_offset, int m_offset, void* stream) {
+                      int mmax, int l_offset, int m_offset, int round_tf32, void* stream) {
   SFNO_CHECK(gsp_out && wp && gsp_in, "null argument");
-  return dhconv_bwd_x(gsp_out, wp, gsp_in, B, Cin, Cout, lmax, mmax, l_offset, m_offset, (cudaStream_t)stream);
+  return dhconv_bwd_x(gsp_out, wp, gsp_in, B, Cin, Cout, lmax, mmax, l_offset, m_offset, round_tf32,
+                      (cudaStream_t)stream);
 }
 int sfno_dhconv_bwd_w(const float* sp_in, const float* gsp_out, float* gwp, int B, int Cin, int Cout, int lmax,
                       int mmax, int l_offset, int m_offset, void* stream) {

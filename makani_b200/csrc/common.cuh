@@ -45,9 +45,11 @@ inline long long round_up_ll(long long x, long long m) { return (x + m - 1) / m 
 
 // TMA descriptor encode via the driver entry point (no -lcuda link dependency: the library must load on
 // a machine without a driver for the CPU-side symbol test).
+// swizzle: 1 = SWIZZLE_128B (16 B atoms; K-major UMMA operands),
+//          2 = SWIZZLE_128B_ATOM_32B (32 B atoms; the only layout tcgen05 accepts for MN-major 32-bit operands)
 int encode_tensor_map(CUtensorMap* map, const void* gptr, int rank, const uint64_t* dims,
                       const uint64_t* strides_bytes /* rank-1 entries */, const uint32_t* box,
-                      bool swizzle128);
+                      int swizzle);
 
 // ------------------------------------------------------------------ device-side PTX wrappers
 #ifdef __CUDACC__
@@ -189,17 +191,29 @@ __device__ __forceinline__ void tmem_ld_32x16(uint32_t taddr, uint32_t (&v)[16])
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
+// round-to-nearest TF32 (10-bit mantissa).  tcgen05 kind::tf32 ignores the low 13 mantissa bits of its fp32
+// operands (truncation, a one-sided ~1e-3 relative bias); producers of GEMM operands pre-round so the error
+// becomes unbiased and ~3x smaller.
+__device__ __forceinline__ float tf32_rn(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return __uint_as_float(r);
+}
+
 // ---- UMMA descriptors
-// Shared-memory matrix descriptor, SWIZZLE_128B, sm_100 version field = 1.
+// Shared-memory matrix descriptor, sm_100 version field = 1.
 //   bits [0,14)  start address >> 4      bits [16,30) leading byte offset >> 4
-//   bits [32,46) stride byte offset >> 4 bits [46,48) version (1)    bits [61,64) layout (2 = SW128)
-__device__ __forceinline__ uint64_t umma_smem_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+//   bits [32,46) stride byte offset >> 4 bits [46,48) version (1)
+//   bits [61,64) layout: 2 = SWIZZLE_128B (16 B atoms), 1 = SWIZZLE_128B_BASE32B (32 B atoms, MN-major tf32)
+constexpr uint32_t kUmmaSw128 = 2, kUmmaSw128Base32 = 1;
+__device__ __forceinline__ uint64_t umma_smem_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes,
+                                                   uint32_t layout) {
   uint64_t d = 0;
   d |= (uint64_t)((saddr & 0x3FFFFu) >> 4);
   d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFFu) << 16;
   d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFFu) << 32;
   d |= (uint64_t)1 << 46;
-  d |= (uint64_t)2 << 61;
+  d |= (uint64_t)layout << 61;
   return d;
 }
 // Instruction descriptor for kind::tf32, fp32 accumulate, M = 128.

@@ -69,7 +69,7 @@ constexpr int kRows = 16;   // flat positions per CTA tile
 template <typename T>
 __global__ void __launch_bounds__(256)
 dft_fwd_generic_kernel(const T* __restrict__ x, float* __restrict__ xm, const float2* __restrict__ tw,
-                       const float* __restrict__ mscale, int B, int C, int K, int Kp, int W, int M) {
+                       const float* __restrict__ mscale, int B, int C, int K, int Kp, int W, int M, int round_out) {
   extern __shared__ float sm[];
   const int Cp = (C + 3) & ~3;
   const long long RS = 2LL * B * Cp;
@@ -111,8 +111,10 @@ dft_fwd_generic_kernel(const T* __restrict__ x, float* __restrict__ xm, const fl
   for (int idx = threadIdx.x; idx < 2 * M * kRows; idx += blockDim.x) {
     const int r = idx % kRows, pm = idx / kRows;
     const int reim = pm / M, m = pm % M;
-    if (f0 + r < flat)
-      xm[((long long)m * RS + (long long)(b * 2 + reim) * Cp) * Kp + f0 + r] = outs[pm * (kRows + 1) + r];
+    if (f0 + r < flat) {
+      const float v = outs[pm * (kRows + 1) + r];
+      xm[((long long)m * RS + (long long)(b * 2 + reim) * Cp) * Kp + f0 + r] = round_out ? tf32_rn(v) : v;
+    }
   }
 }
 
@@ -238,7 +240,7 @@ struct FftSmem {
 template <int R, typename T>
 __global__ void __launch_bounds__(256, 2)
 dft_fwd_fft480_kernel(const T* __restrict__ x, float* __restrict__ xm, const fl::cf* __restrict__ tables,
-                      const float* __restrict__ mscale, int B, int C, int K, int Kp, int M) {
+                      const float* __restrict__ mscale, int B, int C, int K, int Kp, int M, int round_out) {
   using S = FftSmem<R, T>;
   constexpr int W = S::W;
   extern __shared__ __align__(16) uint8_t smraw[];
@@ -305,9 +307,10 @@ dft_fwd_fft480_kernel(const T* __restrict__ x, float* __restrict__ xm, const fl:
     for (int idx = threadIdx.x; idx < 2 * M * kRows; idx += blockDim.x) {
       const int rr = idx % kRows, pm = idx / kRows;
       const int reim = pm / M, m = pm % M;
-      if (f0 + rr < flat)
-        xm[((long long)m * RS + (long long)(b * 2 + reim) * Cp) * Kp + f0 + rr] =
-            stage[(reim * 241 + m) * (kRows + 1) + rr];
+      if (f0 + rr < flat) {
+        const float v = stage[(reim * 241 + m) * (kRows + 1) + rr];
+        xm[((long long)m * RS + (long long)(b * 2 + reim) * Cp) * Kp + f0 + rr] = round_out ? tf32_rn(v) : v;
+      }
     }
     __syncthreads();
   }
@@ -396,7 +399,7 @@ static int sm_count() {
 
 template <int R, typename T>
 static int launch_fwd_fft(const void* x, int B, int C, int K, int Kp, int M, const float* mscale, float* xm,
-                          cudaStream_t stream) {
+                          int round_out, cudaStream_t stream) {
   using S = FftSmem<R, T>;
   const fl::cf* tables;
   if (get_fft_tables(&tables)) return 1;
@@ -407,7 +410,7 @@ static int launch_fwd_fft(const void* x, int B, int C, int K, int Kp, int M, con
   }
   const int ntiles = ((C * Kp + kRows - 1) / kRows) * B;
   const int grid = std::min(ntiles, 2 * sm_count());
-  dft_fwd_fft480_kernel<R, T><<<grid, 256, S::kBytes, stream>>>(static_cast<const T*>(x), xm, tables, mscale, B, C, K, Kp, M);
+  dft_fwd_fft480_kernel<R, T><<<grid, 256, S::kBytes, stream>>>(static_cast<const T*>(x), xm, tables, mscale, B, C, K, Kp, M, round_out);
   SFNO_LAUNCHED();
   return 0;
 }
@@ -431,14 +434,14 @@ static int launch_inv_fft(const float* xm, int B, int C, int K, int Kp, int M, i
 
 template <typename T>
 static int launch_fwd_generic(const void* x, int B, int C, int K, int Kp, int W, int M, const float* mscale, float* xm,
-                              cudaStream_t stream) {
+                              int round_out, cudaStream_t stream) {
   const float2* tw;
   if (get_twiddles(W, &tw)) return 1;
   const size_t smem = (size_t)(kRows * (W + 1) + 2 * W + 2 * M * (kRows + 1)) * 4 + 16;
   SFNO_CHECK(smem <= 200 * 1024, "generic DFT: nlon too large for the shared-memory kernel");
   SFNO_CUDA(cudaFuncSetAttribute(dft_fwd_generic_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
   const int ntiles = ((C * Kp + kRows - 1) / kRows) * B;
-  dft_fwd_generic_kernel<T><<<ntiles, 256, smem, stream>>>(static_cast<const T*>(x), xm, tw, mscale, B, C, K, Kp, W, M);
+  dft_fwd_generic_kernel<T><<<ntiles, 256, smem, stream>>>(static_cast<const T*>(x), xm, tw, mscale, B, C, K, Kp, W, M, round_out);
   SFNO_LAUNCHED();
   return 0;
 }
@@ -463,15 +466,15 @@ static bool use_fft480(int W, int M, const void* p) {
 }
 
 int dft_fwd(const void* x, int x_dtype, int B, int C, int nlat, int nlon, int mmax, const float* mscale,
-            float* xm, cudaStream_t stream) {
+            float* xm, int round_out, cudaStream_t stream) {
   SFNO_CHECK(mmax <= nlon / 2 + 1, "mmax exceeds nlon/2+1");
   const int Kp = round_up(nlat, 4);
   const bool fast = use_fft480(nlon, mmax, x);
 #define SFNO_DISPATCH_FWD(T)                                                                           \
   do {                                                                                                 \
-    if (fast && nlon == 480) return launch_fwd_fft<1, T>(x, B, C, nlat, Kp, mmax, mscale, xm, stream); \
-    if (fast && nlon == 1440) return launch_fwd_fft<3, T>(x, B, C, nlat, Kp, mmax, mscale, xm, stream);\
-    return launch_fwd_generic<T>(x, B, C, nlat, Kp, nlon, mmax, mscale, xm, stream);                   \
+    if (fast && nlon == 480) return launch_fwd_fft<1, T>(x, B, C, nlat, Kp, mmax, mscale, xm, round_out, stream); \
+    if (fast && nlon == 1440) return launch_fwd_fft<3, T>(x, B, C, nlat, Kp, mmax, mscale, xm, round_out, stream);\
+    return launch_fwd_generic<T>(x, B, C, nlat, Kp, nlon, mmax, mscale, xm, round_out, stream);                   \
   } while (0)
   switch (x_dtype) {
     case SFNO_F32: SFNO_DISPATCH_FWD(float);

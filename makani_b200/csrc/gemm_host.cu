@@ -30,7 +30,7 @@ static PFN_encodeTiled get_encode_fn() {
 }
 
 int encode_tensor_map(CUtensorMap* map, const void* gptr, int rank, const uint64_t* dims,
-                      const uint64_t* strides_bytes, const uint32_t* box, bool swizzle128) {
+                      const uint64_t* strides_bytes, const uint32_t* box, int swizzle) {
   PFN_encodeTiled fn = get_encode_fn();
   SFNO_CHECK(fn != nullptr, "cuTensorMapEncodeTiled entry point not available (no CUDA driver?)");
   cuuint64_t d[5];
@@ -48,7 +48,7 @@ int encode_tensor_map(CUtensorMap* map, const void* gptr, int rank, const uint64
   SFNO_CHECK((reinterpret_cast<uintptr_t>(gptr) & 15) == 0, "TMA global address must be 16-byte aligned");
   CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, (cuuint32_t)rank, const_cast<void*>(gptr), d, s, b, e,
                   CU_TENSOR_MAP_INTERLEAVE_NONE,
-                  swizzle128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE,
+                  swizzle == 1 ? CU_TENSOR_MAP_SWIZZLE_128B : (swizzle == 2 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_NONE),
                   CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   SFNO_CHECK(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with code " + std::to_string((int)r));
   return 0;
@@ -133,7 +133,8 @@ static int current_device() {
 }
 
 // ------------------------------------------------------------------ Legendre analysis  (K2)
-int legendre_analysis(const sfno_plan* plan, const float* xm, int B, int C, float* sp, cudaStream_t stream) {
+int legendre_analysis(const sfno_plan* plan, const float* xm, int B, int C, float* sp, int round_out,
+                      cudaStream_t stream) {
   const int K = plan->nlat, Kp = plan->Kp, L = plan->lmax, M = plan->mmax, moff = plan->m_offset;
   const int RS = 2 * B * round_up(C, 4);
   CUtensorMap ma, mb;
@@ -141,13 +142,13 @@ int legendre_analysis(const sfno_plan* plan, const float* xm, int B, int C, floa
     uint64_t dims[3] = {(uint64_t)K, (uint64_t)RS, (uint64_t)M};
     uint64_t str[2] = {(uint64_t)Kp * 4, (uint64_t)RS * Kp * 4};
     uint32_t box[3] = {32, 128, 1};
-    if (encode_tensor_map(&ma, xm, 3, dims, str, box, true)) return 1;
+    if (encode_tensor_map(&ma, xm, 3, dims, str, box, 1)) return 1;
   }
   {
     uint64_t dims[3] = {(uint64_t)K, (uint64_t)L, (uint64_t)M};
     uint64_t str[2] = {(uint64_t)Kp * 4, (uint64_t)L * Kp * 4};
     uint32_t box[3] = {32, 64, 1};
-    if (encode_tensor_map(&mb, plan->table, 3, dims, str, box, true)) return 1;
+    if (encode_tensor_map(&mb, plan->table, 3, dims, str, box, 1)) return 1;
   }
   TileList tl;
   TileKey key{current_device(), LEG_ANA, K, L, M, moff, RS, 0, 0};
@@ -172,6 +173,7 @@ int legendre_analysis(const sfno_plan* plan, const float* xm, int B, int C, floa
   args.out_g_stride = RS;                       // SP[l][m][r]: g = m
   args.out_col_stride = (long long)M * RS;      // column = l
   args.out_im_offset = 0;
+  args.round_out = round_out;
   return launch<LEG_ANA>(ma, mb, args, stream);
 }
 
@@ -184,13 +186,13 @@ int legendre_synthesis(const sfno_plan* plan, const float* sp, int B, int C, flo
     uint64_t dims[3] = {(uint64_t)K, (uint64_t)L, (uint64_t)M};
     uint64_t str[2] = {(uint64_t)Kp * 4, (uint64_t)L * Kp * 4};
     uint32_t box[3] = {32, 32, 1};
-    if (encode_tensor_map(&ma, plan->table, 3, dims, str, box, true)) return 1;
+    if (encode_tensor_map(&ma, plan->table, 3, dims, str, box, 2)) return 1;
   }
   {
     uint64_t dims[3] = {(uint64_t)RS, (uint64_t)M, (uint64_t)L};
     uint64_t str[2] = {(uint64_t)RS * 4, (uint64_t)M * RS * 4};
     uint32_t box[3] = {32, 1, 32};
-    if (encode_tensor_map(&mb, sp, 3, dims, str, box, true)) return 1;
+    if (encode_tensor_map(&mb, sp, 3, dims, str, box, 2)) return 1;
   }
   TileList tl;
   TileKey key{current_device(), LEG_SYN, K, L, M, moff, RS, 0, 0};
@@ -216,6 +218,7 @@ int legendre_synthesis(const sfno_plan* plan, const float* sp, int B, int C, flo
   args.out_g_stride = (long long)RS * Kp;       // XM[m][r][k]: g = m
   args.out_col_stride = Kp;                     // column = r
   args.out_im_offset = 0;
+  args.round_out = 0;                           // consumed by the fp32 inverse DFT
   return launch<LEG_SYN>(ma, mb, args, stream);
 }
 
@@ -226,14 +229,14 @@ static int sp_map_kmajor(CUtensorMap* map, const float* sp, int C, int B, int L,
   uint64_t dims[4] = {(uint64_t)C, 2, (uint64_t)M * B, (uint64_t)L};
   uint64_t str[3] = {(uint64_t)Cp * 4, (uint64_t)2 * Cp * 4, (uint64_t)M * B * 2 * Cp * 4};
   uint32_t box[4] = {32, 1, 64, 1};
-  return encode_tensor_map(map, sp, 4, dims, str, box, true);
+  return encode_tensor_map(map, sp, 4, dims, str, box, 1);
 }
 static int sp_map_mnmajor(CUtensorMap* map, const float* sp, int C, int B, int L, int M) {
   const int Cp = round_up(C, 4);
   uint64_t dims[4] = {(uint64_t)C, 2, (uint64_t)M * B, (uint64_t)L};
   uint64_t str[3] = {(uint64_t)Cp * 4, (uint64_t)2 * Cp * 4, (uint64_t)M * B * 2 * Cp * 4};
   uint32_t box[4] = {32, 1, 32, 1};
-  return encode_tensor_map(map, sp, 4, dims, str, box, true);
+  return encode_tensor_map(map, sp, 4, dims, str, box, 2);
 }
 static int wp_map(CUtensorMap* map, const float* wp, int Cin, int Cout, int L, bool mn_major) {
   const int Cinp = round_up(Cin, 4), Coutp = round_up(Cout, 4);
@@ -241,11 +244,11 @@ static int wp_map(CUtensorMap* map, const float* wp, int Cin, int Cout, int L, b
   uint64_t str[3] = {(uint64_t)Cinp * 4, (uint64_t)Coutp * Cinp * 4, (uint64_t)2 * Coutp * Cinp * 4};
   uint32_t box_k[4] = {32, 128, 1, 1};
   uint32_t box_mn[4] = {32, 32, 1, 1};
-  return encode_tensor_map(map, wp, 4, dims, str, mn_major ? box_mn : box_k, true);
+  return encode_tensor_map(map, wp, 4, dims, str, mn_major ? box_mn : box_k, mn_major ? 2 : 1);
 }
 
 int dhconv_fwd(const float* sp_in, const float* wp, float* sp_out, int B, int Cin, int Cout, int L, int M,
-               int l_offset, int m_offset, cudaStream_t stream) {
+               int l_offset, int m_offset, int round_out, cudaStream_t stream) {
   CUtensorMap ma, mb;
   if (wp_map(&ma, wp, Cin, Cout, L, false)) return 1;
   if (sp_map_kmajor(&mb, sp_in, Cin, B, L, M)) return 1;
@@ -273,11 +276,12 @@ int dhconv_fwd(const float* sp_in, const float* wp, float* sp_out, int B, int Ci
   args.out_g_stride = (long long)M * B * 2 * Coutp;
   args.out_col_stride = 2 * Coutp;              // column = n = m*B + b
   args.out_im_offset = Coutp;
+  args.round_out = round_out;
   return launch<DH_FWD>(ma, mb, args, stream);
 }
 
 int dhconv_bwd_x(const float* gsp_out, const float* wp, float* gsp_in, int B, int Cin, int Cout, int L, int M,
-                 int l_offset, int m_offset, cudaStream_t stream) {
+                 int l_offset, int m_offset, int round_out, cudaStream_t stream) {
   CUtensorMap ma, mb;
   if (wp_map(&ma, wp, Cin, Cout, L, true)) return 1;
   if (sp_map_kmajor(&mb, gsp_out, Cout, B, L, M)) return 1;
@@ -305,6 +309,7 @@ int dhconv_bwd_x(const float* gsp_out, const float* wp, float* gsp_in, int B, in
   args.out_g_stride = (long long)M * B * 2 * Cinp;
   args.out_col_stride = 2 * Cinp;
   args.out_im_offset = Cinp;
+  args.round_out = round_out;
   return launch<DH_BWDX>(ma, mb, args, stream);
 }
 
@@ -337,6 +342,7 @@ int dhconv_bwd_w(const float* sp_in, const float* gsp_out, float* gwp, int B, in
   args.out_g_stride = (long long)2 * Coutp * Cinp;   // WP[l][reim][o][i]: rows = i, columns = o
   args.out_col_stride = Cinp;
   args.out_im_offset = (long long)Coutp * Cinp;
+  args.round_out = 0;
   return launch<DH_BWDW>(ma, mb, args, stream);
 }
 

@@ -41,6 +41,7 @@ struct GemmArgs {
   long long out_g_stride;   // output offset per batch index g
   long long out_col_stride; // output offset per column
   long long out_im_offset;  // complex modes: offset of the imaginary plane
+  int round_out;            // 1: store round-to-nearest TF32 values (the consumer is another TF32 GEMM)
 };
 
 template <int MODE>
@@ -189,14 +190,19 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
             // K-major: advance 8 tf32 = 32 B inside the 128 B swizzle row.  MN-major: 8 k-rows = 1024 B.
             const uint32_t aoff = Cfg::kAMn ? kk * 1024 : kk * 32;
             const uint32_t boff = Cfg::kBMn ? kk * 1024 : kk * 32;
+            // K-major  : SWIZZLE_128B, 8-row groups 1024 B apart (SBO), LBO unused.
+            // MN-major : SWIZZLE_128B_BASE32B - 32-element MN chunks 4096 B apart (LBO), 4-row K atoms 512 B apart (SBO).
             const uint32_t albo = Cfg::kAMn ? 4096 : 0, blbo = Cfg::kBMn ? 4096 : 0;
-            const uint64_t da0 = umma_smem_desc(a0 + aoff, albo, 1024);
-            const uint64_t db0 = umma_smem_desc(b0 + boff, blbo, 1024);
+            const uint32_t asbo = Cfg::kAMn ? 512 : 1024, bsbo = Cfg::kBMn ? 512 : 1024;
+            const uint32_t alay = Cfg::kAMn ? kUmmaSw128Base32 : kUmmaSw128;
+            const uint32_t blay = Cfg::kBMn ? kUmmaSw128Base32 : kUmmaSw128;
+            const uint64_t da0 = umma_smem_desc(a0 + aoff, albo, asbo, alay);
+            const uint64_t db0 = umma_smem_desc(b0 + boff, blbo, bsbo, blay);
             if constexpr (!Cfg::kComplex) {
               umma_tf32(d_re, da0, db0, id_pp, acc);
             } else {
-              const uint64_t da1 = umma_smem_desc(a0 + Cfg::kABytes + aoff, albo, 1024);   // imaginary planes
-              const uint64_t db1 = umma_smem_desc(b0 + Cfg::kBBytes + boff, blbo, 1024);
+              const uint64_t da1 = umma_smem_desc(a0 + Cfg::kABytes + aoff, albo, asbo, alay);   // imaginary planes
+              const uint64_t db1 = umma_smem_desc(b0 + Cfg::kBBytes + boff, blbo, bsbo, blay);
               if constexpr (MODE == DH_FWD) {
                 // Y = W X :  re = Wr Xr - Wi Xi ;  im = Wi Xr + Wr Xi
                 umma_tf32(d_re, da0, db0, id_pp, acc);
@@ -253,7 +259,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
 #pragma unroll
             for (int j = 0; j < 32; ++j) {
               const int col = tile.col0 + c + j;
-              if (col < tile.col_limit) op[(long long)col * args.out_col_stride] = __uint_as_float(v[j]);
+              if (col < tile.col_limit) {
+                const float val = __uint_as_float(v[j]);
+                op[(long long)col * args.out_col_stride] = args.round_out ? tf32_rn(val) : val;
+              }
             }
           }
         }

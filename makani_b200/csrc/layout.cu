@@ -8,6 +8,7 @@
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
 #include <algorithm>
+#include <type_traits>
 
 namespace sfno {
 
@@ -56,8 +57,8 @@ __global__ void c64_to_sp_kernel(const float2* __restrict__ in, float* __restric
     const int m = m0 + j, c = c0 + threadIdx.x;
     if (m < M && c < Cp) {      // pad channels are written as zeros so the whole SP tensor is defined
       const long long base = ((long long)l * M + m) * RS + (long long)(b * 2) * Cp + c;
-      sp[base] = (c < C) ? tr[threadIdx.x][j] : 0.f;
-      sp[base + Cp] = (c < C) ? ti[threadIdx.x][j] : 0.f;
+      sp[base] = (c < C) ? tf32_rn(tr[threadIdx.x][j]) : 0.f;        // operands of TF32 GEMMs: pre-rounded
+      sp[base + Cp] = (c < C) ? tf32_rn(ti[threadIdx.x][j]) : 0.f;
     }
   }
 }
@@ -108,8 +109,8 @@ __global__ void c64_to_xm_kernel(const float2* __restrict__ in, float* __restric
     const int m = m0 + j, k = k0 + threadIdx.x;
     if (m < M && k < Kp) {
       const long long base = ((long long)m * RS + (long long)(b * 2) * Cp + c) * Kp + k;
-      xm[base] = (k < K) ? tr[threadIdx.x][j] : 0.f;
-      xm[base + (long long)Cp * Kp] = (k < K) ? ti[threadIdx.x][j] : 0.f;
+      xm[base] = (k < K) ? tf32_rn(tr[threadIdx.x][j]) : 0.f;
+      xm[base + (long long)Cp * Kp] = (k < K) ? tf32_rn(ti[threadIdx.x][j]) : 0.f;
     }
   }
 }
@@ -133,8 +134,8 @@ __global__ void pack_weight_kernel(const float2* __restrict__ w, float* __restri
     const int l = l0 + j, i = i0 + threadIdx.x;
     if (l < L && i < Cinp) {
       const long long base = (((long long)l * 2) * Coutp + o) * Cinp + i;
-      wp[base] = (i < Cin) ? tr[threadIdx.x][j] : 0.f;
-      wp[base + (long long)Coutp * Cinp] = (i < Cin) ? ti[threadIdx.x][j] : 0.f;
+      wp[base] = (i < Cin) ? tf32_rn(tr[threadIdx.x][j]) : 0.f;
+      wp[base + (long long)Coutp * Cinp] = (i < Cin) ? tf32_rn(ti[threadIdx.x][j]) : 0.f;
     }
   }
 }

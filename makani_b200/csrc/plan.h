@@ -15,17 +15,18 @@ namespace sfno {
 
 int sp_mhi(int l_local, int l_offset, int m_offset, int M_local);
 
-int legendre_analysis(const sfno_plan* plan, const float* xm, int B, int C, float* sp, cudaStream_t stream);
+int legendre_analysis(const sfno_plan* plan, const float* xm, int B, int C, float* sp, int round_out,
+                      cudaStream_t stream);
 int legendre_synthesis(const sfno_plan* plan, const float* sp, int B, int C, float* xm, cudaStream_t stream);
 int dhconv_fwd(const float* sp_in, const float* wp, float* sp_out, int B, int Cin, int Cout, int L, int M,
-               int l_offset, int m_offset, cudaStream_t stream);
+               int l_offset, int m_offset, int round_out, cudaStream_t stream);
 int dhconv_bwd_x(const float* gsp_out, const float* wp, float* gsp_in, int B, int Cin, int Cout, int L, int M,
-                 int l_offset, int m_offset, cudaStream_t stream);
+                 int l_offset, int m_offset, int round_out, cudaStream_t stream);
 int dhconv_bwd_w(const float* sp_in, const float* gsp_out, float* gwp, int B, int Cin, int Cout, int L, int M,
                  int l_offset, int m_offset, cudaStream_t stream);
 
 int dft_fwd(const void* x, int x_dtype, int B, int C, int nlat, int nlon, int mmax, const float* mscale,
-            float* xm, cudaStream_t stream);
+            float* xm, int round_out, cudaStream_t stream);
 int dft_inv(const float* xm, int B, int C, int nlat, int nlon, int mmax, int m_valid, const float* mscale,
             void* y, int y_dtype, cudaStream_t stream);
 

@@ -109,14 +109,15 @@ def rfft_adjoint_scale(nlon: int, mmax: int) -> torch.Tensor:
     return s * (2.0 * math.pi / nlon)
 
 
-def dft_fwd(x: torch.Tensor, mmax: int, mscale: torch.Tensor) -> torch.Tensor:
-    """x [B, C, nlat, nlon] (f32/bf16/f16, contiguous) -> XM."""
+def dft_fwd(x: torch.Tensor, mmax: int, mscale: torch.Tensor, round_tf32: bool = True) -> torch.Tensor:
+    """x [B, C, nlat, nlon] (f32/bf16/f16, contiguous) -> XM.  XM always feeds the TF32 Legendre contraction,
+    so by default its values are stored round-to-nearest TF32 (see tf32_rn in csrc/common.cuh)."""
     _need_cuda(x, "x")
     B, Cn, K, W = x.shape
     x = x.contiguous()
     xm = torch.empty(xm_elems(K, mmax, B, Cn), dtype=torch.float32, device=x.device)
     _ext.check(_ext.load().sfno_dft_fwd(_ptr(x), dtype_code(x.dtype), B, Cn, K, W, mmax, _ptr(mscale), _ptr(xm),
-                                        _stream()), "sfno_dft_fwd")
+                                        int(round_tf32), _stream()), "sfno_dft_fwd")
     return xm
 
 
@@ -130,9 +131,10 @@ def dft_inv(xm: torch.Tensor, B: int, Cn: int, nlat: int, nlon: int, mmax: int, 
 
 
 # ------------------------------------------------------------------------------------------ Legendre
-def legendre_analysis(plan: Plan, xm: torch.Tensor, B: int, Cn: int) -> torch.Tensor:
+def legendre_analysis(plan: Plan, xm: torch.Tensor, B: int, Cn: int, round_tf32: bool = False) -> torch.Tensor:
+    """round_tf32: the result feeds another TF32 contraction (store round-to-nearest TF32 values)."""
     sp = torch.empty(sp_elems(plan.lmax, plan.mmax, B, Cn), dtype=torch.float32, device=xm.device)
-    _ext.check(_ext.load().sfno_legendre_analysis(plan.handle, _ptr(xm), B, Cn, _ptr(sp), _stream()),
+    _ext.check(_ext.load().sfno_legendre_analysis(plan.handle, _ptr(xm), B, Cn, _ptr(sp), int(round_tf32), _stream()),
                "sfno_legendre_analysis")
     return sp
 
@@ -209,17 +211,17 @@ def unpack_wgrad(gwp: torch.Tensor, Cin, Cout, L) -> torch.Tensor:
     return gw
 
 
-def dhconv_fwd(sp_in, wp, B, Cin, Cout, lmax, mmax, l_offset=0, m_offset=0) -> torch.Tensor:
+def dhconv_fwd(sp_in, wp, B, Cin, Cout, lmax, mmax, l_offset=0, m_offset=0, round_tf32=False) -> torch.Tensor:
     sp_out = torch.empty(sp_elems(lmax, mmax, B, Cout), dtype=torch.float32, device=sp_in.device)
     _ext.check(_ext.load().sfno_dhconv_fwd(_ptr(sp_in), _ptr(wp), _ptr(sp_out), B, Cin, Cout, lmax, mmax,
-                                           l_offset, m_offset, _stream()), "sfno_dhconv_fwd")
+                                           l_offset, m_offset, int(round_tf32), _stream()), "sfno_dhconv_fwd")
     return sp_out
 
 
-def dhconv_bwd_x(gsp_out, wp, B, Cin, Cout, lmax, mmax, l_offset=0, m_offset=0) -> torch.Tensor:
+def dhconv_bwd_x(gsp_out, wp, B, Cin, Cout, lmax, mmax, l_offset=0, m_offset=0, round_tf32=False) -> torch.Tensor:
     gsp_in = torch.empty(sp_elems(lmax, mmax, B, Cin), dtype=torch.float32, device=gsp_out.device)
     _ext.check(_ext.load().sfno_dhconv_bwd_x(_ptr(gsp_out), _ptr(wp), _ptr(gsp_in), B, Cin, Cout, lmax, mmax,
-                                             l_offset, m_offset, _stream()), "sfno_dhconv_bwd_x")
+                                             l_offset, m_offset, int(round_tf32), _stream()), "sfno_dhconv_bwd_x")
     return gsp_in
 
 

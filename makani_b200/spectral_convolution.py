@@ -39,7 +39,7 @@ class _SpectralConvFunction(torch.autograd.Function):
         pf, pi = fwd._plan(dev), inv._plan(dev)
 
         xm = ops.dft_fwd(x, M, fwd._scale(dev, "fwd"))
-        sp = ops.legendre_analysis(pf, xm, B, Cin)
+        sp = ops.legendre_analysis(pf, xm, B, Cin, round_tf32=True)
         del xm
         residual = None
         if mod.scale_residual:
@@ -48,7 +48,7 @@ class _SpectralConvFunction(torch.autograd.Function):
             del rxm
         if mod.operator_type == "dhconv":
             wp = mod._packed_weight(weight)
-            sp2 = ops.dhconv_fwd(sp, wp, B, Cin, Cout, L, M)
+            sp2 = ops.dhconv_fwd(sp, wp, B, Cin, Cout, L, M, round_tf32=True)
         else:
             wp = None
             sp2 = ops.diag_fwd(sp, weight, B, Cin, Cout, L, M)
@@ -79,13 +79,13 @@ class _SpectralConvFunction(torch.autograd.Function):
         adj = inv._scale(dev, "irfft_adj")
 
         gxm2 = ops.dft_fwd(gy.contiguous(), M, adj)
-        gsp2 = ops.legendre_analysis(pi, gxm2, B, Cout)
+        gsp2 = ops.legendre_analysis(pi, gxm2, B, Cout, round_tf32=True)
         del gxm2
         gw = None
         if mod.operator_type == "dhconv":
             if ctx.needs_input_grad[1]:
                 gw = ops.unpack_wgrad(ops.dhconv_bwd_w(sp, gsp2, B, Cin, Cout, L, M), Cin, Cout, L)
-            gsp = ops.dhconv_bwd_x(gsp2, wsaved, B, Cin, Cout, L, M) if ctx.needs_input_grad[0] else None
+            gsp = ops.dhconv_bwd_x(gsp2, wsaved, B, Cin, Cout, L, M, round_tf32=True) if ctx.needs_input_grad[0] else None
         else:
             if ctx.needs_input_grad[1]:
                 gw = ops.diag_bwd_w(sp, gsp2, B, Cin, Cout, L, M)
@@ -95,7 +95,7 @@ class _SpectralConvFunction(torch.autograd.Function):
         if ctx.needs_input_grad[0]:
             if ctx.has_residual and gres is not None:
                 grxm = ops.dft_fwd(gres.contiguous(), M, adj)
-                gsp = gsp + ops.legendre_analysis(pi, grxm, B, Cin)     # both zero outside the defined region
+                gsp = gsp + ops.legendre_analysis(pi, grxm, B, Cin, round_tf32=True)     # both zero outside the defined region
                 del grxm
             gxm = ops.legendre_synthesis(pf, gsp, B, Cin)
             gx = ops.dft_inv(gxm, B, Cin, fwd.nlat, fwd.nlon, M, fwd._scale(dev, "rfft_adj"), ctx.in_dtype)

@@ -70,3 +70,11 @@ def rel_err(a, b):
     a = a.double() if not a.is_complex() else a.to(torch.complex128)
     b = b.to(a.dtype)
     return float((a - b).norm() / b.norm().clamp_min(1e-300))
+
+
+def tf32_rn(t):
+    """Round-to-nearest (ties away) to TF32, bit-exact with cvt.rna.tf32.f32 for finite values."""
+    if t.is_complex():
+        return torch.complex(tf32_rn(t.real.contiguous()), tf32_rn(t.imag.contiguous()))
+    u = t.contiguous().view(torch.int32)
+    return ((u + 0x1000) & ~0x1FFF).view(torch.float32)

@@ -11,7 +11,7 @@ import os
 import pytest
 import torch
 
-from layouts import rel_err, rup, sp_decode, sp_encode, tri_mask, wp_decode, xm_decode, xm_encode
+from layouts import rel_err, rup, sp_decode, sp_encode, tf32_rn, tri_mask, wp_decode, xm_decode, xm_encode
 
 pytestmark = pytest.mark.gpu
 
@@ -48,11 +48,14 @@ def test_dft_fwd(ops, B, C, K, W, M, dtype):
     torch.manual_seed(0)
     x = torch.randn(B, C, K, W, device=_dev()).to(dtype)
     mscale = (torch.rand(W // 2 + 1, device=_dev()) + 0.5)
-    xm = ops.dft_fwd(x, M, mscale)
+    xm = ops.dft_fwd(x, M, mscale, round_tf32=False)
     got = xm_decode(xm, B, C, K, M).cpu()
     ref = _rfft_ref(x.double().cpu(), M, mscale[:M].double().cpu())
     assert torch.isfinite(torch.view_as_real(got)).all()
     assert rel_err(got, ref) < TOL_FP32, rel_err(got, ref)
+    # default: values pre-rounded to TF32 for the Legendre GEMM - exactly the RN rounding of the above
+    got_r = xm_decode(ops.dft_fwd(x, M, mscale), B, C, K, M).cpu()
+    assert torch.equal(got_r, tf32_rn(got))
 
 
 @pytest.mark.parametrize("B,C,K,W,M,dtype", [
@@ -143,8 +146,8 @@ def test_dhconv(ops, B, Cin, Cout, L, M):
     w64 = w.cpu().to(torch.complex128)
 
     wp = ops.pack_weight(w)
-    assert rel_err(wp_decode(wp, Cin, Cout, L).cpu(), w64) == 0.0
-    assert rel_err(ops.unpack_wgrad(wp, Cin, Cout, L).cpu(), w64) == 0.0
+    assert torch.equal(wp_decode(wp, Cin, Cout, L), tf32_rn(w))            # packed copy is TF32-rounded
+    assert torch.equal(ops.unpack_wgrad(wp, Cin, Cout, L), tf32_rn(w))
 
     y = sp_decode(ops.dhconv_fwd(sp_encode(x), wp, B, Cin, Cout, L, M), B, Cout, L, M).cpu()
     ref = torch.einsum("bixy,iox->boxy", x64, w64)
@@ -180,13 +183,14 @@ def test_diagonal(ops, B, Cin, Cout, L, M):
 def test_layout_roundtrips(ops, B, C, L, M):
     torch.manual_seed(8)
     c = torch.randn(B, C, L, M, dtype=torch.complex64, device=_dev())
+    cr = tf32_rn(c)                                        # conversions INTO the GEMM layouts round to TF32
     sp = ops.c64_to_sp(c)
-    assert torch.equal(sp_decode(sp, B, C, L, M), c * tri_mask(L, M, c.device))
-    assert torch.equal(ops.sp_to_c64(sp, B, C, L, M), c * tri_mask(L, M, c.device))
-    assert torch.equal(ops.sp_to_c64(sp_encode(c), B, C, L, M), c * tri_mask(L, M, c.device))
+    assert torch.equal(sp_decode(sp, B, C, L, M), cr * tri_mask(L, M, c.device))
+    assert torch.equal(ops.sp_to_c64(sp, B, C, L, M), cr * tri_mask(L, M, c.device))
+    assert torch.equal(ops.sp_to_c64(sp_encode(c), B, C, L, M), c * tri_mask(L, M, c.device))   # out of them: exact
     xm = ops.c64_to_xm(c)
-    assert torch.equal(xm_decode(xm, B, C, L, M), c)
-    assert torch.equal(ops.xm_to_c64(xm, B, C, L, M), c)
+    assert torch.equal(xm_decode(xm, B, C, L, M), cr)
+    assert torch.equal(ops.xm_to_c64(xm, B, C, L, M), cr)
     assert torch.equal(ops.xm_to_c64(xm_encode(c), B, C, L, M), c)
 
 

@@ -20,6 +20,7 @@
 #include <mutex>
 #include <vector>
 #include <cmath>
+#include <type_traits>
 
 namespace sfno {
 
@@ -226,15 +227,52 @@ __device__ __forceinline__ void lane_butterfly_twiddles(fl::cf (&bf)[4]) {
   }
 }
 
+constexpr int kStagePitch = 20;   // floats per (m, re/im) staging row: 16 latitudes + 4 pad (16 B aligned, skews banks)
+constexpr int kStageRows = 2 * 241;
+
 template <int R, typename T>
 struct FftSmem {
   static constexpr int W = 480 * R;
   static constexpr int kRowStride = W + 16 / (int)sizeof(T);         // elements; keeps 16 B alignment, skews banks
   static constexpr int kRawBytes = kRows * kRowStride * (int)sizeof(T);
-  static constexpr int kStageBytes = 2 * 241 * (kRows + 1) * 4;
+  static constexpr int kStageBytes = kStageRows * kStagePitch * 4;
   static constexpr int kBufBytes = ((kRawBytes > kStageBytes ? kRawBytes : kStageBytes) + 15) & ~15;
-  static constexpr int kBytes = kBufBytes + kTwCount * 8 + 241 * 4 + 16;
+  static constexpr int kBytes = kBufBytes + kTwCount * 8 + 244 * 4 + kRows * 8 + 16;
 };
+
+// packed complex sample z_r[n] = (x[2 R n + r], x[2 R n + R + r]) of a row held in shared memory
+template <int R, typename T>
+__device__ __forceinline__ fl::cf load_pair(const T* row, int n, int r) {
+  if constexpr (R == 1) {
+    if constexpr (sizeof(T) == 4) {
+      const float2 v = *reinterpret_cast<const float2*>(row + 2 * n);
+      return fl::mk(v.x, v.y);
+    } else if constexpr (std::is_same<T, __nv_bfloat16>::value) {
+      const float2 v = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(row + 2 * n));
+      return fl::mk(v.x, v.y);
+    } else {
+      const float2 v = __half22float2(*reinterpret_cast<const __half2*>(row + 2 * n));
+      return fl::mk(v.x, v.y);
+    }
+  } else {
+    return fl::mk(to_f32<T>(row[2 * R * n + r]), to_f32<T>(row[2 * R * n + R + r]));
+  }
+}
+template <int R, typename T>
+__device__ __forceinline__ void store_pair(T* row, int n, int r, fl::cf z) {
+  if constexpr (R == 1) {
+    if constexpr (sizeof(T) == 4) {
+      *reinterpret_cast<float2*>(row + 2 * n) = make_float2(z.x, z.y);
+    } else if constexpr (std::is_same<T, __nv_bfloat16>::value) {
+      *reinterpret_cast<__nv_bfloat162*>(row + 2 * n) = __floats2bfloat162_rn(z.x, z.y);
+    } else {
+      *reinterpret_cast<__half2*>(row + 2 * n) = __floats2half2_rn(z.x, z.y);
+    }
+  } else {
+    row[2 * R * n + r] = from_f32<T>(z.x);
+    row[2 * R * n + R + r] = from_f32<T>(z.y);
+  }
+}
 
 // forward: x rows -> XM.  256 threads = 16 rows x 16 lanes; persistent over tiles of 16 flat positions.
 template <int R, typename T>
@@ -248,11 +286,14 @@ dft_fwd_fft480_kernel(const T* __restrict__ x, float* __restrict__ xm, const fl:
   float* stage = reinterpret_cast<float*>(smraw);                     // aliases raw (used after the FFT)
   fl::cf* tw = reinterpret_cast<fl::cf*>(smraw + S::kBufBytes);
   float* msc = reinterpret_cast<float*>(tw + kTwCount);
+  long long* rowoff = reinterpret_cast<long long*>(msc + 244);
 
   for (int j = threadIdx.x; j < kTwCount; j += blockDim.x) tw[j] = tables[j];
   for (int j = threadIdx.x; j < 241; j += blockDim.x) msc[j] = j < M ? mscale[j] : 0.f;
   fl::cf bf[4];
   lane_butterfly_twiddles(bf);
+  const int lane = threadIdx.x & 15;
+  const fl::LaneConsts lc = fl::make_lane_consts(lane, bf);
 
   const int Cp = (C + 3) & ~3;
   const long long RS = 2LL * B * Cp;
@@ -260,56 +301,58 @@ dft_fwd_fft480_kernel(const T* __restrict__ x, float* __restrict__ xm, const fl:
   const int tiles_per_b = (flat + kRows - 1) / kRows;
   const int ntiles = tiles_per_b * B;
   const int r = threadIdx.x >> 4;
-  const int lane = threadIdx.x & 15;
   const int k2 = fl::bitrev4(lane);
   constexpr int kChunks = W * (int)sizeof(T) / 16;                    // 16-byte chunks per row
   DeviceWarp16 warp;
 
   for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     const int b = tile / tiles_per_b;
-    const int f0 = (tile % tiles_per_b) * kRows;
+    const int f0 = (tile - b * tiles_per_b) * kRows;
+    if (threadIdx.x < kRows) {
+      const int f = f0 + threadIdx.x;
+      const int c = f / Kp, lat = f - c * Kp;
+      rowoff[threadIdx.x] = (f < flat && lat < K) ? ((long long)(b * C + c) * K + lat) * W : -1;
+    }
+    __syncthreads();
     // ---- 1. rows -> smem (coalesced 16 B async copies); padded / out-of-range rows are zero filled
     for (int idx = threadIdx.x; idx < kRows * kChunks; idx += blockDim.x) {
-      const int rr = idx / kChunks, ch = idx % kChunks;
-      const int f = f0 + rr;
-      const int c = f / Kp, lat = f % Kp;
+      const int rr = idx / kChunks, ch = idx - rr * kChunks;
       uint8_t* dst = reinterpret_cast<uint8_t*>(raw + rr * S::kRowStride) + ch * 16;
-      if (f < flat && lat < K) {
-        const uint8_t* src = reinterpret_cast<const uint8_t*>(x + ((long long)(b * C + c) * K + lat) * W) + ch * 16;
-        cp_async16(dst, src);
-      } else {
-        *reinterpret_cast<uint4*>(dst) = make_uint4(0, 0, 0, 0);
-      }
+      const long long off = rowoff[rr];
+      if (off >= 0) cp_async16(dst, reinterpret_cast<const uint8_t*>(x + off) + ch * 16);
+      else *reinterpret_cast<uint4*>(dst) = make_uint4(0, 0, 0, 0);
     }
     cp_async_wait_all();
     __syncthreads();
     // ---- 2. per-row FFT in registers / shuffles
     fl::cf X[15], x240;
     const T* myrow = raw + r * S::kRowStride;
-    fl::rfft_row_fwd<R>(warp, [&](int i) { return to_f32<T>(myrow[i]); }, X, x240, tw, tw + 240, tw + 481, bf);
+    fl::rfft_row_fwd<R>(warp, [&](int n, int rr) { return load_pair<R, T>(myrow, n, rr); }, X, x240, tw, tw + 240,
+                        tw + 481, lc);
     __syncthreads();
     // ---- 3. transpose through smem: stage[reim][m][row]
 #pragma unroll
     for (int k1 = 0; k1 < 15; ++k1) {
       const int m = k1 + 15 * k2;
-      if (m < M) {
-        const float s = msc[m];
-        stage[(0 * 241 + m) * (kRows + 1) + r] = X[k1].x * s;
-        stage[(1 * 241 + m) * (kRows + 1) + r] = X[k1].y * s;
-      }
+      const float sc = msc[m];
+      stage[m * kStagePitch + r] = X[k1].x * sc;
+      stage[(241 + m) * kStagePitch + r] = X[k1].y * sc;
     }
-    if (lane == 0 && 240 < M) {
-      const float s = msc[240];
-      stage[(0 * 241 + 240) * (kRows + 1) + r] = x240.x * s;
-      stage[(1 * 241 + 240) * (kRows + 1) + r] = x240.y * s;
+    if (lane == 0) {
+      const float sc = msc[240];
+      stage[240 * kStagePitch + r] = x240.x * sc;
+      stage[(241 + 240) * kStagePitch + r] = x240.y * sc;
     }
     __syncthreads();
-    for (int idx = threadIdx.x; idx < 2 * M * kRows; idx += blockDim.x) {
-      const int rr = idx % kRows, pm = idx / kRows;
-      const int reim = pm / M, m = pm % M;
-      if (f0 + rr < flat) {
-        const float v = stage[(reim * 241 + m) * (kRows + 1) + rr];
-        xm[((long long)m * RS + (long long)(b * 2 + reim) * Cp) * Kp + f0 + rr] = round_out ? tf32_rn(v) : v;
+    const long long obase = ((long long)(b * 2) * Cp) * Kp + f0;
+    for (int idx = threadIdx.x; idx < kStageRows * 4; idx += blockDim.x) {
+      const int pm = idx >> 2, q = idx & 3;
+      const int reim = pm >= 241 ? 1 : 0;
+      const int m = pm - reim * 241;
+      if (m < M && f0 + 4 * q < flat) {
+        float4 v = *reinterpret_cast<const float4*>(stage + pm * kStagePitch + 4 * q);
+        if (round_out) { v.x = tf32_rn(v.x); v.y = tf32_rn(v.y); v.z = tf32_rn(v.z); v.w = tf32_rn(v.w); }
+        *reinterpret_cast<float4*>(xm + ((long long)m * RS + (long long)reim * Cp) * Kp + obase + 4 * q) = v;
       }
     }
     __syncthreads();
@@ -328,11 +371,14 @@ dft_inv_fft480_kernel(const float* __restrict__ xm, T* __restrict__ y, const fl:
   float* stage = reinterpret_cast<float*>(smraw);
   fl::cf* tw = reinterpret_cast<fl::cf*>(smraw + S::kBufBytes);
   float* msc = reinterpret_cast<float*>(tw + kTwCount);
+  long long* rowoff = reinterpret_cast<long long*>(msc + 244);
 
   for (int j = threadIdx.x; j < kTwCount; j += blockDim.x) tw[j] = tables[j];
   for (int j = threadIdx.x; j < 241; j += blockDim.x) msc[j] = j < m_valid ? mscale[j] : 0.f;
   fl::cf bf[4];
   lane_butterfly_twiddles(bf);
+  const int lane = threadIdx.x & 15;
+  const fl::LaneConsts lc = fl::make_lane_consts(lane, bf);
 
   const int Cp = (C + 3) & ~3;
   const long long RS = 2LL * B * Cp;
@@ -340,45 +386,53 @@ dft_inv_fft480_kernel(const float* __restrict__ xm, T* __restrict__ y, const fl:
   const int tiles_per_b = (flat + kRows - 1) / kRows;
   const int ntiles = tiles_per_b * B;
   const int r = threadIdx.x >> 4;
-  const int lane = threadIdx.x & 15;
   const int k2 = fl::bitrev4(lane);
   constexpr int kChunks = W * (int)sizeof(T) / 16;
   DeviceWarp16 warp;
-  __syncthreads();
 
   for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     const int b = tile / tiles_per_b;
-    const int f0 = (tile % tiles_per_b) * kRows;
-    // ---- 1. XM -> stage[reim][m][row] (16 consecutive floats per (m, reim)), scaled
-    for (int idx = threadIdx.x; idx < 2 * 241 * kRows; idx += blockDim.x) {
-      const int rr = idx % kRows, pm = idx / kRows;
-      const int reim = pm / 241, m = pm % 241;
-      float v = 0.f;
-      if (m < m_valid && f0 + rr < flat)
-        v = xm[((long long)m * RS + (long long)(b * 2 + reim) * Cp) * Kp + f0 + rr] * msc[m];
-      stage[(reim * 241 + m) * (kRows + 1) + rr] = v;
+    const int f0 = (tile - b * tiles_per_b) * kRows;
+    if (threadIdx.x < kRows) {
+      const int f = f0 + threadIdx.x;
+      const int c = f / Kp, lat = f - c * Kp;
+      rowoff[threadIdx.x] = (f < flat && lat < K) ? ((long long)(b * C + c) * K + lat) * W : -1;
     }
+    // ---- 1. XM -> stage[reim][m][16 latitudes]: 16 B async copies, all in flight at once
+    const long long ibase = ((long long)(b * 2) * Cp) * Kp + f0;
+    for (int idx = threadIdx.x; idx < kStageRows * 4; idx += blockDim.x) {
+      const int pm = idx >> 2, q = idx & 3;
+      const int reim = pm >= 241 ? 1 : 0;
+      const int m = pm - reim * 241;
+      float* dst = stage + pm * kStagePitch + 4 * q;
+      if (m < m_valid && f0 + 4 * q < flat)
+        cp_async16(dst, xm + ((long long)m * RS + (long long)reim * Cp) * Kp + ibase + 4 * q);
+      else
+        *reinterpret_cast<float4*>(dst) = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    cp_async_wait_all();
     __syncthreads();
-    // ---- 2. gather this lane's bins into registers, then the stage buffer may be overwritten
+    // ---- 2. gather this lane's bins (scaled) into registers, then the stage buffer may be overwritten
     fl::cf H[15], HP[15];
 #pragma unroll
     for (int k1 = 0; k1 < 15; ++k1) {
       const int k = k1 + 15 * k2, kp = 240 - k;
-      H[k1] = fl::mk(stage[(0 * 241 + k) * (kRows + 1) + r], stage[(1 * 241 + k) * (kRows + 1) + r]);
-      HP[k1] = fl::mk(stage[(0 * 241 + kp) * (kRows + 1) + r], stage[(1 * 241 + kp) * (kRows + 1) + r]);
+      const float s0 = msc[k], s1 = msc[kp];
+      H[k1] = fl::mk(stage[k * kStagePitch + r] * s0, stage[(241 + k) * kStagePitch + r] * s0);
+      HP[k1] = fl::mk(stage[kp * kStagePitch + r] * s1, stage[(241 + kp) * kStagePitch + r] * s1);
     }
     __syncthreads();
     T* myrow = raw + r * S::kRowStride;
-    fl::irfft_row<R>(warp, H, HP, [&](int i, float v) { myrow[i] = from_f32<T>(v); }, tw, tw + 240, tw + 481, bf);
+    fl::irfft_row<R>(warp, H, HP, [&](int n, int rr, fl::cf z) { store_pair<R, T>(myrow, n, rr, z); }, tw, tw + 240,
+                     tw + 481, lc);
     __syncthreads();
     // ---- 3. rows -> global, 16 B vectors
     for (int idx = threadIdx.x; idx < kRows * kChunks; idx += blockDim.x) {
-      const int rr = idx / kChunks, ch = idx % kChunks;
-      const int f = f0 + rr;
-      const int c = f / Kp, lat = f % Kp;
-      if (f < flat && lat < K) {
+      const int rr = idx / kChunks, ch = idx - rr * kChunks;
+      const long long off = rowoff[rr];
+      if (off >= 0) {
         const uint4 v = *reinterpret_cast<const uint4*>(reinterpret_cast<const uint8_t*>(raw + rr * S::kRowStride) + ch * 16);
-        *reinterpret_cast<uint4*>(reinterpret_cast<uint8_t*>(y + ((long long)(b * C + c) * K + lat) * W) + ch * 16) = v;
+        *reinterpret_cast<uint4*>(reinterpret_cast<uint8_t*>(y + off) + ch * 16) = v;
       }
     }
     __syncthreads();

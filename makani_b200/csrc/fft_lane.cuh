@@ -105,37 +105,59 @@ FL_HD void dft15(cf (&v)[15]) {
 //   tw480[k]         = e^{-2 pi i k / 480}          k in [0,241)
 //   bf[s]            = e^{-2 pi i (lane & (d-1)) / (2d)},  d = 1 << s   (per lane, 4 entries)
 
+// Per-lane butterfly constants for the 16-lane radix-2 stages (d = 1 << s):
+//   sgn[s] = -1 on "upper" lanes (lane & d), +1 on lower lanes
+//   fw[s]  = forward twiddle e^{-2 pi i (lane & (d-1)) / (2d)} on upper lanes, 1 on lower lanes
+// so that both butterfly outputs are  (t + sgn*v) * fw  (forward, DIF)  and  t' + sgn*(v * conj(fw))  (inverse, DIT)
+// without divergent code.  Stage 0 (d = 1) always has a unit twiddle and skips the multiply.
+struct LaneConsts {
+  float sgn[4];
+  cf fw[4];
+};
+
+FL_HD LaneConsts make_lane_consts(int lane16, const cf (&bf)[4]) {
+  LaneConsts c;
+#pragma unroll
+  for (int s = 0; s < 4; ++s) {
+    const bool upper = (lane16 & (1 << s)) != 0;
+    c.sgn[s] = upper ? -1.f : 1.f;
+    c.fw[s] = upper ? bf[s] : mk(1.f, 0.f);
+  }
+  return c;
+}
+
 // forward complex FFT-240 across 16 lanes.  in: v[a] = z[16 a + lane];  out: v[k1] = Z[k1 + 15 bitrev4(lane)]
 template <class Warp>
-FL_HD void fft240_fwd(Warp& w, cf (&v)[15], const cf* tw240_lane, const cf (&bf)[4]) {
+FL_HD void fft240_fwd(Warp& w, cf (&v)[15], const cf* tw240_lane, const LaneConsts& lc) {
   dft15<-1>(v);
 #pragma unroll
   for (int k1 = 1; k1 < 15; ++k1) v[k1] = cmul(v[k1], tw240_lane[k1]);
 #pragma unroll
   for (int s = 3; s >= 0; --s) {
     const int d = 1 << s;
-    const bool upper = (w.lane16() & d) != 0;
+    const float sg = lc.sgn[s];
 #pragma unroll
     for (int k1 = 0; k1 < 15; ++k1) {
       const cf t = mk(w.shfl_xor(v[k1].x, d), w.shfl_xor(v[k1].y, d));
-      v[k1] = upper ? cmul(csub(t, v[k1]), bf[s]) : cadd(v[k1], t);
+      const cf u = mk(t.x + sg * v[k1].x, t.y + sg * v[k1].y);       // lower: v + t ; upper: t - v
+      v[k1] = (s == 0) ? u : cmul(u, lc.fw[s]);
     }
   }
 }
 
 // inverse (unnormalised, e^{+}) complex FFT-240.  in: v[k1] = V[k1 + 15 bitrev4(lane)];  out: v[a] = z[16 a + lane]
 template <class Warp>
-FL_HD void fft240_inv(Warp& w, cf (&v)[15], const cf* tw240_lane, const cf (&bf)[4]) {
+FL_HD void fft240_inv(Warp& w, cf (&v)[15], const cf* tw240_lane, const LaneConsts& lc) {
 #pragma unroll
   for (int s = 0; s < 4; ++s) {
     const int d = 1 << s;
-    const bool upper = (w.lane16() & d) != 0;
-    const cf wc = cconj(bf[s]);
+    const float sg = lc.sgn[s];
+    const cf wc = cconj(lc.fw[s]);
 #pragma unroll
     for (int k1 = 0; k1 < 15; ++k1) {
-      const cf val = upper ? cmul(v[k1], wc) : v[k1];
+      const cf val = (s == 0) ? v[k1] : cmul(v[k1], wc);
       const cf t = mk(w.shfl_xor(val.x, d), w.shfl_xor(val.y, d));
-      v[k1] = upper ? csub(t, val) : cadd(val, t);
+      v[k1] = mk(t.x + sg * val.x, t.y + sg * val.y);                // lower: val + t ; upper: t - val
     }
   }
 #pragma unroll
@@ -183,10 +205,11 @@ FL_HD cf irfft480_pre(cf h, cf hp, cf tw480_k) {
 //   forward, R = 3: x_r[q] = x[3q + r] (three length-480 real FFTs), X[m] = sum_r w1440^(m r) X_r[m], m <= 240
 //   inverse, R = 3: x[3q + r] = irfft480( X[m] conj(w1440)^(m r) ), with bin 240 doubled (it is not Nyquist)
 //   tw1440[m] = e^{-2 pi i m / 1440}, m in [0, 241)
-// `load(i)` returns sample i of the row; `store(i, v)` writes sample i.
-template <int R, class Warp, class Load>
-FL_HD void rfft_row_fwd(Warp& w, Load load, cf (&X)[15], cf& x240, const cf* tw240, const cf* tw480,
-                        const cf* tw1440, const cf (&bf)[4]) {
+// `loadz(n, r)` returns the packed complex sample (x[2 R n + r], x[2 R n + R + r]) of the row;
+// `storez(n, r, z)` writes it back.
+template <int R, class Warp, class LoadZ>
+FL_HD void rfft_row_fwd(Warp& w, LoadZ loadz, cf (&X)[15], cf& x240, const cf* tw240, const cf* tw480,
+                        const cf* tw1440, const LaneConsts& lc) {
   const int b = w.lane16();
   const int k2 = bitrev4(b);
 #pragma unroll
@@ -196,11 +219,8 @@ FL_HD void rfft_row_fwd(Warp& w, Load load, cf (&X)[15], cf& x240, const cf* tw2
   for (int r = 0; r < R; ++r) {
     cf v[15];
 #pragma unroll
-    for (int a = 0; a < 15; ++a) {
-      const int n = 16 * a + b;
-      v[a] = mk(load(2 * R * n + r), load(2 * R * n + R + r));
-    }
-    fft240_fwd(w, v, tw240 + b * 15, bf);
+    for (int a = 0; a < 15; ++a) v[a] = loadz(16 * a + b, r);
+    fft240_fwd(w, v, tw240 + b * 15, lc);
     cf xr[15];
     float nyq;
     rfft480_post(w, v, xr, nyq, tw480);
@@ -223,9 +243,9 @@ FL_HD void rfft_row_fwd(Warp& w, Load load, cf (&X)[15], cf& x240, const cf* tw2
 }
 
 // H[k1] / HP[k1] hold the (already scaled) spectrum at bins k = k1 + 15 k2 and 240 - k (zero for bins not held).
-template <int R, class Warp, class Store>
-FL_HD void irfft_row(Warp& w, const cf (&H)[15], const cf (&HP)[15], Store store, const cf* tw240,
-                     const cf* tw480, const cf* tw1440, const cf (&bf)[4]) {
+template <int R, class Warp, class StoreZ>
+FL_HD void irfft_row(Warp& w, const cf (&H)[15], const cf (&HP)[15], StoreZ storez, const cf* tw240,
+                     const cf* tw480, const cf* tw1440, const LaneConsts& lc) {
   const int b = w.lane16();
   const int k2 = bitrev4(b);
 #pragma unroll
@@ -247,13 +267,9 @@ FL_HD void irfft_row(Warp& w, const cf (&H)[15], const cf (&HP)[15], Store store
       }
       v[k1] = irfft480_pre(h, hp, tw480[k]);
     }
-    fft240_inv(w, v, tw240 + b * 15, bf);
+    fft240_inv(w, v, tw240 + b * 15, lc);
 #pragma unroll
-    for (int a = 0; a < 15; ++a) {
-      const int n = 16 * a + b;
-      store(2 * R * n + r, v[a].x);
-      store(2 * R * n + R + r, v[a].y);
-    }
+    for (int a = 0; a < 15; ++a) storez(16 * a + b, r, v[a]);
   }
 }
 

@@ -77,7 +77,9 @@ static double run(bool verbose) {
           bf[s] = mk((float)cos(a), (float)sin(a));
         }
         cf Xl[15], x240;
-        rfft_row_fwd<R>(w, [&](int i) { return x[i]; }, Xl, x240, tw240.data(), tw480.data(), tw1440.data(), bf);
+        const LaneConsts lc = make_lane_consts(lane, bf);
+        rfft_row_fwd<R>(w, [&](int n, int r) { return mk(x[2 * R * n + r], x[2 * R * n + R + r]); }, Xl, x240,
+                        tw240.data(), tw480.data(), tw1440.data(), lc);
         int k2 = bitrev4(lane);
         for (int k1 = 0; k1 < 15; ++k1) X[k1 + 15 * k2] = {Xl[k1].x, Xl[k1].y};
         if (lane == 0) X[240] = {x240.x, x240.y};
@@ -122,7 +124,9 @@ static double run(bool verbose) {
           H[k1] = mk(S[k].real(), S[k].imag());
           HP[k1] = mk(S[240 - k].real(), S[240 - k].imag());
         }
-        irfft_row<R>(w, H, HP, [&](int i, float v) { y[i] = v; }, tw240.data(), tw480.data(), tw1440.data(), bf);
+        const LaneConsts lc = make_lane_consts(lane, bf);
+        irfft_row<R>(w, H, HP, [&](int n, int r, cf z) { y[2 * R * n + r] = z.x; y[2 * R * n + R + r] = z.y; },
+                     tw240.data(), tw480.data(), tw1440.data(), lc);
       });
     for (auto& t : th) t.join();
   }

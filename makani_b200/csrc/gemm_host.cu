@@ -72,9 +72,20 @@ int sp_mhi(int l_local, int l_offset, int m_offset, int M_local) {
 }
 
 static int upload_tiles(std::vector<GemmTile>& tiles, TileList* out) {
-  // longest-processing-time first: static round-robin over a cost-sorted list balances the triangular work
-  std::stable_sort(tiles.begin(), tiles.end(), [](const GemmTile& a, const GemmTile& b) {
-    return (long long)a.nkk * a.n_mma > (long long)b.nkk * b.n_mma;
+  // Longest-processing-time first: static round-robin over a cost-sorted list balances the triangular work.
+  // The cost of a tile is taken as the largest cost inside its batch index g, so that all tiles of one g
+  // (which share an operand: the table of order m, the weight of degree l) stay adjacent in the list and run
+  // at the same time on neighbouring CTAs - the shared operand is then read from HBM once and hits L2 after.
+  std::map<int, long long> gcost;
+  for (const GemmTile& t : tiles) {
+    long long c = (long long)t.nkk * t.n_mma;
+    auto it = gcost.find(t.g);
+    if (it == gcost.end() || it->second < c) gcost[t.g] = c;
+  }
+  std::stable_sort(tiles.begin(), tiles.end(), [&](const GemmTile& a, const GemmTile& b) {
+    const long long ca = gcost[a.g], cb = gcost[b.g];
+    if (ca != cb) return ca > cb;
+    return a.g > b.g;
   });
   out->count = (int)tiles.size();
   if (tiles.empty()) return 0;
@@ -114,6 +125,8 @@ template <int MODE>
 static int launch(const CUtensorMap& ma, const CUtensorMap& mb, const GemmArgs& args, cudaStream_t stream) {
   using Cfg = GemmCfg<MODE>;
   if (args.num_tiles == 0) return 0;
+  SFNO_CHECK(args.out_col_stride > 0 && args.out_col_stride < (1LL << 31) / 32,
+             "output column stride too large for the 32-bit epilogue addressing (reduce batch*channels)");
   static bool attr_set = false;
   if (!attr_set) {
     SFNO_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,

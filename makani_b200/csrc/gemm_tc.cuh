@@ -247,24 +247,40 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
       mbar_wait(&tmem_full[buf], acc_phase);
       tc_fence_after();
       const uint32_t tbase = tmem_base + buf * Cfg::kAccCols + ((uint32_t)(q * 32) << 16);
+      // Stores: lane = output row (contiguous in memory), one STG per column => 128 B per warp store.
+      // The column stride fits 32 bits (asserted on the host), so every address is one IMAD.WIDE off a
+      // per-chunk base pointer; full chunks take the unpredicated path.
+      const int cstride = (int)args.out_col_stride;
+      const int nvalid = tile.col_limit - tile.col0;
 #pragma unroll 1
       for (int p = 0; p < Cfg::kPlanes; ++p) {
-        float* op = obase + (p ? args.out_im_offset : 0);
+        float* op = obase + (p ? args.out_im_offset : 0) + (long long)tile.col0 * args.out_col_stride;
+        uint32_t v[32];
+        tmem_ld_32x32(tbase + p * 128, v);
 #pragma unroll 1
         for (int c = 0; c < tile.n_mma; c += 32) {
-          uint32_t v[32];
-          tmem_ld_32x32(tbase + p * 128 + c, v);
           tmem_ld_wait();
-          if (row_ok) {
+          float w[32];
+          if (args.round_out) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
-              const int col = tile.col0 + c + j;
-              if (col < tile.col_limit) {
-                const float val = __uint_as_float(v[j]);
-                op[(long long)col * args.out_col_stride] = args.round_out ? tf32_rn(val) : val;
-              }
+            for (int j = 0; j < 32; ++j) w[j] = tf32_rn(__uint_as_float(v[j]));
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) w[j] = __uint_as_float(v[j]);
+          }
+          if (c + 32 < tile.n_mma) tmem_ld_32x32(tbase + p * 128 + c + 32, v);   // prefetch the next chunk
+          if (row_ok) {
+            const int nv = nvalid - c;
+            if (nv >= 32) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) op[j * cstride] = w[j];
+            } else {
+#pragma unroll
+              for (int j = 0; j < 32; ++j)
+                if (j < nv) op[j * cstride] = w[j];
             }
           }
+          op += 32 * (long long)cstride;
         }
       }
       tc_fence_before();

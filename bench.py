@@ -81,6 +81,7 @@ def gpu_step(blocks, xs_dev, grads):
     for blk, x, (gy, gr) in zip(blocks, xs_dev, grads):
         x.grad = None
         blk.weight.grad = None
+        blk._wp_cache = None          # a training step follows an optimizer update: the packed weight copy is rebuilt
         y, res = blk(x)
         if gr is not None:
             torch.autograd.backward([y, res], [gy, gr])
@@ -313,8 +314,8 @@ def run_ours(args):
         for blk in blocks:
             blk.weight.register_post_accumulate_grad_hook(hook)
 
-    def step():
-        out = gpu_step(blocks, xs_dev, grads)
+    def step(xs=None):
+        out = gpu_step(blocks, xs_dev if xs is None else xs, grads)
         for w in pending:
             w.wait()
         pending.clear()
@@ -341,21 +342,45 @@ def run_ours(args):
     clocks = sampler.stop() if sampler else None
     launches = _ext.launch_count() - launches0
 
-    # ---- end-to-end timing: pinned host inputs -> device, step, checksum back to host, every step
-    def e2e_step():
-        for xd, xh in zip(xs_dev, xs_host):
-            xd.data.copy_(xh, non_blocking=True)
-        return step().cpu()
-    e2e_step()
+    # ---- end-to-end timing: pinned host inputs -> device, step, checksum back to host, every step.
+    # Two device input sets: while step i computes on one, the copy engine fills the other with the inputs of step
+    # i+1 (a data loader's prefetch); every step's host->device copy and device->host read are inside the timed region.
+    sets = [xs_dev, [x.detach().clone().requires_grad_(True) for x in xs_dev]]
+    copy_stream = torch.cuda.Stream()
+    ready = [torch.cuda.Event(), torch.cuda.Event()]
+    consumed = [torch.cuda.Event(), torch.cuda.Event()]
+
+    def enqueue_copy(k):
+        with torch.cuda.stream(copy_stream):
+            copy_stream.wait_event(consumed[k])
+            for xd, xh in zip(sets[k], xs_host):
+                xd.data.copy_(xh, non_blocking=True)
+            ready[k].record(copy_stream)
+
+    def e2e_step(i, last):
+        k = i & 1
+        torch.cuda.current_stream().wait_event(ready[k])
+        out = step(sets[k])
+        consumed[k].record()
+        if not last:
+            enqueue_copy(k ^ 1)
+        return out.cpu()
+
+    for k in range(2):
+        consumed[k].record()
+    enqueue_copy(0)
+    e2e_step(0, True)
     barrier()
     t0 = torch.cuda.Event(enable_timing=True)
     t1 = torch.cuda.Event(enable_timing=True)
     t0.record()
-    for _ in range(args.steps):
-        chk = e2e_step()
+    enqueue_copy(0)
+    for i in range(args.steps):
+        chk = e2e_step(i, i == args.steps - 1)
     t1.record()
     barrier()
     ms_e2e = t0.elapsed_time(t1)
+    del sets
     h2d = sum(x.numel() * x.element_size() for x in xs_host)
     d2h = chk.numel() * chk.element_size()
 
@@ -398,7 +423,8 @@ def run_ours(args):
             "config": {"workload": WORKLOAD, "per_gpu_batch": batch, "embed_dim": C_EMBED, "modes": [L_MODES, M_MODES],
                        "io_dtype": "bf16", "accumulate": "fp32", "parallelism": f"dp{world}",
                        "l2": "inputs (1.4 GB/step) and intermediates are far larger than the 126 MB L2",
-                       "includes": "fwd + dX + dW of all 8 blocks, weight repack; no optimizer update"},
+                       "includes": "fwd + dX + dW of all 8 blocks, weight repack every step; no optimizer update",
+                       "e2e": "pinned-host inputs copied every step on a copy stream, double buffered against compute"},
             "e2e": {"value": samples / (ms_e2e * 1e-3), "unit": "samples/s", "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e / args.steps},
             "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu, "kernels": top,

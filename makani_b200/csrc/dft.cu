@@ -13,6 +13,7 @@
 #include "common.cuh"
 #include "plan.h"
 #include "fft_lane.cuh"
+#include "fft_pass.cuh"
 
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
@@ -451,6 +452,10 @@ static int sm_count() {
   return n;
 }
 
+}  // namespace sfno
+#include "dft_p2.cuh"
+namespace sfno {
+
 template <int R, typename T>
 static int launch_fwd_fft(const void* x, int B, int C, int K, int Kp, int M, const float* mscale, float* xm,
                           int round_out, cudaStream_t stream) {
@@ -513,6 +518,16 @@ static int launch_inv_generic(const float* xm, int B, int C, int K, int Kp, int 
   return 0;
 }
 
+// SFNO_DFT_IMPL=lane selects the older 16-lane shuffle FFT kernels (kept for A/B measurements)
+static bool use_lane_fft() {
+  static int v = -1;
+  if (v < 0) {
+    const char* env = getenv("SFNO_DFT_IMPL");
+    v = (env && std::string(env) == "lane") ? 1 : 0;
+  }
+  return v == 1;
+}
+
 static bool use_fft480(int W, int M, const void* p) {
   const char* env = getenv("SFNO_FORCE_GENERIC_DFT");
   if (env && env[0] == '1') return false;
@@ -524,10 +539,13 @@ int dft_fwd(const void* x, int x_dtype, int B, int C, int nlat, int nlon, int mm
   SFNO_CHECK(mmax <= nlon / 2 + 1, "mmax exceeds nlon/2+1");
   const int Kp = round_up(nlat, 4);
   const bool fast = use_fft480(nlon, mmax, x);
+  const bool lane_fft = use_lane_fft();
 #define SFNO_DISPATCH_FWD(T)                                                                           \
   do {                                                                                                 \
-    if (fast && nlon == 480) return launch_fwd_fft<1, T>(x, B, C, nlat, Kp, mmax, mscale, xm, round_out, stream); \
-    if (fast && nlon == 1440) return launch_fwd_fft<3, T>(x, B, C, nlat, Kp, mmax, mscale, xm, round_out, stream);\
+    if (fast && lane_fft && nlon == 480) return launch_fwd_fft<1, T>(x, B, C, nlat, Kp, mmax, mscale, xm, round_out, stream); \
+    if (fast && lane_fft && nlon == 1440) return launch_fwd_fft<3, T>(x, B, C, nlat, Kp, mmax, mscale, xm, round_out, stream);\
+    if (fast && nlon == 480) return launch_fwd_p2<1, T>(x, B, C, nlat, Kp, mmax, mscale, xm, round_out, stream); \
+    if (fast && nlon == 1440) return launch_fwd_p2<3, T>(x, B, C, nlat, Kp, mmax, mscale, xm, round_out, stream);\
     return launch_fwd_generic<T>(x, B, C, nlat, Kp, nlon, mmax, mscale, xm, round_out, stream);                   \
   } while (0)
   switch (x_dtype) {
@@ -545,10 +563,13 @@ int dft_inv(const float* xm, int B, int C, int nlat, int nlon, int mmax, int m_v
   const int Kp = round_up(nlat, 4);
   m_valid = std::min(m_valid, mmax);
   const bool fast = use_fft480(nlon, mmax, y);
+  const bool lane_fft = use_lane_fft();
 #define SFNO_DISPATCH_INV(T)                                                                                    \
   do {                                                                                                          \
-    if (fast && nlon == 480) return launch_inv_fft<1, T>(xm, B, C, nlat, Kp, mmax, m_valid, mscale, y, stream); \
-    if (fast && nlon == 1440) return launch_inv_fft<3, T>(xm, B, C, nlat, Kp, mmax, m_valid, mscale, y, stream);\
+    if (fast && lane_fft && nlon == 480) return launch_inv_fft<1, T>(xm, B, C, nlat, Kp, mmax, m_valid, mscale, y, stream); \
+    if (fast && lane_fft && nlon == 1440) return launch_inv_fft<3, T>(xm, B, C, nlat, Kp, mmax, m_valid, mscale, y, stream);\
+    if (fast && nlon == 480) return launch_inv_p2<1, T>(xm, B, C, nlat, Kp, mmax, m_valid, mscale, y, stream); \
+    if (fast && nlon == 1440) return launch_inv_p2<3, T>(xm, B, C, nlat, Kp, mmax, m_valid, mscale, y, stream);\
     return launch_inv_generic<T>(xm, B, C, nlat, Kp, nlon, mmax, m_valid, mscale, y, stream);                   \
   } while (0)
   switch (y_dtype) {

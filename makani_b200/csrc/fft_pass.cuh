@@ -1,0 +1,214 @@
+// Two-pass (16 x 15) length-240 complex FFT for the longitude DFT kernels, exchange through shared memory.
+//
+// A row of 480 real samples is packed into 240 complex points z[n] = x[2n] + i x[2n+1] and transformed by the
+// 16 lanes of a half-warp:
+//     n = 15 n1 + n2   (n1 in [0,16), n2 in [0,15)),      k = k1 + 16 k2   (k1 in [0,16), k2 in [0,15))
+//     Z[k1 + 16 k2] = sum_n2 w15^(n2 k2) * [ w240^(n2 k1) * sum_n1 w16^(n1 k1) z[15 n1 + n2] ]
+//   pass A  lane n2 (< 15): 16-point FFT over n1 in registers, twiddle by w240^(n2 k1), store work[k1*15 + n2]
+//   pass B  lane k1       : load work[k1*15 + n2], 15-point DFT over n2 in registers  ->  Z[k1 + 16 k2]
+// Both shared-memory access patterns are conflict free for 8-byte elements (lane stride 1 / lane stride 15).
+// Only the real-input split needs data of another lane (bin 240-k lives on lane 16-k1): two shuffles per bin.
+// Compared with the 16-lane shuffle FFT of fft_lane.cuh this removes four shuffle butterfly stages
+// (8 instructions per complex value and stage) - about half of the instructions per row.
+//
+// The inverse runs the transposed flow graph (15-point DFT first, then 16-point FFT).
+//
+// Written against a "Warp" policy (lane16 / shfl_idx / sync over a 16-lane group) so the same code runs on
+// the device (DeviceWarp16p) and in a host emulation with one thread per lane (tests/cpp/fft_pass_host_test.cpp).
+#pragma once
+#include "fft_lane.cuh"
+
+namespace sfno {
+namespace fp {
+
+using fl::cf;
+using fl::mk;
+using fl::cadd;
+using fl::csub;
+using fl::cmul;
+using fl::cconj;
+using fl::cscale;
+
+// 4-point DFT, natural order.  w = e^{SGN i pi/2} = SGN i
+template <int SGN>
+FL_HD void dft4(cf& a0, cf& a1, cf& a2, cf& a3) {
+  const cf s02 = cadd(a0, a2), d02 = csub(a0, a2), s13 = cadd(a1, a3), d13 = csub(a1, a3);
+  const cf t = fl::mul_i<SGN>(d13);
+  a0 = cadd(s02, s13);
+  a2 = csub(s02, s13);
+  a1 = cadd(d02, t);
+  a3 = csub(d02, t);
+}
+
+// 16-point FFT, natural order in and out (radix 4 x 4).  n = 4a + b, k = c + 4d.
+template <int SGN>
+FL_HD void fft16(cf (&v)[16]) {
+  const float C1 = 0.9238795325112867f, S1 = 0.3826834323650898f, R2 = 0.7071067811865476f;
+  cf y[4][4];
+#pragma unroll
+  for (int b = 0; b < 4; ++b) {
+#pragma unroll
+    for (int a = 0; a < 4; ++a) y[b][a] = v[4 * a + b];
+    dft4<SGN>(y[b][0], y[b][1], y[b][2], y[b][3]);          // second index is now c
+  }
+  // twiddles w16^(b c), w16 = e^{SGN 2 pi i / 16}
+  y[1][1] = cmul(y[1][1], mk(C1, SGN * S1));                // w^1
+  y[1][2] = cmul(y[1][2], mk(R2, SGN * R2));                // w^2
+  y[1][3] = cmul(y[1][3], mk(S1, SGN * C1));                // w^3
+  y[2][1] = cmul(y[2][1], mk(R2, SGN * R2));                // w^2
+  y[2][2] = fl::mul_i<SGN>(y[2][2]);                        // w^4 = SGN i
+  y[2][3] = cmul(y[2][3], mk(-R2, SGN * R2));               // w^6
+  y[3][1] = cmul(y[3][1], mk(S1, SGN * C1));                // w^3
+  y[3][2] = cmul(y[3][2], mk(-R2, SGN * R2));               // w^6
+  y[3][3] = cmul(y[3][3], mk(-C1, -SGN * S1));              // w^9 = -w^1
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+    dft4<SGN>(y[0][c], y[1][c], y[2][c], y[3][c]);          // first index is now d
+#pragma unroll
+    for (int d = 0; d < 4; ++d) v[c + 4 * d] = y[d][c];
+  }
+}
+
+// Twiddle tables (built once on the host in double precision):
+//   twA[k1*15 + n2] = e^{-2 pi i n2 k1 / 240}     k1 in [0,16), n2 in [0,15)
+//   tw480[k]        = e^{-2 pi i k / 480}          k in [0,241)
+//   tw1440[m]       = e^{-2 pi i m / 1440}         m in [0,241)
+
+// forward complex FFT-240.  loadz(n) returns z[n].  out: Z[k2] = Z[lane + 16 k2].
+// `work` is a 240-element scratch row in shared memory owned by this 16-lane group.
+template <class Warp, class LoadZ>
+FL_HD void fft240p_fwd(Warp& w, LoadZ loadz, cf* work, const cf* twA, cf (&Z)[15]) {
+  const int t = w.lane16();
+  if (t < 15) {
+    cf a[16];
+#pragma unroll
+    for (int n1 = 0; n1 < 16; ++n1) a[n1] = loadz(15 * n1 + t);
+    fft16<-1>(a);
+    work[t] = a[0];
+#pragma unroll
+    for (int k1 = 1; k1 < 16; ++k1) work[k1 * 15 + t] = cmul(a[k1], twA[k1 * 15 + t]);
+  }
+  w.sync();
+#pragma unroll
+  for (int n2 = 0; n2 < 15; ++n2) Z[n2] = work[t * 15 + n2];
+  fl::dft15<-1>(Z);
+  w.sync();
+}
+
+// inverse (unnormalised, e^{+}) complex FFT-240.  in: V[k2] = V[lane + 16 k2] (destroyed);  storez(n, z[n]).
+template <class Warp, class StoreZ>
+FL_HD void fft240p_inv(Warp& w, cf (&V)[15], cf* work, const cf* twA, StoreZ storez) {
+  const int t = w.lane16();
+  fl::dft15<+1>(V);                                          // index is now n2
+  work[t * 15] = V[0];
+#pragma unroll
+  for (int n2 = 1; n2 < 15; ++n2) work[t * 15 + n2] = cmul(V[n2], cconj(twA[t * 15 + n2]));
+  w.sync();
+  if (t < 15) {
+    cf a[16];
+#pragma unroll
+    for (int k1 = 0; k1 < 16; ++k1) a[k1] = work[k1 * 15 + t];
+    fft16<+1>(a);
+#pragma unroll
+    for (int n1 = 0; n1 < 16; ++n1) storez(15 * n1 + t, a[n1]);
+  }
+  w.sync();
+}
+
+// Per-bin constants of the real-input split with the output scale s_k folded in:
+//   a = s_k / 2,   (bx, by) = (s_k / 2) * e^{-2 pi i k / 480}
+struct SplitC {
+  float a, bx, by, pad;
+};
+
+// real-input split.  in: Z[k2] = Z[lane + 16 k2];  emit(k2, s_k * X[lane + 16 k2]) for the length-480 real sequence;
+// returns the unscaled X[240] (meaningful on lane 0 only).  Bin 240-k of lane k1 > 0 is register 14-k2 of lane 16-k1;
+// lane 0 pairs its own registers (k2 <-> 15-k2, bin 0 with itself).
+//   X = (Z + conj(Zp))/2 - i w (Z - conj(Zp))/2
+template <class Warp, class Emit>
+FL_HD float rfft480_split(Warp& w, const cf (&Z)[15], Emit emit, const SplitC* sc) {
+  const int k1 = w.lane16();
+  const int src = (16 - k1) & 15;
+#pragma unroll
+  for (int k2 = 0; k2 < 15; ++k2) {
+    const SplitC c = sc[k1 + 16 * k2];
+    const cf zs = mk(w.shfl_idx(Z[14 - k2].x, src), w.shfl_idx(Z[14 - k2].y, src));
+    const cf z0 = (k2 == 0) ? Z[0] : Z[15 - k2];
+    const cf zp = (k1 == 0) ? z0 : zs;
+    const float sx = Z[k2].x + zp.x, sy = Z[k2].y - zp.y;     // Z + conj(Zp)
+    const float dx = Z[k2].x - zp.x, dy = Z[k2].y + zp.y;     // Z - conj(Zp)
+    const float px = c.bx * dx - c.by * dy, py = c.bx * dy + c.by * dx;
+    emit(k2, mk(c.a * sx + py, c.a * sy - px));
+  }
+  return Z[0].x - Z[0].y;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Row-level composition for nlon = 480 * R (R = 1: 240x480 Gauss grid, R = 3: 721x1440 equiangular).
+//   forward, R = 3: x_r[q] = x[3q + r] (three length-480 real FFTs), X[m] = sum_r w1440^(m r) X_r[m], m <= 240
+//                   (X[0..239] come out scaled by the SplitC table, x240 unscaled)
+//   inverse, R = 3: x[3q + r] = irfft480( X[m] conj(w1440)^(m r) ), bin 240 doubled (it is not Nyquist there)
+// loadz(n, r) returns (x[2 R n + r], x[2 R n + R + r]);  storez(n, r, z) writes that pair back.
+template <int R, class Warp, class LoadZ>
+FL_HD void rfft_row_fwd(Warp& w, LoadZ loadz, cf* work, cf (&X)[15], cf& x240, const cf* twA, const SplitC* sc,
+                        const cf* tw1440) {
+  const int k1 = w.lane16();
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    cf Z[15];
+    fft240p_fwd(w, [&](int n) { return loadz(n, r); }, work, twA, Z);
+    if (r == 0) {
+      const float nyq = rfft480_split(w, Z, [&](int k2, cf v) { X[k2] = v; }, sc);
+      x240 = mk(nyq, 0.f);
+    } else {
+      const float nyq = rfft480_split(w, Z, [&](int k2, cf v) {
+        const cf t1 = tw1440[k1 + 16 * k2];
+        const cf t = (r == 1) ? t1 : cmul(t1, t1);
+        X[k2] = cadd(X[k2], cmul(t, v));
+      }, sc);
+      const cf e1 = tw1440[240];
+      const cf e = (r == 1) ? e1 : cmul(e1, e1);
+      x240 = cadd(x240, cscale(e, nyq));
+    }
+  }
+}
+
+// Pre-processing of the inverse real FFT for one bin pair: from h = H[k], hp = H[240-k] (Hermitian half-spectrum of a
+// length-480 real sequence) build V[k] = A + i conj(w) B,  A = h + conj(hp), B = h - conj(hp),  so that
+// x[2n] + i x[2n+1] = sum_k V[k] e^{+2 pi i k n / 240}.
+FL_HD cf irfft480_prep(cf h, cf hp, cf w480_k) {
+  const float ax = h.x + hp.x, ay = h.y - hp.y;
+  const float bx = h.x - hp.x, by = h.y + hp.y;
+  const float px = w480_k.x * bx + w480_k.y * by, py = w480_k.x * by - w480_k.y * bx;   // conj(w) B
+  return mk(ax - py, ay + px);
+}
+
+// The R sub-sequence twist of bin pair (k, 240-k) for nlon = 480 R:  h *= conj(w1440^k)^r, hp *= conj(w1440^(240-k))^r,
+// and the k = 0 pair made real (bin 240 is a true Nyquist bin only for R = 1; otherwise an ordinary, doubled bin).
+template <int R>
+FL_HD void irfft_twist(int r, int k, cf& h, cf& hp, const cf* tw1440) {
+  if (R != 1 && r > 0) {
+    const cf t1 = cconj(tw1440[k]), u1 = cconj(tw1440[240 - k]);
+    h = cmul(h, r == 1 ? t1 : cmul(t1, t1));
+    hp = cmul(hp, r == 1 ? u1 : cmul(u1, u1));
+  }
+  if (k == 0) {
+    h = mk(h.x, 0.f);
+    hp = mk((R == 1 ? 1.f : 2.f) * hp.x, 0.f);
+  }
+}
+
+// makev(r, k2) returns V[lane + 16 k2] of sub-sequence r (built with irfft_twist + irfft480_prep from the scaled spectrum).
+template <int R, class Warp, class MakeV, class StoreZ>
+FL_HD void irfft_row(Warp& w, MakeV makev, cf* work, StoreZ storez, const cf* twA) {
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    cf V[15];
+#pragma unroll
+    for (int k2 = 0; k2 < 15; ++k2) V[k2] = makev(r, k2);
+    fft240p_inv(w, V, work, twA, [&](int n, cf z) { storez(n, r, z); });
+  }
+}
+
+}  // namespace fp
+}  // namespace sfno

@@ -389,13 +389,21 @@ def run_ours(args):
         dist.all_reduce(times, op=dist.ReduceOp.MAX)
     ms, ms_e2e = times.tolist()
 
-    line = None
+    # ---- roofline of the dominant kernel, measured live with CUDA events in a separate profiled pass.
+    # Every rank runs the pass (the steps contain the gradient all-reduce); only rank 0 instruments and reports.
+    rows = None
     if rank == 0:
-        # ---- roofline of the dominant kernel, measured live with CUDA events in a separate profiled pass
         with KernelProfiler() as prof:
             for _ in range(3):
                 step()
             rows = prof.summary()
+    else:
+        for _ in range(3):
+            step()
+    barrier()
+
+    line = None
+    if rank == 0:
         peak, peak_src = measured_peaks()
         dom = rows[0]
         step_ms_prof = sum(r["total_ms"] for r in rows) / 3

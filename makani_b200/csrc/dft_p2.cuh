@@ -31,9 +31,13 @@ __device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait0() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
-// staging tile: float index of (pm = reim*241 + m, row r); 16-byte chunks are XOR-swizzled with pm
-__device__ __forceinline__ int stage_idx(int pm, int r) { return pm * 16 + ((((r >> 2) ^ pm) & 3) << 2) + (r & 3); }
-__device__ __forceinline__ int stage_chunk(int pm, int q) { return pm * 16 + (((q ^ pm) & 3) << 2); }
+// staging tile: float index of (pm = reim*241 + m, row r).  The 16-byte chunk (4 rows) is XOR-swizzled with pm >> 1:
+// 16 lanes with consecutive pm then spread over 2 (pm & 1: 64-byte row parity) x 4 (chunk) bank groups, i.e. the
+// per-lane 4-byte accesses of the FFT side are 2-way conflicted (4-way with a pm & 3 swizzle, 16-way without).
+__device__ __forceinline__ int stage_idx(int pm, int r) {
+  return pm * 16 + ((((r >> 2) ^ (pm >> 1)) & 3) << 2) + (r & 3);
+}
+__device__ __forceinline__ int stage_chunk(int pm, int q) { return pm * 16 + (((q ^ (pm >> 1)) & 3) << 2); }
 
 constexpr int kStageTileBytes = 2 * 241 * 16 * 4;      // 30848 >= 16 rows x 240 complex (30720)
 
@@ -80,7 +84,7 @@ struct P2FwdSmem {
   static constexpr int kOffU = NBUF * kRawBytes;
   static constexpr int kOffTw = kOffU + kStageTileBytes;
   static constexpr int kOffSc = kOffTw + kTwCount * 8;
-  static constexpr int kOffBar = kOffSc + 241 * 16;
+  static constexpr int kOffBar = kOffSc + 244 * 4;
   static constexpr int kBytes = kOffBar + 64;
   static constexpr int kFit = (227 * 1024) / (kBytes + 1024);
   static constexpr int kCtasPerSm = kFit >= 3 ? 3 : (kFit >= 2 ? 2 : 1);
@@ -97,21 +101,12 @@ dft_fwd_p2_kernel(const T* __restrict__ x, float* __restrict__ xm, const fl::cf*
   fl::cf* work = reinterpret_cast<fl::cf*>(smp2 + S::kOffU);
   float* stage = reinterpret_cast<float*>(smp2 + S::kOffU);
   fl::cf* tw = reinterpret_cast<fl::cf*>(smp2 + S::kOffTw);
-  fp::SplitC* sc = reinterpret_cast<fp::SplitC*>(smp2 + S::kOffSc);
+  float* hs = reinterpret_cast<float*>(smp2 + S::kOffSc);      // half of the output scale of bin m (0 for m >= M)
   uint64_t* full = reinterpret_cast<uint64_t*>(smp2 + S::kOffBar);
 
   const int tid = threadIdx.x;
   for (int j = tid; j < kTwCount; j += 256) tw[j] = tables[j];
-  for (int j = tid; j < 241; j += 256) {
-    const float ms = j < M ? mscale[j] : 0.f;
-    const fl::cf w480 = tables[240 + j];
-    fp::SplitC c;
-    c.a = 0.5f * ms;
-    c.bx = 0.5f * ms * w480.x;
-    c.by = 0.5f * ms * w480.y;
-    c.pad = ms;                                  // full scale (used for bin 240)
-    sc[j] = c;
-  }
+  for (int j = tid; j < 244; j += 256) hs[j] = j < M ? 0.5f * mscale[j] : 0.f;
   if (tid == 0) {
     for (int b = 0; b < NBUF; ++b) mbar_init(&full[b], 1);
     fence_barrier_init();
@@ -127,10 +122,10 @@ dft_fwd_p2_kernel(const T* __restrict__ x, float* __restrict__ xm, const fl::cf*
   const int lane = tid & 15;
   DeviceWarp16p warp;
   // staging addresses of this thread: bin m = lane + 16 k2 sits 256 floats after bin m - 16 (the chunk swizzle only
-  // depends on m & 3 = lane & 3), so every store below is base + immediate
+  // depends on (m >> 1) & 3, unchanged by + 16), so every store below is base + immediate.
+  // The staging tile holds TWICE the unscaled spectrum; scale (and TF32 rounding) happen on the way out.
   float* st_re = stage + stage_idx(lane, r);
   float* st_im = stage + stage_idx(241 + lane, r);
-  auto rnd = [](float v) { return ROUND ? tf32_rn(v) : v; };
 
   // rows of `tile` -> raw[buf]   (executed by all 32 lanes of warp 0)
   auto issue = [&](int tile, int buf) {
@@ -174,17 +169,17 @@ dft_fwd_p2_kernel(const T* __restrict__ x, float* __restrict__ xm, const fl::cf*
         if (nt < ntiles) issue(nt, buf);
       }
       const float nyq = fp::rfft480_split(warp, Z, [&](int k2, fl::cf v) {
-        st_re[k2 * 256] = rnd(v.x);
-        st_im[k2 * 256] = rnd(v.y);
-      }, sc);
+        st_re[k2 * 256] = v.x;
+        st_im[k2 * 256] = v.y;
+      }, tw + 240);
       if (lane == 0) {
-        stage[stage_idx(240, r)] = rnd(nyq * sc[240].pad);
+        stage[stage_idx(240, r)] = nyq;
         stage[stage_idx(481, r)] = 0.f;
       }
     } else {
       fl::cf X[15], x240;
       fp::rfft_row_fwd<R>(warp, [&](int n, int rr) { return load_pair<R, T>(myrow, n, rr); }, work + r * 240, X, x240,
-                          tw, sc, tw + 481);
+                          tw, tw + 240, tw + 481);
       __syncthreads();
       if (tid < 32) {
         const int nt = tile + NBUF * gridDim.x;
@@ -192,13 +187,12 @@ dft_fwd_p2_kernel(const T* __restrict__ x, float* __restrict__ xm, const fl::cf*
       }
 #pragma unroll
       for (int k2 = 0; k2 < 15; ++k2) {
-        st_re[k2 * 256] = rnd(X[k2].x);
-        st_im[k2 * 256] = rnd(X[k2].y);
+        st_re[k2 * 256] = X[k2].x;
+        st_im[k2 * 256] = X[k2].y;
       }
       if (lane == 0) {
-        const float s240 = sc[240].pad;
-        stage[stage_idx(240, r)] = rnd(x240.x * s240);
-        stage[stage_idx(481, r)] = rnd(x240.y * s240);
+        stage[stage_idx(240, r)] = x240.x;
+        stage[stage_idx(481, r)] = x240.y;
       }
     }
     __syncthreads();
@@ -211,7 +205,10 @@ dft_fwd_p2_kernel(const T* __restrict__ x, float* __restrict__ xm, const fl::cf*
       for (int reim = 0; reim < 2; ++reim) {
         float* gp = xm + ((long long)(tid >> 2) * RS + (long long)(b * 2 + reim) * Cp) * Kp + f0 + 4 * q;
         for (int m = tid >> 2; m < M; m += 64, gp += gstep) {
-          const float4 v = *reinterpret_cast<const float4*>(stage + stage_chunk(reim * 241 + m, q));
+          float4 v = *reinterpret_cast<const float4*>(stage + stage_chunk(reim * 241 + m, q));
+          const float sc = hs[m];
+          v.x *= sc; v.y *= sc; v.z *= sc; v.w *= sc;
+          if (ROUND) { v.x = tf32_rn(v.x); v.y = tf32_rn(v.y); v.z = tf32_rn(v.z); v.w = tf32_rn(v.w); }
           if (fok) *reinterpret_cast<float4*>(gp) = v;
         }
       }

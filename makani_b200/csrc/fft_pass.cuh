@@ -115,42 +115,37 @@ FL_HD void fft240p_inv(Warp& w, cf (&V)[15], cf* work, const cf* twA, StoreZ sto
   w.sync();
 }
 
-// Per-bin constants of the real-input split with the output scale s_k folded in:
-//   a = s_k / 2,   (bx, by) = (s_k / 2) * e^{-2 pi i k / 480}
-struct SplitC {
-  float a, bx, by, pad;
-};
-
-// real-input split.  in: Z[k2] = Z[lane + 16 k2];  emit(k2, s_k * X[lane + 16 k2]) for the length-480 real sequence;
-// returns the unscaled X[240] (meaningful on lane 0 only).  Bin 240-k of lane k1 > 0 is register 14-k2 of lane 16-k1;
+// real-input split.  in: Z[k2] = Z[lane + 16 k2];  emit(k2, 2 X[lane + 16 k2]) for the length-480 real sequence
+// (TWICE the spectrum: the factor 1/2 is left to the caller, who folds it into its output scale);
+// returns 2 X[240] (meaningful on lane 0 only).  Bin 240-k of lane k1 > 0 is register 14-k2 of lane 16-k1;
 // lane 0 pairs its own registers (k2 <-> 15-k2, bin 0 with itself).
-//   X = (Z + conj(Zp))/2 - i w (Z - conj(Zp))/2
+//   2 X = (Z + conj(Zp)) - i w (Z - conj(Zp)),   w = e^{-2 pi i k / 480}
 template <class Warp, class Emit>
-FL_HD float rfft480_split(Warp& w, const cf (&Z)[15], Emit emit, const SplitC* sc) {
+FL_HD float rfft480_split(Warp& w, const cf (&Z)[15], Emit emit, const cf* tw480) {
   const int k1 = w.lane16();
   const int src = (16 - k1) & 15;
 #pragma unroll
   for (int k2 = 0; k2 < 15; ++k2) {
-    const SplitC c = sc[k1 + 16 * k2];
+    const cf c = tw480[k1 + 16 * k2];
     const cf zs = mk(w.shfl_idx(Z[14 - k2].x, src), w.shfl_idx(Z[14 - k2].y, src));
     const cf z0 = (k2 == 0) ? Z[0] : Z[15 - k2];
     const cf zp = (k1 == 0) ? z0 : zs;
     const float sx = Z[k2].x + zp.x, sy = Z[k2].y - zp.y;     // Z + conj(Zp)
     const float dx = Z[k2].x - zp.x, dy = Z[k2].y + zp.y;     // Z - conj(Zp)
-    const float px = c.bx * dx - c.by * dy, py = c.bx * dy + c.by * dx;
-    emit(k2, mk(c.a * sx + py, c.a * sy - px));
+    const float px = c.x * dx - c.y * dy, py = c.x * dy + c.y * dx;
+    emit(k2, mk(sx + py, sy - px));
   }
-  return Z[0].x - Z[0].y;
+  return 2.f * (Z[0].x - Z[0].y);
 }
 
 // ---------------------------------------------------------------------------------------------
 // Row-level composition for nlon = 480 * R (R = 1: 240x480 Gauss grid, R = 3: 721x1440 equiangular).
 //   forward, R = 3: x_r[q] = x[3q + r] (three length-480 real FFTs), X[m] = sum_r w1440^(m r) X_r[m], m <= 240
-//                   (X[0..239] come out scaled by the SplitC table, x240 unscaled)
+//                   (outputs are TWICE the spectrum, see rfft480_split)
 //   inverse, R = 3: x[3q + r] = irfft480( X[m] conj(w1440)^(m r) ), bin 240 doubled (it is not Nyquist there)
 // loadz(n, r) returns (x[2 R n + r], x[2 R n + R + r]);  storez(n, r, z) writes that pair back.
 template <int R, class Warp, class LoadZ>
-FL_HD void rfft_row_fwd(Warp& w, LoadZ loadz, cf* work, cf (&X)[15], cf& x240, const cf* twA, const SplitC* sc,
+FL_HD void rfft_row_fwd(Warp& w, LoadZ loadz, cf* work, cf (&X)[15], cf& x240, const cf* twA, const cf* tw480,
                         const cf* tw1440) {
   const int k1 = w.lane16();
 #pragma unroll
@@ -158,14 +153,14 @@ FL_HD void rfft_row_fwd(Warp& w, LoadZ loadz, cf* work, cf (&X)[15], cf& x240, c
     cf Z[15];
     fft240p_fwd(w, [&](int n) { return loadz(n, r); }, work, twA, Z);
     if (r == 0) {
-      const float nyq = rfft480_split(w, Z, [&](int k2, cf v) { X[k2] = v; }, sc);
+      const float nyq = rfft480_split(w, Z, [&](int k2, cf v) { X[k2] = v; }, tw480);
       x240 = mk(nyq, 0.f);
     } else {
       const float nyq = rfft480_split(w, Z, [&](int k2, cf v) {
         const cf t1 = tw1440[k1 + 16 * k2];
         const cf t = (r == 1) ? t1 : cmul(t1, t1);
         X[k2] = cadd(X[k2], cmul(t, v));
-      }, sc);
+      }, tw480);
       const cf e1 = tw1440[240];
       const cf e = (r == 1) ? e1 : cmul(e1, e1);
       x240 = cadd(x240, cscale(e, nyq));

@@ -42,6 +42,7 @@ struct GemmArgs {
   long long out_col_stride; // output offset per column
   long long out_im_offset;  // complex modes: offset of the imaginary plane
   int round_out;            // 1: store round-to-nearest TF32 values (the consumer is another TF32 GEMM)
+  unsigned long long pol_a, pol_b, pol_out;   // L2 cache policies of the two operand streams and of the output
 };
 
 template <int MODE>
@@ -128,32 +129,32 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
             uint8_t* sb = stage_b(stage, p);
             // ---- A operand
             if constexpr (MODE == LEG_ANA) {                 // XM (k, r, m)  K-major
-              tma_load_3d(sa, &map_a, &full_bar[stage], kc, tile.row0, tile.g);
+              tma_load_3d_hint(sa, &map_a, &full_bar[stage], kc, tile.row0, tile.g, args.pol_a);
             } else if constexpr (MODE == LEG_SYN) {          // table (k_lat, l, m)  MN-major: 4 chunks of 32 rows
 #pragma unroll
               for (int j = 0; j < 4; ++j)
-                tma_load_3d(sa + j * 4096, &map_a, &full_bar[stage], tile.row0 + 32 * j, kc, tile.g);
+                tma_load_3d_hint(sa + j * 4096, &map_a, &full_bar[stage], tile.row0 + 32 * j, kc, tile.g, args.pol_a);
             } else if constexpr (MODE == DH_FWD) {           // WP (i, o, reim, l)  K-major
-              tma_load_4d(sa, &map_a, &full_bar[stage], kc, tile.row0, p, tile.g);
+              tma_load_4d_hint(sa, &map_a, &full_bar[stage], kc, tile.row0, p, tile.g, args.pol_a);
             } else if constexpr (MODE == DH_BWDX) {          // WP (i, o, reim, l)  MN-major in i
 #pragma unroll
               for (int j = 0; j < 4; ++j)
-                tma_load_4d(sa + j * 4096, &map_a, &full_bar[stage], tile.row0 + 32 * j, kc, p, tile.g);
+                tma_load_4d_hint(sa + j * 4096, &map_a, &full_bar[stage], tile.row0 + 32 * j, kc, p, tile.g, args.pol_a);
             } else {                                         // DH_BWDW: SP_in (i, reim, n, l)  MN-major in i
 #pragma unroll
               for (int j = 0; j < 4; ++j)
-                tma_load_4d(sa + j * 4096, &map_a, &full_bar[stage], tile.row0 + 32 * j, p, kc, tile.g);
+                tma_load_4d_hint(sa + j * 4096, &map_a, &full_bar[stage], tile.row0 + 32 * j, p, kc, tile.g, args.pol_a);
             }
             // ---- B operand
             for (int j = 0; j < nb_boxes; ++j) {
               if constexpr (MODE == LEG_ANA) {               // table (k, l, m) K-major, 64-row boxes
-                tma_load_3d(sb + j * 8192, &map_b, &full_bar[stage], kc, tile.col0 + 64 * j, tile.g);
+                tma_load_3d_hint(sb + j * 8192, &map_b, &full_bar[stage], kc, tile.col0 + 64 * j, tile.g, args.pol_b);
               } else if constexpr (MODE == LEG_SYN) {        // SP (r, m, l) MN-major, 32-col chunks
-                tma_load_3d(sb + j * 4096, &map_b, &full_bar[stage], tile.col0 + 32 * j, tile.g, kc);
+                tma_load_3d_hint(sb + j * 4096, &map_b, &full_bar[stage], tile.col0 + 32 * j, tile.g, kc, args.pol_b);
               } else if constexpr (MODE == DH_FWD || MODE == DH_BWDX) {   // SP (c, reim, n, l) K-major
-                tma_load_4d(sb + j * 8192, &map_b, &full_bar[stage], kc, p, tile.col0 + 64 * j, tile.g);
+                tma_load_4d_hint(sb + j * 8192, &map_b, &full_bar[stage], kc, p, tile.col0 + 64 * j, tile.g, args.pol_b);
               } else {                                       // DH_BWDW: gSP_out (o, reim, n, l) MN-major in o
-                tma_load_4d(sb + j * 4096, &map_b, &full_bar[stage], tile.col0 + 32 * j, p, kc, tile.g);
+                tma_load_4d_hint(sb + j * 4096, &map_b, &full_bar[stage], tile.col0 + 32 * j, p, kc, tile.g, args.pol_b);
               }
             }
           }
@@ -273,11 +274,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
             const int nv = nvalid - c;
             if (nv >= 32) {
 #pragma unroll
-              for (int j = 0; j < 32; ++j) op[j * cstride] = w[j];
+              for (int j = 0; j < 32; ++j) st_global_hint(op + j * cstride, w[j], args.pol_out);
             } else {
 #pragma unroll
               for (int j = 0; j < 32; ++j)
-                if (j < nv) op[j * cstride] = w[j];
+                if (j < nv) st_global_hint(op + j * cstride, w[j], args.pol_out);
             }
           }
           op += 32 * (long long)cstride;

@@ -51,8 +51,7 @@ static double run(bool verbose) {
       twA[k1 * 15 + n2] = mk((float)cos(a), (float)sin(a));
     }
   std::vector<cf> work(240);
-  std::vector<fp::SplitC> sc(241);
-  for (int k = 0; k < 241; ++k) sc[k] = fp::SplitC{0.5f, 0.5f * tw480[k].x, 0.5f * tw480[k].y, 0.f};
+
   std::vector<float> x(W);
   srand(1234 + R);
   for (auto& v : x) v = (float)rand() / RAND_MAX - 0.5f;
@@ -77,9 +76,9 @@ static double run(bool verbose) {
         HostWarp w{lane, slots, &bar};
         cf Xl[15], x240;
         fp::rfft_row_fwd<R, HostWarp>(w, [&](int n, int r) { return mk(x[2 * R * n + r], x[2 * R * n + R + r]); }, work.data(),
-                            Xl, x240, twA.data(), sc.data(), tw1440.data());
-        for (int k2 = 0; k2 < 15; ++k2) X[lane + 16 * k2] = {Xl[k2].x, Xl[k2].y};
-        if (lane == 0) X[240] = {x240.x, x240.y};
+                            Xl, x240, twA.data(), tw480.data(), tw1440.data());
+        for (int k2 = 0; k2 < 15; ++k2) X[lane + 16 * k2] = {0.5f * Xl[k2].x, 0.5f * Xl[k2].y};
+        if (lane == 0) X[240] = {0.5f * x240.x, 0.5f * x240.y};
       });
     for (auto& t : th) t.join();
   }

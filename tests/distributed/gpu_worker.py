@@ -1,0 +1,132 @@
+"""Multi-GPU parity worker (launched by torchrun from tests/test_gpu_distributed.py, one rank per GPU, NCCL).
+
+Compares the h/w spatially sharded transforms (makani_b200.distributed) and a SpectralConv built on them with the
+single-GPU modules on the same seeded inputs, forward and backward - the pattern of the reference's
+tests/distributed/tests_fft.py:150-244 (local result -> split -> compare with the distributed result)."""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
+import torch
+import torch.distributed as dist
+
+import makani_b200 as mk
+import makani_b200.distributed as thd
+
+TOL = 2e-3     # relative L2; every transform is one TF32 contraction (tests/test_gpu_modules.py uses the same bound)
+
+
+def rel(a, b):
+    return float((a - b).norm() / b.norm().clamp_min(1e-30))
+
+
+def split_slice(shapes, idx):
+    o = sum(shapes[:idx])
+    return slice(o, o + shapes[idx])
+
+
+def main():
+    h, w = int(sys.argv[1]), int(sys.argv[2])
+    nlat, nlon, grid, C = int(sys.argv[3]), int(sys.argv[4]), sys.argv[5], int(sys.argv[6])
+    lmax = int(sys.argv[7]) if len(sys.argv) > 7 else None
+    mmax = int(sys.argv[8]) if len(sys.argv) > 8 else None
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    assert h * w == world
+    dev = torch.device("cuda", int(os.environ["LOCAL_RANK"]))
+    torch.cuda.set_device(dev)
+    dist.init_process_group("nccl", device_id=dev)
+    ih, iw = rank // w, rank % w
+    polar = azimuth = None
+    for j in range(w):                       # polar (h) groups: same w index
+        g = dist.new_group([i * w + j for i in range(h)])
+        if j == iw:
+            polar = g
+    for i in range(h):                       # azimuth (w) groups: same h index
+        g = dist.new_group([i * w + j for j in range(w)])
+        if i == ih:
+            azimuth = g
+    thd.init(polar if h > 1 else None, azimuth if w > 1 else None)
+
+    B = 2
+    kw = dict(lmax=lmax, mmax=mmax, grid=grid)
+    fwd = mk.RealSHT(nlat, nlon, **kw).to(dev)
+    inv = mk.InverseRealSHT(nlat, nlon, **kw).to(dev)
+    dfwd = thd.DistributedRealSHT(nlat, nlon, **kw).to(dev)
+    dinv = thd.DistributedInverseRealSHT(nlat, nlon, **kw).to(dev)
+    L, M = fwd.lmax, fwd.mmax
+    assert dfwd.lat_shapes == thd.compute_split_shapes(nlat, h) and dfwd.m_shapes == thd.compute_split_shapes(M, w)
+    sl_lat, sl_lon = split_slice(dfwd.lat_shapes, ih), split_slice(dfwd.lon_shapes, iw)
+    sl_l, sl_m = split_slice(dfwd.l_shapes, ih), split_slice(dfwd.m_shapes, iw)
+
+    g = torch.Generator(device="cpu").manual_seed(1234)
+    x_full = torch.randn(B, C, nlat, nlon, generator=g).to(dev)
+    gc_full = torch.randn(B, C, L, M, 2, generator=g).to(dev)
+    gc_full = torch.view_as_complex(gc_full.contiguous())
+    gx_full = torch.randn(B, C, nlat, nlon, generator=g).to(dev)
+    errs = {}
+
+    # ---- forward SHT, forward + backward
+    xr = x_full.clone().requires_grad_(True)
+    cr = fwd(xr)
+    (cr * gc_full.conj()).real.sum().backward()
+    xl = x_full[:, :, sl_lat, sl_lon].contiguous().requires_grad_(True)
+    cl = dfwd(xl)
+    (cl * gc_full[:, :, sl_l, sl_m].conj()).real.sum().backward()
+    assert cl.shape == (B, C, dfwd.l_shapes[ih], dfwd.m_shapes[iw]), cl.shape
+    errs["sht_fwd"] = rel(cl.detach(), cr.detach()[:, :, sl_l, sl_m])
+    errs["sht_bwd"] = rel(xl.grad, xr.grad[:, :, sl_lat, sl_lon])
+
+    # ---- inverse SHT, forward + backward (triangular coefficients, like real use)
+    tri = (torch.arange(M, device=dev)[None, :] <= torch.arange(L, device=dev)[:, None])
+    c_full = (gc_full * tri).contiguous()
+    c1 = c_full.clone().requires_grad_(True)
+    y1 = inv(c1)
+    (y1 * gx_full).sum().backward()
+    c2 = c_full[:, :, sl_l, sl_m].contiguous().requires_grad_(True)
+    y2 = dinv(c2)
+    (y2 * gx_full[:, :, sl_lat, sl_lon]).sum().backward()
+    assert y2.shape == (B, C, dinv.lat_shapes[ih], dinv.lon_shapes[iw]), y2.shape
+    errs["isht_fwd"] = rel(y2.detach(), y1.detach()[:, :, sl_lat, sl_lon])
+    errs["isht_bwd"] = rel(c2.grad[..., :, :] * tri[sl_l, sl_m], (c1.grad * tri)[:, :, sl_l, sl_m])
+
+    # ---- SpectralConv (dhconv) on the distributed transforms vs the fused single-GPU module
+    torch.manual_seed(7)
+    conv = mk.SpectralConv(fwd, inv, C, C, operator_type="dhconv").to(dev)
+    dconv = mk.SpectralConv(dfwd, dinv, C, C, operator_type="dhconv").to(dev)
+    wfull = conv.weight.detach().clone()
+    dist.broadcast(torch.view_as_real(wfull), src=0)
+    with torch.no_grad():
+        conv.weight.copy_(wfull)
+        dconv.weight.copy_(wfull[..., sl_l])
+    assert dconv.weight.shape == (C, C, dfwd.l_shapes[ih])
+    xr = x_full.clone().requires_grad_(True)
+    yr, _ = conv(xr)
+    (yr * gx_full).sum().backward()
+    xl = x_full[:, :, sl_lat, sl_lon].contiguous().requires_grad_(True)
+    yl, _ = dconv(xl)
+    (yl * gx_full[:, :, sl_lat, sl_lon]).sum().backward()
+    errs["conv_fwd"] = rel(yl.detach(), yr.detach()[:, :, sl_lat, sl_lon])
+    errs["conv_dx"] = rel(xl.grad, xr.grad[:, :, sl_lat, sl_lon])
+    # dhconv weights are shared over the azimuth group (is_shared_mp = ["matmul", "w"]): the reference reduces
+    # their gradients over "w" (makani/mpu/mappings.py:104-172); do the same before comparing
+    gw = dconv.weight.grad.clone()
+    if w > 1:
+        dist.all_reduce(torch.view_as_real(gw), group=azimuth)
+    errs["conv_dw"] = rel(gw, conv.weight.grad[..., sl_l])
+
+    torch.cuda.synchronize()
+    worst = torch.tensor([max(errs.values())], device=dev)
+    dist.all_reduce(worst, op=dist.ReduceOp.MAX)
+    line = " ".join(f"{k}={v:.2e}" for k, v in errs.items())
+    print(f"[rank {rank} h{ih} w{iw}] {line}", flush=True)
+    dist.barrier()
+    dist.destroy_process_group()
+    if float(worst) >= TOL:
+        print(f"DIST_GPU_FAIL worst={float(worst):.3e}", flush=True)
+        sys.exit(1)
+    if rank == 0:
+        print(f"DIST_GPU_OK h={h} w={w} {nlat}x{nlon} worst={float(worst):.3e}", flush=True)
+
+
+if __name__ == "__main__":
+    main()

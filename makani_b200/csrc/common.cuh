@@ -47,6 +47,7 @@ inline long long round_up_ll(long long x, long long m) { return (x + m - 1) / m 
 // a machine without a driver for the CPU-side symbol test).
 // swizzle: 1 = SWIZZLE_128B (16 B atoms; K-major UMMA operands),
 //          2 = SWIZZLE_128B_ATOM_32B (32 B atoms; the only layout tcgen05 accepts for MN-major 32-bit operands)
+//          3 = SWIZZLE_64B (staging tiles of the DFT kernels: 64-byte rows)
 int encode_tensor_map(CUtensorMap* map, const void* gptr, int rank, const uint64_t* dims,
                       const uint64_t* strides_bytes /* rank-1 entries */, const uint32_t* box,
                       int swizzle);

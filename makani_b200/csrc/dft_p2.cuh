@@ -31,15 +31,29 @@ __device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait0() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
-// staging tile: float index of (pm = reim*241 + m, row r).  The 16-byte chunk (4 rows) is XOR-swizzled with pm >> 1:
-// 16 lanes with consecutive pm then spread over 2 (pm & 1: 64-byte row parity) x 4 (chunk) bank groups, i.e. the
-// per-lane 4-byte accesses of the FFT side are 2-way conflicted (4-way with a pm & 3 swizzle, 16-way without).
-__device__ __forceinline__ int stage_idx(int pm, int r) {
-  return pm * 16 + ((((r >> 2) ^ (pm >> 1)) & 3) << 2) + (r & 3);
-}
-__device__ __forceinline__ int stage_chunk(int pm, int q) { return pm * 16 + (((q ^ (pm >> 1)) & 3) << 2); }
+// Staging tile between the FFT lanes and XM: two planes (re, im) of [248][16] floats; plane p, bin m, row r at
+//     p*3968 + m*16 + (((r >> 2) ^ (m >> 1)) & 3)*4 + (r & 3)
+// This is exactly the TMA SWIZZLE_64B layout of a box {16 latitudes, 1, 241 bins} (16-byte chunk index XOR address
+// bits [7,9)), so one tensor copy per plane moves the whole tile to / from XM[m][r][k]; on the FFT side 16 lanes with
+// consecutive m and two adjacent rows hit 16 different banks (2-way conflict; a dense tile would be 16-way).
+constexpr int kPlaneFloats = 248 * 16;                     // 15872 B: planes start 512-byte aligned (swizzle period)
+constexpr int kStageTileBytes = 2 * kPlaneFloats * 4;      // 31744 >= 16 rows x 240 complex (30720)
+__device__ __forceinline__ int stage_idx(int m, int r) { return m * 16 + ((((r >> 2) ^ (m >> 1)) & 3) << 2) + (r & 3); }
 
-constexpr int kStageTileBytes = 2 * 241 * 16 * 4;      // 30848 >= 16 rows x 240 complex (30720)
+__device__ __forceinline__ void tma_store_3d(const CUtensorMap* m, const void* smem_src, int c0, int c1, int c2) {
+  asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
+               ::"l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2) : "memory");
+}
+
+// XM viewed as [m][j = b*2 + reim][f = c*Kp + lat]; box = 16 flat positions x 241 bins of one (b, re/im) plane.
+// mdim bounds the bins (loads beyond it read zeros, stores beyond it are dropped).
+static int xm_stage_map(CUtensorMap* map, const float* xm, int B, int C, int Kp, int mdim) {
+  const int Cp = (C + 3) & ~3;
+  uint64_t dims[3] = {(uint64_t)C * Kp, (uint64_t)2 * B, (uint64_t)mdim};
+  uint64_t str[2] = {(uint64_t)Cp * Kp * 4, (uint64_t)2 * B * Cp * Kp * 4};
+  uint32_t box[3] = {16, 1, 241};
+  return encode_tensor_map(map, xm, 3, dims, str, box, 3);
+}
 
 // tables for the p2 kernels: twA[240] | tw480[241] | tw1440[241]
 static std::map<int, fl::cf*> g_p2_tw_cache;
@@ -81,25 +95,27 @@ struct P2FwdSmem {
   static constexpr int W = 480 * R;
   static constexpr int kRowBytes = W * (int)sizeof(T);
   static constexpr int kRawBytes = kRows * kRowBytes;
-  static constexpr int kOffU = NBUF * kRawBytes;
-  static constexpr int kOffTw = kOffU + kStageTileBytes;
+  static constexpr int kOffRaw = kStageTileBytes;           // staging tile first (1024-byte aligned base)
+  static constexpr int kOffTw = kOffRaw + NBUF * kRawBytes;
   static constexpr int kOffSc = kOffTw + kTwCount * 8;
   static constexpr int kOffBar = kOffSc + 244 * 4;
-  static constexpr int kBytes = kOffBar + 64;
+  static constexpr int kBytes = kOffBar + 64 + 1024;        // + slack for the manual 1024-byte alignment
   static constexpr int kFit = (227 * 1024) / (kBytes + 1024);
   static constexpr int kCtasPerSm = kFit >= 3 ? 3 : (kFit >= 2 ? 2 : 1);
 };
 
 template <int R, typename T, int NBUF, bool ROUND, int OCC>
 __global__ void __launch_bounds__(256, OCC)
-dft_fwd_p2_kernel(const T* __restrict__ x, float* __restrict__ xm, const fl::cf* __restrict__ tables,
-                  const float* __restrict__ mscale, int B, int C, int K, int Kp, int M) {
+dft_fwd_p2_kernel(const T* __restrict__ x, const __grid_constant__ CUtensorMap xm_map,
+                  const fl::cf* __restrict__ tables, const float* __restrict__ mscale, int B, int C, int K, int Kp,
+                  int M) {
   using S = P2FwdSmem<R, T, NBUF>;
   constexpr int W = S::W;
-  extern __shared__ __align__(128) uint8_t smp2[];
-  uint8_t* raw = smp2;
-  fl::cf* work = reinterpret_cast<fl::cf*>(smp2 + S::kOffU);
-  float* stage = reinterpret_cast<float*>(smp2 + S::kOffU);
+  extern __shared__ uint8_t smp2_raw[];
+  uint8_t* smp2 = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smp2_raw) + 1023) & ~uintptr_t(1023));
+  fl::cf* work = reinterpret_cast<fl::cf*>(smp2);
+  float* stage = reinterpret_cast<float*>(smp2);
+  uint8_t* raw = smp2 + S::kOffRaw;
   fl::cf* tw = reinterpret_cast<fl::cf*>(smp2 + S::kOffTw);
   float* hs = reinterpret_cast<float*>(smp2 + S::kOffSc);      // half of the output scale of bin m (0 for m >= M)
   uint64_t* full = reinterpret_cast<uint64_t*>(smp2 + S::kOffBar);
@@ -108,13 +124,12 @@ dft_fwd_p2_kernel(const T* __restrict__ x, float* __restrict__ xm, const fl::cf*
   for (int j = tid; j < kTwCount; j += 256) tw[j] = tables[j];
   for (int j = tid; j < 244; j += 256) hs[j] = j < M ? 0.5f * mscale[j] : 0.f;
   if (tid == 0) {
+    tma_prefetch_desc(&xm_map);
     for (int b = 0; b < NBUF; ++b) mbar_init(&full[b], 1);
     fence_barrier_init();
   }
   __syncthreads();
 
-  const int Cp = (C + 3) & ~3;
-  const long long RS = 2LL * B * Cp;
   const int flat = C * Kp;
   const int tiles_per_b = (flat + kRows - 1) / kRows;
   const int ntiles = tiles_per_b * B;
@@ -122,10 +137,10 @@ dft_fwd_p2_kernel(const T* __restrict__ x, float* __restrict__ xm, const fl::cf*
   const int lane = tid & 15;
   DeviceWarp16p warp;
   // staging addresses of this thread: bin m = lane + 16 k2 sits 256 floats after bin m - 16 (the chunk swizzle only
-  // depends on (m >> 1) & 3, unchanged by + 16), so every store below is base + immediate.
-  // The staging tile holds TWICE the unscaled spectrum; scale (and TF32 rounding) happen on the way out.
+  // depends on (m >> 1) & 3, unchanged by + 16), so every store below is base + immediate
   float* st_re = stage + stage_idx(lane, r);
-  float* st_im = stage + stage_idx(241 + lane, r);
+  float* st_im = st_re + kPlaneFloats;
+  auto fin = [](float v, float sc) { return ROUND ? tf32_rn(v * sc) : v * sc; };
 
   // rows of `tile` -> raw[buf]   (executed by all 32 lanes of warp 0)
   auto issue = [&](int tile, int buf) {
@@ -158,6 +173,10 @@ dft_fwd_p2_kernel(const T* __restrict__ x, float* __restrict__ xm, const fl::cf*
     const int b = tile / tiles_per_b;
     const int f0 = (tile - b * tiles_per_b) * kRows;
     mbar_wait(&full[buf], parity);
+    if (it > 0) {                                // the staging tile doubles as the FFT work buffer: the tensor stores
+      if (tid == 0) bulk_wait_read0();           // of the previous tile must have read it (overlaps the row wait above)
+      __syncthreads();
+    }
     const T* myrow = reinterpret_cast<const T*>(raw + buf * S::kRawBytes + r * S::kRowBytes);
 
     if constexpr (R == 1) {
@@ -169,12 +188,13 @@ dft_fwd_p2_kernel(const T* __restrict__ x, float* __restrict__ xm, const fl::cf*
         if (nt < ntiles) issue(nt, buf);
       }
       const float nyq = fp::rfft480_split(warp, Z, [&](int k2, fl::cf v) {
-        st_re[k2 * 256] = v.x;
-        st_im[k2 * 256] = v.y;
+        const float sc = hs[lane + 16 * k2];
+        st_re[k2 * 256] = fin(v.x, sc);
+        st_im[k2 * 256] = fin(v.y, sc);
       }, tw + 240);
       if (lane == 0) {
-        stage[stage_idx(240, r)] = nyq;
-        stage[stage_idx(481, r)] = 0.f;
+        stage[3840 + r] = fin(nyq, hs[240]);
+        stage[kPlaneFloats + 3840 + r] = 0.f;
       }
     } else {
       fl::cf X[15], x240;
@@ -187,159 +207,130 @@ dft_fwd_p2_kernel(const T* __restrict__ x, float* __restrict__ xm, const fl::cf*
       }
 #pragma unroll
       for (int k2 = 0; k2 < 15; ++k2) {
-        st_re[k2 * 256] = X[k2].x;
-        st_im[k2 * 256] = X[k2].y;
+        const float sc = hs[lane + 16 * k2];
+        st_re[k2 * 256] = fin(X[k2].x, sc);
+        st_im[k2 * 256] = fin(X[k2].y, sc);
       }
       if (lane == 0) {
-        stage[stage_idx(240, r)] = x240.x;
-        stage[stage_idx(481, r)] = x240.y;
+        stage[3840 + r] = fin(x240.x, hs[240]);
+        stage[kPlaneFloats + 3840 + r] = fin(x240.y, hs[240]);
       }
     }
+    fence_proxy_async();                         // staging tile (generic-proxy writes) -> visible to the tensor stores
     __syncthreads();
-    // ---- staging tile -> XM: 16-byte vectors, 4 lanes cover the 16 latitudes of one (m, re/im)
-    {
-      const int q = tid & 3;
-      const bool fok = f0 + 4 * q < flat;
-      const long long gstep = 64LL * RS * Kp;
-#pragma unroll
-      for (int reim = 0; reim < 2; ++reim) {
-        float* gp = xm + ((long long)(tid >> 2) * RS + (long long)(b * 2 + reim) * Cp) * Kp + f0 + 4 * q;
-        for (int m = tid >> 2; m < M; m += 64, gp += gstep) {
-          float4 v = *reinterpret_cast<const float4*>(stage + stage_chunk(reim * 241 + m, q));
-          const float sc = hs[m];
-          v.x *= sc; v.y *= sc; v.z *= sc; v.w *= sc;
-          if (ROUND) { v.x = tf32_rn(v.x); v.y = tf32_rn(v.y); v.z = tf32_rn(v.z); v.w = tf32_rn(v.w); }
-          if (fok) *reinterpret_cast<float4*>(gp) = v;
-        }
-      }
+    // ---- staging tile -> XM: one tensor store per plane (16 latitudes x 241 bins; bins >= M and positions beyond
+    //      C*Kp are clipped by the tensor map)
+    if (tid == 0) {
+      tma_store_3d(&xm_map, stage, f0, 2 * b, 0);
+      tma_store_3d(&xm_map, stage + kPlaneFloats, f0, 2 * b + 1, 0);
+      bulk_commit();
     }
-    __syncthreads();
   }
+  if (tid == 0) bulk_wait_read0();               // shared memory must outlive the last tensor stores' reads
 }
 
 // ================================================================================ inverse
-// per-bin constants of the inverse pre-processing, k in [0, 240): scales of bins k and 240-k, and e^{-2 pi i k / 480}
-struct InvC {
-  float s0, s1, wx, wy;
-};
-
 template <int R, typename T, int NST>
 struct P2InvSmem {
   static constexpr int W = 480 * R;
   static constexpr int kRowBytes = W * (int)sizeof(T);
   static constexpr int kRowsBytes = kRows * kRowBytes;
-  static constexpr int kOffRows = NST * kStageTileBytes;
+  static constexpr int kOffRows = NST * kStageTileBytes;    // staging tiles first (1024-byte aligned base)
   static constexpr int kOffTw = kOffRows + kRowsBytes;
-  static constexpr int kOffC = kOffTw + kTwCount * 8;
-  static constexpr int kBytes = kOffC + 240 * 16;
+  static constexpr int kOffMsc = kOffTw + kTwCount * 8;
+  static constexpr int kOffBar = kOffMsc + 244 * 4;
+  static constexpr int kBytes = kOffBar + 64 + 1024;
   static constexpr int kFit = (227 * 1024) / (kBytes + 1024);
   static constexpr int kCtasPerSm = kFit >= 2 ? 2 : 1;
 };
 
 template <int R, typename T, int NST>
 __global__ void __launch_bounds__(256, P2InvSmem<R, T, NST>::kCtasPerSm)
-dft_inv_p2_kernel(const float* __restrict__ xm, T* __restrict__ y, const fl::cf* __restrict__ tables,
-                  const float* __restrict__ mscale, int B, int C, int K, int Kp, int M, int m_valid) {
+dft_inv_p2_kernel(const __grid_constant__ CUtensorMap xm_map, T* __restrict__ y, const fl::cf* __restrict__ tables,
+                  const float* __restrict__ mscale, int B, int C, int K, int Kp, int m_valid) {
   using S = P2InvSmem<R, T, NST>;
   constexpr int W = S::W;
-  extern __shared__ __align__(128) uint8_t smp2[];
+  extern __shared__ uint8_t smp2_raw[];
+  uint8_t* smp2 = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smp2_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* rows = smp2 + S::kOffRows;
   fl::cf* tw = reinterpret_cast<fl::cf*>(smp2 + S::kOffTw);
-  InvC* ic = reinterpret_cast<InvC*>(smp2 + S::kOffC);
+  float* msc = reinterpret_cast<float*>(smp2 + S::kOffMsc);
+  uint64_t* full = reinterpret_cast<uint64_t*>(smp2 + S::kOffBar);
 
   const int tid = threadIdx.x;
   for (int j = tid; j < kTwCount; j += 256) tw[j] = tables[j];
-  for (int j = tid; j < 240; j += 256) {
-    const fl::cf w480 = tables[240 + j];
-    InvC c;
-    c.s0 = j < m_valid ? mscale[j] : 0.f;
-    c.s1 = (240 - j) < m_valid ? mscale[240 - j] : 0.f;
-    c.wx = w480.x;
-    c.wy = w480.y;
-    ic[j] = c;
+  for (int j = tid; j < 244; j += 256) msc[j] = j < m_valid ? mscale[j] : 0.f;
+  if (tid == 0) {
+    tma_prefetch_desc(&xm_map);
+    for (int b = 0; b < NST; ++b) mbar_init(&full[b], 1);
+    fence_barrier_init();
   }
+  __syncthreads();
 
-  const int Cp = (C + 3) & ~3;
-  const long long RS = 2LL * B * Cp;
   const int flat = C * Kp;
   const int tiles_per_b = (flat + kRows - 1) / kRows;
   const int ntiles = tiles_per_b * B;
   const int r = tid >> 4;
   const int lane = tid & 15;
+  const int psrc = (16 - lane) & 15;
   DeviceWarp16p warp;
-  // float offsets inside a staging tile of this thread's bins: k = lane + 16 k2 -> + 256 k2 ; 240 - k -> - 256 k2
-  const int o_re = stage_idx(lane, r), o_im = stage_idx(241 + lane, r);
-  const int o_pre = stage_idx(240 - lane, r), o_pim = stage_idx(481 - lane, r);
+  const int o_re = stage_idx(lane, r);           // bin k = lane + 16 k2 -> + 256 floats per k2
 
-  // XM slices of `tile` -> staging tile `buf` (all threads; 16-byte async copies)
+  // XM slices of `tile` -> staging tile `buf`: one tensor load per plane (thread 0).  The tensor map is bounded by
+  // m_valid bins and C*Kp positions; everything outside is zero filled, and the full box always counts for the mbarrier.
   auto prefetch = [&](int tile, int buf) {
     float* st = reinterpret_cast<float*>(smp2 + buf * kStageTileBytes);
     const int b = tile / tiles_per_b;
     const int f0 = (tile - b * tiles_per_b) * kRows;
-    const int q = tid & 3;
-    const bool fok = f0 + 4 * q < flat;
-    const long long gstep = 64LL * RS * Kp;
-#pragma unroll
-    for (int reim = 0; reim < 2; ++reim) {
-      const float* gp = xm + ((long long)(tid >> 2) * RS + (long long)(b * 2 + reim) * Cp) * Kp + f0 + 4 * q;
-      for (int m = tid >> 2; m < 241; m += 64, gp += gstep) {
-        float* dst = st + stage_chunk(reim * 241 + m, q);
-        if (m < m_valid && fok) cp_async16(dst, gp);
-        else *reinterpret_cast<float4*>(dst) = make_float4(0.f, 0.f, 0.f, 0.f);
-      }
-    }
-    cp_async_commit();
+    mbar_arrive_expect_tx(&full[buf], 2u * 241u * 64u);
+    tma_load_3d(st, &xm_map, &full[buf], f0, 2 * b, 0);
+    tma_load_3d(st + kPlaneFloats, &xm_map, &full[buf], f0, 2 * b + 1, 0);
   };
 
-  if (blockIdx.x < ntiles) prefetch(blockIdx.x, 0);
-  __syncthreads();                               // tables visible
+  if (tid == 0 && blockIdx.x < ntiles) prefetch(blockIdx.x, 0);
 
   int it = 0;
   for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
     const int cur = (NST == 2) ? (it & 1) : 0;
+    const uint32_t parity = (NST == 2) ? ((uint32_t)(it >> 1) & 1u) : ((uint32_t)it & 1u);
     const int b = tile / tiles_per_b;
     const int f0 = (tile - b * tiles_per_b) * kRows;
     const int nt = tile + gridDim.x;
-    cp_async_wait0();
     if (tid < 32) bulk_wait_read0();             // row buffer of the previous tile has been read by the bulk stores
-    __syncthreads();
-    if (NST == 2 && nt < ntiles) prefetch(nt, cur ^ 1);
+    __syncthreads();                             // ... and everybody is done with the other staging tile (FFT work buffer)
+    if (NST == 2 && tid == 0 && nt < ntiles) prefetch(nt, cur ^ 1);
+    mbar_wait(&full[cur], parity);
     const float* st = reinterpret_cast<const float*>(smp2 + cur * kStageTileBytes);
     fl::cf* work = reinterpret_cast<fl::cf*>(smp2 + cur * kStageTileBytes);
     T* myrow = reinterpret_cast<T*>(rows + r * S::kRowBytes);
     auto storez = [&](int n, int rr, fl::cf z) { store_pair<R, T>(myrow, n, rr, z); };
 
-    if constexpr (R == 1) {
-      fl::cf V[15];
+    // this lane's bins k = lane + 16 k2 (scaled); the partner bins 240 - k come from lane 16 - k1 by shuffle
+    // (register 14 - k2), lane 0 pairs its own registers (k2 <-> 15 - k2) and bin 0 with the extra bin 240
+    fl::cf H[15], HP[15];
 #pragma unroll
-      for (int k2 = 0; k2 < 15; ++k2) {
-        const InvC c = ic[lane + 16 * k2];
-        fl::cf h = fl::mk(st[o_re + 256 * k2] * c.s0, st[o_im + 256 * k2] * c.s0);
-        fl::cf hp = fl::mk(st[o_pre - 256 * k2] * c.s1, st[o_pim - 256 * k2] * c.s1);
-        if (k2 == 0) fp::irfft_twist<1>(0, lane, h, hp, tw + 481);
-        V[k2] = fp::irfft480_prep(h, hp, fl::mk(c.wx, c.wy));
-      }
-      __syncthreads();                           // staging tile consumed: it now serves as the FFT work buffer
-      fp::irfft_row<1>(warp, [&](int, int k2) { return V[k2]; }, work + r * 240, storez, tw);
-    } else {
-      fl::cf H[15], HP[15];
-#pragma unroll
-      for (int k2 = 0; k2 < 15; ++k2) {
-        const InvC c = ic[lane + 16 * k2];
-        H[k2] = fl::mk(st[o_re + 256 * k2] * c.s0, st[o_im + 256 * k2] * c.s0);
-        HP[k2] = fl::mk(st[o_pre - 256 * k2] * c.s1, st[o_pim - 256 * k2] * c.s1);
-      }
-      __syncthreads();
-      fp::irfft_row<R>(warp, [&](int rr, int k2) {
-        const int k = lane + 16 * k2;
-        fl::cf h = H[k2], hp = HP[k2];
-        fp::irfft_twist<R>(rr, k, h, hp, tw + 481);
-        return fp::irfft480_prep(h, hp, tw[240 + k]);
-      }, work + r * 240, storez, tw);
+    for (int k2 = 0; k2 < 15; ++k2) {
+      const float s0 = msc[lane + 16 * k2];
+      H[k2] = fl::mk(st[o_re + 256 * k2] * s0, st[kPlaneFloats + o_re + 256 * k2] * s0);
     }
+    const float s240 = msc[240];
+    const fl::cf h240 = fl::mk(st[3840 + r] * s240, st[kPlaneFloats + 3840 + r] * s240);
+#pragma unroll
+    for (int k2 = 0; k2 < 15; ++k2) {
+      const fl::cf hs = fl::mk(warp.shfl_idx(H[14 - k2].x, psrc), warp.shfl_idx(H[14 - k2].y, psrc));
+      const fl::cf h0 = (k2 == 0) ? h240 : H[15 - k2];
+      HP[k2] = (lane == 0) ? h0 : hs;
+    }
+    __syncthreads();                             // staging tile consumed: it now serves as the FFT work buffer
+    fp::irfft_row<R>(warp, [&](int rr, int k2) {
+      const int k = lane + 16 * k2;
+      fl::cf h = H[k2], hp = HP[k2];
+      if (R != 1 || k2 == 0) fp::irfft_twist<R>(rr, k, h, hp, tw + 481);
+      return fp::irfft480_prep(h, hp, tw[240 + k]);
+    }, work + r * 240, storez, tw);
     fence_proxy_async();                         // generic-proxy row writes -> visible to the bulk (async proxy) stores
     __syncthreads();
-    if (NST == 1 && nt < ntiles) prefetch(nt, 0);
+    if (NST == 1 && tid == 0 && nt < ntiles) prefetch(nt, 0);
     if (tid < 32) {
       const int f = f0 + tid;
       const int c = f / Kp, lat = f - c * Kp;
@@ -348,7 +339,6 @@ dft_inv_p2_kernel(const float* __restrict__ xm, T* __restrict__ y, const fl::cf*
       bulk_commit();
     }
   }
-  cp_async_wait0();
   if (tid < 32) bulk_wait_read0();
 }
 
@@ -360,27 +350,23 @@ static int launch_fwd_p2(const void* x, int B, int C, int K, int Kp, int M, cons
   constexpr int NBUF = (R == 3 && sizeof(T) == 2) ? 1 : 2;
   using S = P2FwdSmem<R, T, NBUF>;
   static_assert(S::kBytes <= 227 * 1024, "forward DFT tile does not fit shared memory");
+  constexpr int OCC = S::kCtasPerSm;
   const fl::cf* tables;
   if (get_p2_tables(&tables)) return 1;
-  constexpr int OCC = S::kCtasPerSm;
-  constexpr int OCC2 = OCC > 1 ? OCC - 1 : 1;        // experiment knob: SFNO_P2_OCC=low trades occupancy for registers
+  CUtensorMap map;
+  if (xm_stage_map(&map, xm, B, C, Kp, M)) return 1;
   static bool attr = false;
   if (!attr) {
     SFNO_CUDA(cudaFuncSetAttribute(dft_fwd_p2_kernel<R, T, NBUF, true, OCC>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kBytes));
     SFNO_CUDA(cudaFuncSetAttribute(dft_fwd_p2_kernel<R, T, NBUF, false, OCC>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kBytes));
-    SFNO_CUDA(cudaFuncSetAttribute(dft_fwd_p2_kernel<R, T, NBUF, true, OCC2>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kBytes));
     attr = true;
   }
   const int ntiles = ((C * Kp + kRows - 1) / kRows) * B;
-  const char* env = getenv("SFNO_P2_OCC");
-  const bool low = env && env[0] == 'l';
-  const int grid = std::min(ntiles, (low ? OCC2 : OCC) * sm_count());
-  if (low && round_out)
-    dft_fwd_p2_kernel<R, T, NBUF, true, OCC2><<<grid, 256, S::kBytes, stream>>>(static_cast<const T*>(x), xm, tables, mscale, B, C, K, Kp, M);
-  else if (round_out)
-    dft_fwd_p2_kernel<R, T, NBUF, true, OCC><<<grid, 256, S::kBytes, stream>>>(static_cast<const T*>(x), xm, tables, mscale, B, C, K, Kp, M);
+  const int grid = std::min(ntiles, OCC * sm_count());
+  if (round_out)
+    dft_fwd_p2_kernel<R, T, NBUF, true, OCC><<<grid, 256, S::kBytes, stream>>>(static_cast<const T*>(x), map, tables, mscale, B, C, K, Kp, M);
   else
-    dft_fwd_p2_kernel<R, T, NBUF, false, OCC><<<grid, 256, S::kBytes, stream>>>(static_cast<const T*>(x), xm, tables, mscale, B, C, K, Kp, M);
+    dft_fwd_p2_kernel<R, T, NBUF, false, OCC><<<grid, 256, S::kBytes, stream>>>(static_cast<const T*>(x), map, tables, mscale, B, C, K, Kp, M);
   SFNO_LAUNCHED();
   return 0;
 }
@@ -393,6 +379,8 @@ static int launch_inv_p2(const float* xm, int B, int C, int K, int Kp, int M, in
   static_assert(S::kBytes <= 227 * 1024, "inverse DFT tile does not fit shared memory");
   const fl::cf* tables;
   if (get_p2_tables(&tables)) return 1;
+  CUtensorMap map;
+  if (xm_stage_map(&map, xm, B, C, Kp, std::max(1, std::min(M, m_valid)))) return 1;
   static bool attr = false;
   if (!attr) {
     SFNO_CUDA(cudaFuncSetAttribute(dft_inv_p2_kernel<R, T, NST>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kBytes));
@@ -400,7 +388,7 @@ static int launch_inv_p2(const float* xm, int B, int C, int K, int Kp, int M, in
   }
   const int ntiles = ((C * Kp + kRows - 1) / kRows) * B;
   const int grid = std::min(ntiles, S::kCtasPerSm * sm_count());
-  dft_inv_p2_kernel<R, T, NST><<<grid, 256, S::kBytes, stream>>>(xm, static_cast<T*>(y), tables, mscale, B, C, K, Kp, M, m_valid);
+  dft_inv_p2_kernel<R, T, NST><<<grid, 256, S::kBytes, stream>>>(map, static_cast<T*>(y), tables, mscale, B, C, K, Kp, std::min(M, m_valid));
   SFNO_LAUNCHED();
   return 0;
 }

@@ -48,7 +48,9 @@ int encode_tensor_map(CUtensorMap* map, const void* gptr, int rank, const uint64
   SFNO_CHECK((reinterpret_cast<uintptr_t>(gptr) & 15) == 0, "TMA global address must be 16-byte aligned");
   CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, (cuuint32_t)rank, const_cast<void*>(gptr), d, s, b, e,
                   CU_TENSOR_MAP_INTERLEAVE_NONE,
-                  swizzle == 1 ? CU_TENSOR_MAP_SWIZZLE_128B : (swizzle == 2 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_NONE),
+                  swizzle == 1 ? CU_TENSOR_MAP_SWIZZLE_128B
+                               : (swizzle == 2 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B
+                                               : (swizzle == 3 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_NONE)),
                   CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   SFNO_CHECK(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with code " + std::to_string((int)r));
   return 0;

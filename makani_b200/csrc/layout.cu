@@ -116,50 +116,95 @@ __global__ void c64_to_xm_kernel(const float2* __restrict__ in, float* __restric
 }
 
 // ------------------------------------------------------------------ dhconv weights  w[Cin][Cout][L] c64 <-> WP[L][2][Coutp][Cinp]
-// grid (ceil(L/32), ceil(Cin/32), Cout), block (32, 8)
-__global__ void pack_weight_kernel(const float2* __restrict__ w, float* __restrict__ wp, int Cin, int Cout, int L) {
-  __shared__ float tr[32][33], ti[32][33];
+// A 283 MB transpose of the slowest and the fastest dimension (per block of the model, every step).  One CTA moves a
+// 64 (i) x 64 (l) tile of one output channel o through shared memory: the complex side is accessed in 512-byte runs
+// (64 consecutive degrees), the planar side in 256-byte runs (64 consecutive input channels, 16-byte vectors), and
+// every thread keeps 16 independent 8-byte (or 8 x 16-byte) loads in flight.
+// grid (ceil(L/64), ceil(Cinp/64), Cout), block 256
+constexpr int kWT = 64;
+// shared tile element (i, l) lives at [i][l ^ (i >> 2)]: conflict free both for lanes along l (fixed i) and for
+// lanes along i in steps of 4 (fixed l)
+__device__ __forceinline__ int wsw(int i, int l) { return l ^ (i >> 2); }
+
+__global__ void __launch_bounds__(256)
+pack_weight_kernel(const float2* __restrict__ w, float* __restrict__ wp, int Cin, int Cout, int L) {
+  __shared__ float tr[kWT][kWT], ti[kWT][kWT];
   const int Cinp = (Cin + 3) & ~3, Coutp = (Cout + 3) & ~3;
   const int o = blockIdx.z;
-  const int l0 = blockIdx.x * 32, i0 = blockIdx.y * 32;
-  for (int j = threadIdx.y; j < 32; j += 8) {
-    const int i = i0 + j, l = l0 + threadIdx.x;
-    float2 v = make_float2(0.f, 0.f);
-    if (i < Cin && l < L) v = w[((long long)i * Cout + o) * L + l];
-    tr[j][threadIdx.x] = v.x;
-    ti[j][threadIdx.x] = v.y;
+  const int l0 = blockIdx.x * kWT, i0 = blockIdx.y * kWT;
+  const int tid = threadIdx.x;
+  {
+    const int ll = tid & 63, ib = tid >> 6;           // 64 degrees x 4 rows per pass
+    float2 v[16];
+#pragma unroll
+    for (int p = 0; p < 16; ++p) {
+      const int i = i0 + ib + 4 * p, l = l0 + ll;
+      v[p] = (i < Cin && l < L) ? w[((long long)i * Cout + o) * L + l] : make_float2(0.f, 0.f);
+    }
+#pragma unroll
+    for (int p = 0; p < 16; ++p) {
+      tr[ib + 4 * p][wsw(ib + 4 * p, ll)] = tf32_rn(v[p].x);   // operands of TF32 GEMMs: pre-rounded (pads are exact zeros)
+      ti[ib + 4 * p][wsw(ib + 4 * p, ll)] = tf32_rn(v[p].y);
+    }
   }
   __syncthreads();
-  for (int j = threadIdx.y; j < 32; j += 8) {
-    const int l = l0 + j, i = i0 + threadIdx.x;
-    if (l < L && i < Cinp) {
-      const long long base = (((long long)l * 2) * Coutp + o) * Cinp + i;
-      wp[base] = (i < Cin) ? tf32_rn(tr[threadIdx.x][j]) : 0.f;
-      wp[base + (long long)Coutp * Cinp] = (i < Cin) ? tf32_rn(ti[threadIdx.x][j]) : 0.f;
+  {
+    const int iq = (tid & 15) * 4, lb = tid >> 4;     // 16 lanes x float4 = 64 channels, 16 (l, re/im) rows per pass
+    const bool iok = i0 + iq < Cinp;                  // Cinp is a multiple of 4: a vector is entirely in or out
+#pragma unroll
+    for (int p = 0; p < 8; ++p) {
+      const int row = lb + 16 * p;                    // 0..127: row = 2 * l_local + reim
+      const int ll = row >> 1, reim = row & 1;
+      const int l = l0 + ll;
+      float (*t)[kWT] = reim ? ti : tr;
+      const int cl = wsw(iq, ll);                     // iq .. iq+3 share i >> 2
+      const float4 v = make_float4(t[iq][cl], t[iq + 1][cl], t[iq + 2][cl], t[iq + 3][cl]);
+      if (iok && l < L)
+        *reinterpret_cast<float4*>(wp + (((long long)l * 2 + reim) * Coutp + o) * Cinp + i0 + iq) = v;
     }
   }
 }
 
-__global__ void unpack_wgrad_kernel(const float* __restrict__ gwp, float2* __restrict__ gw, int Cin, int Cout, int L) {
-  __shared__ float tr[32][33], ti[32][33];
+__global__ void __launch_bounds__(256)
+unpack_wgrad_kernel(const float* __restrict__ gwp, float2* __restrict__ gw, int Cin, int Cout, int L) {
+  __shared__ float tr[kWT][kWT], ti[kWT][kWT];
   const int Cinp = (Cin + 3) & ~3, Coutp = (Cout + 3) & ~3;
   const int o = blockIdx.z;
-  const int l0 = blockIdx.x * 32, i0 = blockIdx.y * 32;
-  for (int j = threadIdx.y; j < 32; j += 8) {
-    const int l = l0 + j, i = i0 + threadIdx.x;
-    float re = 0.f, im = 0.f;
-    if (l < L && i < Cin) {
-      const long long base = (((long long)l * 2) * Coutp + o) * Cinp + i;
-      re = gwp[base];
-      im = gwp[base + (long long)Coutp * Cinp];
+  const int l0 = blockIdx.x * kWT, i0 = blockIdx.y * kWT;
+  const int tid = threadIdx.x;
+  {
+    const int iq = (tid & 15) * 4, lb = tid >> 4;
+    const bool iok = i0 + iq < Cinp;
+    float4 v[8];
+#pragma unroll
+    for (int p = 0; p < 8; ++p) {
+      const int row = lb + 16 * p;
+      const int l = l0 + (row >> 1), reim = row & 1;
+      v[p] = (iok && l < L)
+                 ? *reinterpret_cast<const float4*>(gwp + (((long long)l * 2 + reim) * Coutp + o) * Cinp + i0 + iq)
+                 : make_float4(0.f, 0.f, 0.f, 0.f);
     }
-    tr[j][threadIdx.x] = re;
-    ti[j][threadIdx.x] = im;
+#pragma unroll
+    for (int p = 0; p < 8; ++p) {
+      const int row = lb + 16 * p;
+      const int ll = row >> 1, reim = row & 1;
+      float (*t)[kWT] = reim ? ti : tr;
+      const int cl = wsw(iq, ll);
+      t[iq][cl] = v[p].x;
+      t[iq + 1][cl] = v[p].y;
+      t[iq + 2][cl] = v[p].z;
+      t[iq + 3][cl] = v[p].w;
+    }
   }
   __syncthreads();
-  for (int j = threadIdx.y; j < 32; j += 8) {
-    const int i = i0 + j, l = l0 + threadIdx.x;
-    if (i < Cin && l < L) gw[((long long)i * Cout + o) * L + l] = make_float2(tr[threadIdx.x][j], ti[threadIdx.x][j]);
+  {
+    const int ll = tid & 63, ib = tid >> 6;
+#pragma unroll
+    for (int p = 0; p < 16; ++p) {
+      const int i = i0 + ib + 4 * p, l = l0 + ll;
+      if (i < Cin && l < L) gw[((long long)i * Cout + o) * L + l] =
+            make_float2(tr[ib + 4 * p][wsw(ib + 4 * p, ll)], ti[ib + 4 * p][wsw(ib + 4 * p, ll)]);
+    }
   }
 }
 
@@ -306,14 +351,14 @@ int sfno_c64_to_xm(const void* in_c64, int B, int C, int nlat, int mmax, float* 
 }
 int sfno_dhconv_pack_weight(const void* w_c64, int Cin, int Cout, int L, float* wp, void* stream) {
   const int Cinp = (Cin + 3) & ~3;
-  dim3 grid((L + 31) / 32, (Cinp + 31) / 32, Cout), block(32, 8);
-  pack_weight_kernel<<<grid, block, 0, (cudaStream_t)stream>>>((const float2*)w_c64, wp, Cin, Cout, L);
+  dim3 grid((L + kWT - 1) / kWT, (Cinp + kWT - 1) / kWT, Cout);
+  pack_weight_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const float2*)w_c64, wp, Cin, Cout, L);
   SFNO_LAUNCHED();
   return 0;
 }
 int sfno_dhconv_unpack_wgrad(const float* gwp, int Cin, int Cout, int L, void* gw_c64, void* stream) {
-  dim3 grid((L + 31) / 32, (Cin + 31) / 32, Cout), block(32, 8);
-  unpack_wgrad_kernel<<<grid, block, 0, (cudaStream_t)stream>>>(gwp, (float2*)gw_c64, Cin, Cout, L);
+  dim3 grid((L + kWT - 1) / kWT, (Cin + kWT - 1) / kWT, Cout);
+  unpack_wgrad_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(gwp, (float2*)gw_c64, Cin, Cout, L);
   SFNO_LAUNCHED();
   return 0;
 }

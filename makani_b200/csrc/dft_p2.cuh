@@ -108,7 +108,7 @@ template <int R, typename T, int NBUF, bool ROUND, int OCC>
 __global__ void __launch_bounds__(256, OCC)
 dft_fwd_p2_kernel(const T* __restrict__ x, const __grid_constant__ CUtensorMap xm_map,
                   const fl::cf* __restrict__ tables, const float* __restrict__ mscale, int B, int C, int K, int Kp,
-                  int M) {
+                  int M, int* __restrict__ sched) {
   using S = P2FwdSmem<R, T, NBUF>;
   constexpr int W = S::W;
   extern __shared__ uint8_t smp2_raw[];
@@ -119,6 +119,7 @@ dft_fwd_p2_kernel(const T* __restrict__ x, const __grid_constant__ CUtensorMap x
   fl::cf* tw = reinterpret_cast<fl::cf*>(smp2 + S::kOffTw);
   float* hs = reinterpret_cast<float*>(smp2 + S::kOffSc);      // half of the output scale of bin m (0 for m >= M)
   uint64_t* full = reinterpret_cast<uint64_t*>(smp2 + S::kOffBar);
+  volatile int* tq = reinterpret_cast<volatile int*>(full + 2);   // ring of claimed tile indices (-1: no more work)
 
   const int tid = threadIdx.x;
   for (int j = tid; j < kTwCount; j += 256) tw[j] = tables[j];
@@ -159,15 +160,24 @@ dft_fwd_p2_kernel(const T* __restrict__ x, const __grid_constant__ CUtensorMap x
     if (valid) bulk_g2s(dst, x + ((long long)(b * C + c) * K + lat) * W, S::kRowBytes, &full[buf]);
   };
 
+  // tiles are claimed from a global counter (a CTA that starts late - SMs shared with NCCL kernels - just takes fewer);
+  // warp 0 claims tile it+NBUF while tile it is transformed and starts its row copies
+  auto claim = [&](int slot, int buf) {          // all 32 lanes of warp 0
+    int t = 0;
+    if ((tid & 31) == 0) t = atomicAdd(sched, 1);
+    t = __shfl_sync(0xffffffffu, t, 0);
+    if (t >= ntiles) t = -1;
+    if ((tid & 31) == 0) tq[slot] = t;
+    if (t >= 0) issue(t, buf);
+  };
   if (tid < 32) {
-    for (int j = 0; j < NBUF; ++j) {
-      const int t = blockIdx.x + j * gridDim.x;
-      if (t < ntiles) issue(t, j);
-    }
+    for (int j = 0; j < NBUF; ++j) claim(j, j);
   }
+  __syncthreads();
 
-  int it = 0;
-  for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+  for (int it = 0;; ++it) {
+    const int tile = tq[it & 3];
+    if (tile < 0) break;
     const int buf = it % NBUF;
     const uint32_t parity = (uint32_t)(it / NBUF) & 1u;
     const int b = tile / tiles_per_b;
@@ -183,10 +193,7 @@ dft_fwd_p2_kernel(const T* __restrict__ x, const __grid_constant__ CUtensorMap x
       fl::cf Z[15];
       fp::fft240p_fwd(warp, [&](int n) { return load_pair<1, T>(myrow, n, 0); }, work + r * 240, tw, Z);
       __syncthreads();                          // raw[buf] consumed by every row; work no longer read
-      if (tid < 32) {
-        const int nt = tile + NBUF * gridDim.x;
-        if (nt < ntiles) issue(nt, buf);
-      }
+      if (tid < 32) claim((it + NBUF) & 3, buf);
       const float nyq = fp::rfft480_split(warp, Z, [&](int k2, fl::cf v) {
         const float sc = hs[lane + 16 * k2];
         st_re[k2 * 256] = fin(v.x, sc);
@@ -201,10 +208,7 @@ dft_fwd_p2_kernel(const T* __restrict__ x, const __grid_constant__ CUtensorMap x
       fp::rfft_row_fwd<R>(warp, [&](int n, int rr) { return load_pair<R, T>(myrow, n, rr); }, work + r * 240, X, x240,
                           tw, tw + 240, tw + 481);
       __syncthreads();
-      if (tid < 32) {
-        const int nt = tile + NBUF * gridDim.x;
-        if (nt < ntiles) issue(nt, buf);
-      }
+      if (tid < 32) claim((it + NBUF) & 3, buf);
 #pragma unroll
       for (int k2 = 0; k2 < 15; ++k2) {
         const float sc = hs[lane + 16 * k2];
@@ -226,7 +230,14 @@ dft_fwd_p2_kernel(const T* __restrict__ x, const __grid_constant__ CUtensorMap x
       bulk_commit();
     }
   }
-  if (tid == 0) bulk_wait_read0();               // shared memory must outlive the last tensor stores' reads
+  if (tid == 0) {
+    bulk_wait_read0();                           // shared memory must outlive the last tensor stores' reads
+    __threadfence();
+    if (atomicAdd(sched + 1, 1) == (int)gridDim.x - 1) {   // last CTA re-arms the scheduler for the next launch
+      sched[0] = 0;
+      sched[1] = 0;
+    }
+  }
 }
 
 // ================================================================================ inverse
@@ -247,7 +258,7 @@ struct P2InvSmem {
 template <int R, typename T, int NST>
 __global__ void __launch_bounds__(256, P2InvSmem<R, T, NST>::kCtasPerSm)
 dft_inv_p2_kernel(const __grid_constant__ CUtensorMap xm_map, T* __restrict__ y, const fl::cf* __restrict__ tables,
-                  const float* __restrict__ mscale, int B, int C, int K, int Kp, int m_valid) {
+                  const float* __restrict__ mscale, int B, int C, int K, int Kp, int m_valid, int* __restrict__ sched) {
   using S = P2InvSmem<R, T, NST>;
   constexpr int W = S::W;
   extern __shared__ uint8_t smp2_raw[];
@@ -256,6 +267,7 @@ dft_inv_p2_kernel(const __grid_constant__ CUtensorMap xm_map, T* __restrict__ y,
   fl::cf* tw = reinterpret_cast<fl::cf*>(smp2 + S::kOffTw);
   float* msc = reinterpret_cast<float*>(smp2 + S::kOffMsc);
   uint64_t* full = reinterpret_cast<uint64_t*>(smp2 + S::kOffBar);
+  volatile int* tq = reinterpret_cast<volatile int*>(full + 2);   // ring of claimed tile indices (-1: no more work)
 
   const int tid = threadIdx.x;
   for (int j = tid; j < kTwCount; j += 256) tw[j] = tables[j];
@@ -287,18 +299,27 @@ dft_inv_p2_kernel(const __grid_constant__ CUtensorMap xm_map, T* __restrict__ y,
     tma_load_3d(st + kPlaneFloats, &xm_map, &full[buf], f0, 2 * b + 1, 0);
   };
 
-  if (tid == 0 && blockIdx.x < ntiles) prefetch(blockIdx.x, 0);
+  // thread 0 claims the next tile from the global counter and starts its tensor loads
+  auto claim = [&](int slot, int buf) {
+    int t = atomicAdd(sched, 1);
+    if (t >= ntiles) t = -1;
+    tq[slot] = t;
+    if (t >= 0) prefetch(t, buf);
+  };
+  if (tid == 0) claim(0, 0);
+  __syncthreads();
 
-  int it = 0;
-  for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+  for (int it = 0;; ++it) {
+    if (tid < 32) bulk_wait_read0();             // row buffer of the previous tile has been read by the bulk stores
+    __syncthreads();                             // ... and everybody is done with the other staging tile (FFT work buffer);
+                                                 // also orders thread 0's tq write (NST == 1: made after the last barrier)
+    const int tile = tq[it & 3];
+    if (tile < 0) break;
     const int cur = (NST == 2) ? (it & 1) : 0;
     const uint32_t parity = (NST == 2) ? ((uint32_t)(it >> 1) & 1u) : ((uint32_t)it & 1u);
     const int b = tile / tiles_per_b;
     const int f0 = (tile - b * tiles_per_b) * kRows;
-    const int nt = tile + gridDim.x;
-    if (tid < 32) bulk_wait_read0();             // row buffer of the previous tile has been read by the bulk stores
-    __syncthreads();                             // ... and everybody is done with the other staging tile (FFT work buffer)
-    if (NST == 2 && tid == 0 && nt < ntiles) prefetch(nt, cur ^ 1);
+    if (NST == 2 && tid == 0) claim((it + 1) & 3, cur ^ 1);
     mbar_wait(&full[cur], parity);
     const float* st = reinterpret_cast<const float*>(smp2 + cur * kStageTileBytes);
     fl::cf* work = reinterpret_cast<fl::cf*>(smp2 + cur * kStageTileBytes);
@@ -330,7 +351,7 @@ dft_inv_p2_kernel(const __grid_constant__ CUtensorMap xm_map, T* __restrict__ y,
     }, work + r * 240, storez, tw);
     fence_proxy_async();                         // generic-proxy row writes -> visible to the bulk (async proxy) stores
     __syncthreads();
-    if (NST == 1 && tid == 0 && nt < ntiles) prefetch(nt, 0);
+    if (NST == 1 && tid == 0) claim((it + 1) & 3, 0);
     if (tid < 32) {
       const int f = f0 + tid;
       const int c = f / Kp, lat = f - c * Kp;
@@ -340,6 +361,13 @@ dft_inv_p2_kernel(const __grid_constant__ CUtensorMap xm_map, T* __restrict__ y,
     }
   }
   if (tid < 32) bulk_wait_read0();
+  if (tid == 0) {
+    __threadfence();
+    if (atomicAdd(sched + 1, 1) == (int)gridDim.x - 1) {
+      sched[0] = 0;
+      sched[1] = 0;
+    }
+  }
 }
 
 // ================================================================================ host launchers
@@ -363,10 +391,12 @@ static int launch_fwd_p2(const void* x, int B, int C, int K, int Kp, int M, cons
   }
   const int ntiles = ((C * Kp + kRows - 1) / kRows) * B;
   const int grid = std::min(ntiles, OCC * sm_count());
+  int* sched = sched_counters();
+  SFNO_CHECK(sched != nullptr, "could not allocate the tile scheduler counters");
   if (round_out)
-    dft_fwd_p2_kernel<R, T, NBUF, true, OCC><<<grid, 256, S::kBytes, stream>>>(static_cast<const T*>(x), map, tables, mscale, B, C, K, Kp, M);
+    dft_fwd_p2_kernel<R, T, NBUF, true, OCC><<<grid, 256, S::kBytes, stream>>>(static_cast<const T*>(x), map, tables, mscale, B, C, K, Kp, M, sched);
   else
-    dft_fwd_p2_kernel<R, T, NBUF, false, OCC><<<grid, 256, S::kBytes, stream>>>(static_cast<const T*>(x), map, tables, mscale, B, C, K, Kp, M);
+    dft_fwd_p2_kernel<R, T, NBUF, false, OCC><<<grid, 256, S::kBytes, stream>>>(static_cast<const T*>(x), map, tables, mscale, B, C, K, Kp, M, sched);
   SFNO_LAUNCHED();
   return 0;
 }
@@ -388,7 +418,9 @@ static int launch_inv_p2(const float* xm, int B, int C, int K, int Kp, int M, in
   }
   const int ntiles = ((C * Kp + kRows - 1) / kRows) * B;
   const int grid = std::min(ntiles, S::kCtasPerSm * sm_count());
-  dft_inv_p2_kernel<R, T, NST><<<grid, 256, S::kBytes, stream>>>(map, static_cast<T*>(y), tables, mscale, B, C, K, Kp, std::min(M, m_valid));
+  int* sched = sched_counters();
+  SFNO_CHECK(sched != nullptr, "could not allocate the tile scheduler counters");
+  dft_inv_p2_kernel<R, T, NST><<<grid, 256, S::kBytes, stream>>>(map, static_cast<T*>(y), tables, mscale, B, C, K, Kp, std::min(M, m_valid), sched);
   SFNO_LAUNCHED();
   return 0;
 }

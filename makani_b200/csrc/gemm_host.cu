@@ -147,10 +147,33 @@ static void set_policies(GemmArgs& a, bool keep_a, bool keep_b, bool keep_out, b
   if (stream_out) a.pol_out = kL2EvictFirst;
 }
 
+// Dynamic tile scheduler state: a pool of {next tile, finished CTAs} counter pairs on the device, used round-robin by
+// successive launches.  A kernel finds its pair zeroed and its last CTA zeroes it again, so no memset is enqueued
+// (calls stay CUDA-graph capturable); 64 pairs keep launches that may overlap on different streams apart.
+int* sched_counters() {
+  static std::map<int, int*> pool;
+  static std::map<int, unsigned> next;
+  static std::mutex mu;
+  std::lock_guard<std::mutex> lock(mu);
+  int dev = 0;
+  cudaGetDevice(&dev);
+  auto it = pool.find(dev);
+  if (it == pool.end()) {
+    int* p = nullptr;
+    if (cudaMalloc(&p, 64 * 2 * sizeof(int)) != cudaSuccess) return nullptr;
+    cudaMemset(p, 0, 64 * 2 * sizeof(int));
+    it = pool.emplace(dev, p).first;
+    next[dev] = 0;
+  }
+  return it->second + 2 * (next[dev]++ % 64);
+}
+
 template <int MODE>
-static int launch(const CUtensorMap& ma, const CUtensorMap& mb, const GemmArgs& args, cudaStream_t stream) {
+static int launch(const CUtensorMap& ma, const CUtensorMap& mb, GemmArgs args, cudaStream_t stream) {
   using Cfg = GemmCfg<MODE>;
   if (args.num_tiles == 0) return 0;
+  args.sched = sched_counters();
+  SFNO_CHECK(args.sched != nullptr, "could not allocate the tile scheduler counters");
   SFNO_CHECK(args.out_col_stride > 0 && args.out_col_stride < (1LL << 31) / 32,
              "output column stride too large for the 32-bit epilogue addressing (reduce batch*channels)");
   static bool attr_set = false;

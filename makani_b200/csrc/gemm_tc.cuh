@@ -10,8 +10,9 @@
 //   roles   warp 0: TMA producer (one lane)     warp 1: tcgen05.mma issuer (one lane)
 //           warp 2: TMEM allocator              warps 4-7: epilogue (TMEM -> registers -> coalesced st.global)
 //   pipes   smem ring  full[]/empty[]  (TMA <-> MMA),  TMEM double buffer  tmem_full[]/tmem_empty[] (MMA <-> epilogue)
-//   tiles   host-built, cost-sorted tile list (triangular l >= m structure is skipped at 16/8 granularity);
-//           CTA c processes tiles c, c+grid, ...
+//   tiles   host-built, cost-sorted tile list (triangular l >= m structure is skipped at 16/8 granularity), handed out
+//           through a global atomic counter: the producer warp claims the next tile and publishes it to the MMA and
+//           epilogue warps through a small ring, so CTAs that start late (SMs shared with NCCL) just take less
 //
 //   D is always stored "row contiguous": TMEM lane == output row == fastest memory index, so each
 //   st.global of a warp writes 128 contiguous bytes without staging through shared memory.
@@ -43,6 +44,7 @@ struct GemmArgs {
   long long out_im_offset;  // complex modes: offset of the imaginary plane
   int round_out;            // 1: store round-to-nearest TF32 values (the consumer is another TF32 GEMM)
   unsigned long long pol_a, pol_b, pol_out;   // L2 cache policies of the two operand streams and of the output
+  int* sched;               // [0] next tile (dynamic scheduler), [1] finished CTAs; both zero at launch, reset by the last CTA
 };
 
 template <int MODE>
@@ -61,6 +63,7 @@ struct GemmCfg {
 };
 
 constexpr int kGemmThreads = 256;
+constexpr int kSchedDepth = 4;     // tiles the producer may claim ahead of the slowest consumer warp (power of two)
 
 template <int MODE>
 __global__ void __launch_bounds__(kGemmThreads, 1)
@@ -74,7 +77,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
   uint64_t* empty_bar = bars + Cfg::kStages;
   uint64_t* tmem_full = bars + 2 * Cfg::kStages;
   uint64_t* tmem_empty = tmem_full + 2;
-  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+  uint64_t* sched_full = tmem_empty + 2;
+  uint64_t* sched_empty = sched_full + kSchedDepth;
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(sched_empty + kSchedDepth);
+  volatile int* sched_tile = reinterpret_cast<volatile int*>(tmem_ptr_smem + 1);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -91,6 +97,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
     for (int b = 0; b < 2; ++b) {
       mbar_init(&tmem_full[b], 1);
       mbar_init(&tmem_empty[b], 128);
+    }
+    for (int b = 0; b < kSchedDepth; ++b) {
+      mbar_init(&sched_full[b], 1);
+      mbar_init(&sched_empty[b], 5);             // MMA lane + one lane of each epilogue warp
     }
     fence_barrier_init();
   }
@@ -113,7 +123,16 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int t = blockIdx.x; t < args.num_tiles; t += gridDim.x) {
+      int t_next = atomicAdd(args.sched, 1);
+      for (uint32_t sn = 0;; ++sn) {
+        const int slot = sn & (kSchedDepth - 1);
+        int t = t_next;
+        if (t >= args.num_tiles) t = -1;
+        else t_next = atomicAdd(args.sched, 1);    // claim one tile ahead: the atomic's latency hides behind this tile's loads
+        mbar_wait(&sched_empty[slot], ((sn / kSchedDepth) & 1) ^ 1);
+        sched_tile[slot] = t;
+        mbar_arrive(&sched_full[slot]);
+        if (t < 0) break;
         const GemmTile tile = args.tiles[t];
         if (tile.nkk == 0) continue;
         const int nkb = (tile.nkk + 3) >> 2;
@@ -168,7 +187,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
       int stage = 0;
       uint32_t phase = 0;
       uint32_t acc_it = 0;
-      for (int t = blockIdx.x; t < args.num_tiles; t += gridDim.x) {
+      for (uint32_t sn = 0;; ++sn) {
+        const int slot = sn & (kSchedDepth - 1);
+        mbar_wait(&sched_full[slot], (sn / kSchedDepth) & 1);
+        const int t = sched_tile[slot];
+        mbar_arrive(&sched_empty[slot]);
+        if (t < 0) break;
         const GemmTile tile = args.tiles[t];
         if (tile.nkk == 0) continue;
         const uint32_t buf = acc_it & 1, acc_phase = (acc_it >> 1) & 1;
@@ -230,7 +254,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
     // =========================================================== epilogue
     const int q = warp - 4;                        // TMEM lane quarter of this warp (== warp % 4)
     uint32_t acc_it = 0;
-    for (int t = blockIdx.x; t < args.num_tiles; t += gridDim.x) {
+    for (uint32_t sn = 0;; ++sn) {
+      const int slot = sn & (kSchedDepth - 1);
+      mbar_wait(&sched_full[slot], (sn / kSchedDepth) & 1);
+      const int t = sched_tile[slot];
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&sched_empty[slot]);
+      if (t < 0) break;
       const GemmTile tile = args.tiles[t];
       const int row = tile.row0 + q * 32 + lane;
       const bool row_ok = row < args.row_limit;
@@ -295,6 +325,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
   if (warp == 2) {
     tc_fence_after();
     tmem_dealloc(tmem_base, 512);
+  }
+  if (threadIdx.x == 0) {                        // the last CTA to finish re-arms the scheduler for the next launch
+    __threadfence();
+    if (atomicAdd(args.sched + 1, 1) == (int)gridDim.x - 1) {
+      args.sched[0] = 0;
+      args.sched[1] = 0;
+    }
   }
 }
 

@@ -14,6 +14,7 @@ struct sfno_plan {
 namespace sfno {
 
 int sp_mhi(int l_local, int l_offset, int m_offset, int M_local);
+int* sched_counters();   // {next tile, finished CTAs} pair for one launch of a dynamically scheduled kernel
 
 int legendre_analysis(const sfno_plan* plan, const float* xm, int B, int C, float* sp, int round_out,
                       cudaStream_t stream);

@@ -43,6 +43,8 @@ def _rfft_ref(x64, M, scale):
     (2, 3, 21, 480, 241, torch.bfloat16),
     (1, 4, 18, 1440, 241, torch.float32),     # fft480 R=3
     (1, 3, 17, 1440, 200, torch.float16),
+    (1, 40, 240, 1440, 241, torch.bfloat16),  # 600 tiles: several tiles per CTA (dynamic scheduler, single row buffer)
+    (2, 160, 240, 480, 241, torch.bfloat16),  # 4800 tiles at R=1 (double-buffered rows)
 ])
 def test_dft_fwd(ops, B, C, K, W, M, dtype):
     torch.manual_seed(0)
@@ -67,6 +69,9 @@ def test_dft_fwd(ops, B, C, K, W, M, dtype):
     (1, 4, 18, 1440, 241, torch.float32),
     (1, 3, 17, 1440, 200, torch.float32),
     (1, 4, 16, 480, 241, torch.bfloat16),
+    (1, 40, 240, 1440, 241, torch.bfloat16),  # 600 tiles: several tiles per CTA, single staging tile (NST = 1)
+    (2, 160, 240, 480, 241, torch.bfloat16),  # 4800 tiles at R=1
+    (1, 4, 18, 1440, 241, torch.float16),
 ])
 def test_dft_inv(ops, B, C, K, W, M, dtype):
     torch.manual_seed(1)

@@ -219,6 +219,23 @@ class KernelProfiler:
         return rows
 
 
+def ncu_traffic(kernel, shape):
+    """DRAM bytes per launch of `kernel` from the committed ncu --set full capture (profiles/ncu_traffic.json,
+    built by tools/ncu_traffic.py); None when that kernel / shape was not captured."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            t = json.load(f)
+    except Exception:
+        return None
+    key = kernel
+    if kernel.startswith("dft_"):
+        key = f"{kernel}_{shape.get('W')}"
+    elif kernel.startswith("legendre_"):
+        key = f"{kernel}_{shape.get('K')}"
+    e = t.get(key)
+    return float(e["bytes"]) if e else None
+
+
 def measured_peaks():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
@@ -411,7 +428,8 @@ def run_ours(args):
                     avg_us=round(r["avg_us"], 1), share=round(r["total_ms"] / 3 / step_ms_prof, 3),
                     gbs=round(r["gbs"], 1), frac=round(r["gbs"] / peak, 3)) for r in rows[:12]]
         roofline = {"bound": "hbm", "kernel": dom["kernel"], "shape": dom["shape"], "achieved": dom["gbs"], "peak": peak,
-                    "peak_source": peak_src, "unit": "GB/s", "frac": dom["gbs"] / peak, "traffic": None,
+                    "peak_source": peak_src, "unit": "GB/s", "frac": dom["gbs"] / peak, "traffic": ncu_traffic(dom["kernel"], dom["shape"]),
+                    "alg_bytes": dom["alg_bytes"],
                     "avg_us": dom["avg_us"], "share_of_step": dom["total_ms"] / 3 / step_ms_prof}
         # CPU baseline: bounded sample on the host cores (rank 0, N = 1 only)
         cpu = None

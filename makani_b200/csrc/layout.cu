@@ -197,7 +197,20 @@ unpack_wgrad_kernel(const float* __restrict__ gwp, float2* __restrict__ gw, int 
     }
   }
   __syncthreads();
-  {
+  if ((L & 1) == 0) {
+    // two degrees per thread: 16-byte stores, a warp writes 512 contiguous bytes of one (i, o) row
+    const int lp = (tid & 31) * 2, ib = tid >> 5;
+#pragma unroll
+    for (int p = 0; p < 8; ++p) {
+      const int il = ib + 8 * p;
+      const int i = i0 + il, l = l0 + lp;
+      if (i < Cin && l < L) {                           // L even and l even: l + 1 < L as well
+        const int c0 = wsw(il, lp), c1 = wsw(il, lp + 1);
+        *reinterpret_cast<float4*>(gw + ((long long)i * Cout + o) * L + l) =
+            make_float4(tr[il][c0], ti[il][c0], tr[il][c1], ti[il][c1]);
+      }
+    }
+  } else {
     const int ll = tid & 63, ib = tid >> 6;
 #pragma unroll
     for (int p = 0; p < 16; ++p) {

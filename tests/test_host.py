@@ -65,12 +65,15 @@ def test_library_has_tcgen05_and_tma_sass(built_lib):
     assert "LDTM" in out, "no tcgen05.ld in SASS"
 
 
-def test_fft_lane_host_emulation():
-    exe = os.path.join(ROOT, "tests", "cpp", "fft_lane_host_test.bin")
-    subprocess.run(["g++", "-O2", "-std=c++17", "-pthread", os.path.join(ROOT, "tests", "cpp", "fft_lane_host_test.cpp"),
+@pytest.mark.parametrize("name,token", [("fft_lane_host_test", "FFT_LANE_OK"), ("fft_pass_host_test", "FFT_PASS_OK")])
+def test_fft_host_emulation(name, token):
+    """The per-lane FFT code of the DFT kernels (csrc/fft_lane.cuh: 16-lane shuffle FFT; csrc/fft_pass.cuh: two-pass
+    16 x 15 FFT) compiled for the host, one thread per lane, against a direct double-precision DFT."""
+    exe = os.path.join(ROOT, "tests", "cpp", name + ".bin")
+    subprocess.run(["g++", "-O2", "-std=c++17", "-pthread", os.path.join(ROOT, "tests", "cpp", name + ".cpp"),
                     "-o", exe], check=True)
     r = subprocess.run([exe], capture_output=True, text=True, timeout=300)
-    assert r.returncode == 0 and "FFT_LANE_OK" in r.stdout, r.stdout + r.stderr
+    assert r.returncode == 0 and token in r.stdout, r.stdout + r.stderr
 
 
 def test_module_surface_and_cpu_refusal(built_lib):

@@ -111,8 +111,10 @@ dft_fwd_p2_kernel(const T* __restrict__ x, const __grid_constant__ CUtensorMap x
                   int M, int* __restrict__ sched) {
   using S = P2FwdSmem<R, T, NBUF>;
   constexpr int W = S::W;
-  extern __shared__ uint8_t smp2_raw[];
-  uint8_t* smp2 = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smp2_raw) + 1023) & ~uintptr_t(1023));
+  // 1024-byte aligned base, computed as an OFFSET from the shared array so that every access below stays in the
+  // shared address space (an integer round-trip of the pointer turns them into slower generic LD / ST)
+  extern __shared__ __align__(1024) uint8_t smp2_raw[];
+  uint8_t* smp2 = smp2_raw + ((1024u - (smem_u32(smp2_raw) & 1023u)) & 1023u);
   fl::cf* work = reinterpret_cast<fl::cf*>(smp2);
   float* stage = reinterpret_cast<float*>(smp2);
   uint8_t* raw = smp2 + S::kOffRaw;
@@ -261,8 +263,10 @@ dft_inv_p2_kernel(const __grid_constant__ CUtensorMap xm_map, T* __restrict__ y,
                   const float* __restrict__ mscale, int B, int C, int K, int Kp, int m_valid, int* __restrict__ sched) {
   using S = P2InvSmem<R, T, NST>;
   constexpr int W = S::W;
-  extern __shared__ uint8_t smp2_raw[];
-  uint8_t* smp2 = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smp2_raw) + 1023) & ~uintptr_t(1023));
+  // 1024-byte aligned base, computed as an OFFSET from the shared array so that every access below stays in the
+  // shared address space (an integer round-trip of the pointer turns them into slower generic LD / ST)
+  extern __shared__ __align__(1024) uint8_t smp2_raw[];
+  uint8_t* smp2 = smp2_raw + ((1024u - (smem_u32(smp2_raw) & 1023u)) & 1023u);
   uint8_t* rows = smp2 + S::kOffRows;
   fl::cf* tw = reinterpret_cast<fl::cf*>(smp2 + S::kOffTw);
   float* msc = reinterpret_cast<float*>(smp2 + S::kOffMsc);

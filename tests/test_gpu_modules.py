@@ -185,3 +185,46 @@ def test_full_size_block0_shapes(mk):
     rhs = float((x.detach().double() * x.grad.double()).sum())
     assert abs(lhs - rhs) / abs(lhs) < 5e-3, (lhs, rhs)
     assert torch.isfinite(conv.weight.grad.abs()).all()
+
+
+def test_spectral_conv_cuda_graph_capture(mk):
+    """The reference captures forward + backward of the model in a CUDA graph (makani/utils/trainer.py:84-152).
+    The calls behind SpectralConv only enqueue work (no host sync, no allocation outside torch's caching allocator,
+    tile-scheduler counters re-armed by the kernels themselves), so a warmed-up step must capture and replay
+    bit-identically - on a side stream, as the trainer does."""
+    torch.manual_seed(0)
+    nlat, nlon, C = 60, 480, 24
+    fwd = mk.RealSHT(nlat, nlon, lmax=60, mmax=61, grid="legendre-gauss").to(DEV)
+    inv = mk.InverseRealSHT(nlat, nlon, lmax=60, mmax=61, grid="legendre-gauss").to(DEV)
+    conv = mk.SpectralConv(fwd, inv, C, C, operator_type="dhconv").to(DEV)
+    x = torch.randn(2, C, nlat, nlon, device=DEV).to(torch.bfloat16).requires_grad_(True)
+    gy = torch.randn(2, C, nlat, nlon, device=DEV).to(torch.bfloat16)
+
+    def step():
+        x.grad = None
+        conv.weight.grad = None
+        y, _ = conv(x)
+        torch.autograd.backward([y], [gy])
+        return y
+
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        for _ in range(3):                       # warm-up: plans, tile lists, twiddle tables, allocator pools
+            y_eager = step()
+    torch.cuda.current_stream().wait_stream(s)
+    torch.cuda.synchronize()
+    gx_eager, gw_eager = x.grad.clone(), conv.weight.grad.clone()
+    y_eager = y_eager.detach().clone()
+
+    g = torch.cuda.CUDAGraph()
+    x.grad = None
+    conv.weight.grad = None
+    with torch.cuda.graph(g):
+        y_graph = step()
+    for _ in range(3):                           # replays reuse the captured scheduler counters: they must re-arm
+        g.replay()
+    torch.cuda.synchronize()
+    assert torch.equal(y_graph, y_eager)
+    assert torch.equal(x.grad, gx_eager)
+    assert torch.equal(torch.view_as_real(conv.weight.grad), torch.view_as_real(gw_eager))

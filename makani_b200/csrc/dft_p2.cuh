@@ -347,12 +347,7 @@ dft_inv_p2_kernel(const __grid_constant__ CUtensorMap xm_map, T* __restrict__ y,
       HP[k2] = (lane == 0) ? h0 : hs;
     }
     __syncthreads();                             // staging tile consumed: it now serves as the FFT work buffer
-    fp::irfft_row<R>(warp, [&](int rr, int k2) {
-      const int k = lane + 16 * k2;
-      fl::cf h = H[k2], hp = HP[k2];
-      if (R != 1 || k2 == 0) fp::irfft_twist<R>(rr, k, h, hp, tw + 481);
-      return fp::irfft480_prep(h, hp, tw[240 + k]);
-    }, work + r * 240, storez, tw);
+    fp::irfft_row<R>(warp, H, HP, work + r * 240, storez, tw, tw + 240, tw + 481);
     fence_proxy_async();                         // generic-proxy row writes -> visible to the bulk (async proxy) stores
     __syncthreads();
     if (NST == 1 && tid == 0) claim((it + 1) & 3, 0);

@@ -148,22 +148,19 @@ template <int R, class Warp, class LoadZ>
 FL_HD void rfft_row_fwd(Warp& w, LoadZ loadz, cf* work, cf (&X)[15], cf& x240, const cf* twA, const cf* tw480,
                         const cf* tw1440) {
   const int k1 = w.lane16();
+  // Horner in the sub-sequence index: X = X_0 + t (X_1 + t X_2),  t = w1440^m  - one complex multiply per bin and r
 #pragma unroll
-  for (int r = 0; r < R; ++r) {
+  for (int r = R - 1; r >= 0; --r) {
     cf Z[15];
     fft240p_fwd(w, [&](int n) { return loadz(n, r); }, work, twA, Z);
-    if (r == 0) {
+    if (r == R - 1) {
       const float nyq = rfft480_split(w, Z, [&](int k2, cf v) { X[k2] = v; }, tw480);
       x240 = mk(nyq, 0.f);
     } else {
       const float nyq = rfft480_split(w, Z, [&](int k2, cf v) {
-        const cf t1 = tw1440[k1 + 16 * k2];
-        const cf t = (r == 1) ? t1 : cmul(t1, t1);
-        X[k2] = cadd(X[k2], cmul(t, v));
+        X[k2] = cadd(v, cmul(tw1440[k1 + 16 * k2], X[k2]));
       }, tw480);
-      const cf e1 = tw1440[240];
-      const cf e = (r == 1) ? e1 : cmul(e1, e1);
-      x240 = cadd(x240, cscale(e, nyq));
+      x240 = cadd(mk(nyq, 0.f), cmul(tw1440[240], x240));
     }
   }
 }
@@ -178,29 +175,37 @@ FL_HD cf irfft480_prep(cf h, cf hp, cf w480_k) {
   return mk(ax - py, ay + px);
 }
 
-// The R sub-sequence twist of bin pair (k, 240-k) for nlon = 480 R:  h *= conj(w1440^k)^r, hp *= conj(w1440^(240-k))^r,
-// and the k = 0 pair made real (bin 240 is a true Nyquist bin only for R = 1; otherwise an ordinary, doubled bin).
+// For nlon = 480 R the sub-sequence r of the output needs the spectrum twisted by conj(w1440^k)^r (bin k) and
+// conj(w1440^(240-k))^r (bin 240-k): advance (h, hp) by one step of r.
+FL_HD void irfft_twist_step(int k, cf& h, cf& hp, const cf* tw1440) {
+  h = cmul(h, cconj(tw1440[k]));
+  hp = cmul(hp, cconj(tw1440[240 - k]));
+}
+// The k = 0 pair is made real (bin 240 is a true Nyquist bin only for R = 1; otherwise an ordinary, doubled bin).
 template <int R>
-FL_HD void irfft_twist(int r, int k, cf& h, cf& hp, const cf* tw1440) {
-  if (R != 1 && r > 0) {
-    const cf t1 = cconj(tw1440[k]), u1 = cconj(tw1440[240 - k]);
-    h = cmul(h, r == 1 ? t1 : cmul(t1, t1));
-    hp = cmul(hp, r == 1 ? u1 : cmul(u1, u1));
-  }
+FL_HD void irfft_fix0(int k, cf& h, cf& hp) {
   if (k == 0) {
     h = mk(h.x, 0.f);
     hp = mk((R == 1 ? 1.f : 2.f) * hp.x, 0.f);
   }
 }
 
-// makev(r, k2) returns V[lane + 16 k2] of sub-sequence r (built with irfft_twist + irfft480_prep from the scaled spectrum).
-template <int R, class Warp, class MakeV, class StoreZ>
-FL_HD void irfft_row(Warp& w, MakeV makev, cf* work, StoreZ storez, const cf* twA) {
+// H[k2] / HP[k2]: the (already scaled) spectrum at bins k = lane + 16 k2 and 240 - k; destroyed (twisted in place).
+template <int R, class Warp, class StoreZ>
+FL_HD void irfft_row(Warp& w, cf (&H)[15], cf (&HP)[15], cf* work, StoreZ storez, const cf* twA, const cf* tw480,
+                     const cf* tw1440) {
+  const int k1 = w.lane16();
 #pragma unroll
   for (int r = 0; r < R; ++r) {
     cf V[15];
 #pragma unroll
-    for (int k2 = 0; k2 < 15; ++k2) V[k2] = makev(r, k2);
+    for (int k2 = 0; k2 < 15; ++k2) {
+      const int k = k1 + 16 * k2;
+      if (r > 0) irfft_twist_step(k, H[k2], HP[k2], tw1440);
+      cf h = H[k2], hp = HP[k2];
+      if (k2 == 0) irfft_fix0<R>(k, h, hp);
+      V[k2] = irfft480_prep(h, hp, tw480[k]);
+    }
     fft240p_inv(w, V, work, twA, [&](int n, cf z) { storez(n, r, z); });
   }
 }

@@ -29,6 +29,16 @@ static PFN_encodeTiled get_encode_fn() {
   return fn;
 }
 
+// L2 fetch granularity of TMA loads; SFNO_L2_PROMO = 64 | 128 | 256 (default 128) for A/B measurements
+static CUtensorMapL2promotion l2_promotion() {
+  static int v = -1;
+  if (v < 0) {
+    const char* env = getenv("SFNO_L2_PROMO");
+    v = env ? atoi(env) : 128;
+  }
+  return v == 256 ? CU_TENSOR_MAP_L2_PROMOTION_L2_256B : (v == 64 ? CU_TENSOR_MAP_L2_PROMOTION_L2_64B : CU_TENSOR_MAP_L2_PROMOTION_L2_128B);
+}
+
 int encode_tensor_map(CUtensorMap* map, const void* gptr, int rank, const uint64_t* dims,
                       const uint64_t* strides_bytes, const uint32_t* box, int swizzle) {
   PFN_encodeTiled fn = get_encode_fn();
@@ -51,7 +61,7 @@ int encode_tensor_map(CUtensorMap* map, const void* gptr, int rank, const uint64
                   swizzle == 1 ? CU_TENSOR_MAP_SWIZZLE_128B
                                : (swizzle == 2 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B
                                                : (swizzle == 3 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_NONE)),
-                  CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                  l2_promotion(), CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   SFNO_CHECK(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with code " + std::to_string((int)r));
   return 0;
 }

@@ -123,12 +123,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      int t_next = atomicAdd(args.sched, 1);
+      // first tile: static (blockIdx.x < num_tiles, no atomic on the start-up path); later tiles: claimed from the
+      // counter, one tile ahead so that the atomic's latency hides behind the current tile's loads
+      int t_next = (int)blockIdx.x;
       for (uint32_t sn = 0;; ++sn) {
         const int slot = sn & (kSchedDepth - 1);
         int t = t_next;
         if (t >= args.num_tiles) t = -1;
-        else t_next = atomicAdd(args.sched, 1);    // claim one tile ahead: the atomic's latency hides behind this tile's loads
+        else t_next = (int)gridDim.x + atomicAdd(args.sched, 1);
         mbar_wait(&sched_empty[slot], ((sn / kSchedDepth) & 1) ^ 1);
         sched_tile[slot] = t;
         mbar_arrive(&sched_full[slot]);

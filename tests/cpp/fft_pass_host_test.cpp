@@ -113,13 +113,9 @@ static double run(bool verbose) {
           H[k2] = mk(S[k].real(), S[k].imag());
           HP[k2] = mk(S[240 - k].real(), S[240 - k].imag());
         }
-        fp::irfft_row<R>(w, [&](int r, int k2) {
-                           const int k = lane + 16 * k2;
-                           cf h = H[k2], hp = HP[k2];
-                           fp::irfft_twist<R>(r, k, h, hp, tw1440.data());
-                           return fp::irfft480_prep(h, hp, tw480[k]);
-                         }, work.data(),
-                         [&](int n, int r, cf z) { y[2 * R * n + r] = z.x; y[2 * R * n + R + r] = z.y; }, twA.data());
+        fp::irfft_row<R>(w, H, HP, work.data(),
+                         [&](int n, int r, cf z) { y[2 * R * n + r] = z.x; y[2 * R * n + R + r] = z.y; }, twA.data(),
+                         tw480.data(), tw1440.data());
       });
     for (auto& t : th) t.join();
   }

@@ -4,6 +4,7 @@
 #include "plan.h"
 
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -23,6 +24,15 @@ static float tf32_rn_host(float x) {
 std::atomic<long long> g_launch_count{0};
 
 void set_error(const std::string& msg) { t_last_error = msg; }
+
+bool pdl_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* env = getenv("SFNO_PDL");
+    v = (env && env[0] == '0') ? 0 : 1;
+  }
+  return v == 1;
+}
 
 }  // namespace sfno
 

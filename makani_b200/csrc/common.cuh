@@ -40,6 +40,25 @@ extern std::atomic<long long> g_launch_count;
     SFNO_CUDA(cudaGetLastError());                                                 \
   } while (0)
 
+// Programmatic dependent launch: the kernel may become resident while its predecessor in the stream is still
+// draining (it must call pdl_wait() before touching global data).  SFNO_PDL=0 disables the attribute.
+bool pdl_enabled();
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                              Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 inline int round_up(int x, int m) { return (x + m - 1) / m * m; }
 inline long long round_up_ll(long long x, long long m) { return (x + m - 1) / m * m; }
 
@@ -70,6 +89,12 @@ __device__ __forceinline__ bool elect_one() {
       : "=r"(pred));
   return pred != 0;
 }
+
+// ---- programmatic dependent launch (see launch_pdl)
+// wait: all prerequisite grids have completed and their memory is visible (no-op without the launch attribute);
+// launch_dependents: the next kernel of the stream may start becoming resident as SM resources free up
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
 // ---- mbarrier
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {

@@ -132,6 +132,8 @@ dft_fwd_p2_kernel(const T* __restrict__ x, const __grid_constant__ CUtensorMap x
     fence_barrier_init();
   }
   __syncthreads();
+  pdl_launch_dependents();                       // set-up above overlapped the previous kernel's tail (launch_pdl)
+  pdl_wait();
 
   const int flat = C * Kp;
   const int tiles_per_b = (flat + kRows - 1) / kRows;
@@ -282,6 +284,8 @@ dft_inv_p2_kernel(const __grid_constant__ CUtensorMap xm_map, T* __restrict__ y,
     fence_barrier_init();
   }
   __syncthreads();
+  pdl_launch_dependents();
+  pdl_wait();
 
   const int flat = C * Kp;
   const int tiles_per_b = (flat + kRows - 1) / kRows;
@@ -393,9 +397,11 @@ static int launch_fwd_p2(const void* x, int B, int C, int K, int Kp, int M, cons
   int* sched = sched_counters();
   SFNO_CHECK(sched != nullptr, "could not allocate the tile scheduler counters");
   if (round_out)
-    dft_fwd_p2_kernel<R, T, NBUF, true, OCC><<<grid, 256, S::kBytes, stream>>>(static_cast<const T*>(x), map, tables, mscale, B, C, K, Kp, M, sched);
+    SFNO_CUDA(launch_pdl(dft_fwd_p2_kernel<R, T, NBUF, true, OCC>, dim3(grid), dim3(256), S::kBytes, stream,
+                         static_cast<const T*>(x), map, tables, mscale, B, C, K, Kp, M, sched));
   else
-    dft_fwd_p2_kernel<R, T, NBUF, false, OCC><<<grid, 256, S::kBytes, stream>>>(static_cast<const T*>(x), map, tables, mscale, B, C, K, Kp, M, sched);
+    SFNO_CUDA(launch_pdl(dft_fwd_p2_kernel<R, T, NBUF, false, OCC>, dim3(grid), dim3(256), S::kBytes, stream,
+                         static_cast<const T*>(x), map, tables, mscale, B, C, K, Kp, M, sched));
   SFNO_LAUNCHED();
   return 0;
 }
@@ -419,7 +425,8 @@ static int launch_inv_p2(const float* xm, int B, int C, int K, int Kp, int M, in
   const int grid = std::min(ntiles, S::kCtasPerSm * sm_count());
   int* sched = sched_counters();
   SFNO_CHECK(sched != nullptr, "could not allocate the tile scheduler counters");
-  dft_inv_p2_kernel<R, T, NST><<<grid, 256, S::kBytes, stream>>>(map, static_cast<T*>(y), tables, mscale, B, C, K, Kp, std::min(M, m_valid), sched);
+  SFNO_CUDA(launch_pdl(dft_inv_p2_kernel<R, T, NST>, dim3(grid), dim3(256), S::kBytes, stream, map, static_cast<T*>(y),
+                       tables, mscale, B, C, K, Kp, std::min(M, m_valid), sched));
   SFNO_LAUNCHED();
   return 0;
 }

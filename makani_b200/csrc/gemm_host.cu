@@ -193,7 +193,7 @@ static int launch(const CUtensorMap& ma, const CUtensorMap& mb, GemmArgs args, c
     attr_set = true;
   }
   int grid = std::min(args.num_tiles, num_sms());
-  gemm_tc_kernel<MODE><<<grid, kGemmThreads, Cfg::kSmemBytes, stream>>>(ma, mb, args);
+  SFNO_CUDA(launch_pdl(gemm_tc_kernel<MODE>, dim3(grid), dim3(kGemmThreads), Cfg::kSmemBytes, stream, ma, mb, args));
   SFNO_LAUNCHED();
   return 0;
 }

@@ -112,6 +112,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
+  // everything above overlapped the tail of the previous kernel in the stream (programmatic dependent launch);
+  // from here on global memory written by it is read / buffers it read are overwritten
+  pdl_launch_dependents();
+  pdl_wait();
 
   auto stage_a = [&](int s, int plane) -> uint8_t* { return smem + s * Cfg::kStageBytes + plane * Cfg::kABytes; };
   auto stage_b = [&](int s, int plane) -> uint8_t* {

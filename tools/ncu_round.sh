@@ -14,4 +14,7 @@ ncu --set full --clock-control none --import-source on -c 13 -o gpurun_out/${tag
 python tools/prof_block.py block0 1 > gpurun_out/plain_b1.log 2>&1 &&
 ncu --set full --clock-control none --import-source on -k regex:"dft_|gemm_tc_kernel" -c 10 -o gpurun_out/${tag}_full_block0 -f \
     python tools/prof_block.py block0 1 > gpurun_out/ncu_f_block0.log 2>&1
+python tools/prof_block.py block7 1 > gpurun_out/plain_b7.log 2>&1 &&
+ncu --set full --clock-control none --import-source on -k regex:"dft_inv_p2_kernel|gemm_tc_kernel" -c 6 -o gpurun_out/${tag}_full_block7 -f \
+    python tools/prof_block.py block7 1 > gpurun_out/ncu_f_block7.log 2>&1
 ls -la gpurun_out

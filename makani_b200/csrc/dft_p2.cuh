@@ -1,11 +1,11 @@
 // Longitude DFT kernels for nlon = 480*R built on the two-pass FFT of fft_pass.cuh  (included by dft.cu).
 //
 //   tile      16 consecutive flat positions f = c*Kp + lat of one batch entry; 256 threads = 16 rows x 16 lanes
-//   rows      move with 1-D bulk async copies (cp.async.bulk, one per row, completion on an mbarrier),
-//             double buffered: the rows of tile i+1 (i+2) are in flight while tile i is transformed
+//   rows      move with 1-D bulk async copies (cp.async.bulk, one per row); the rows of tile i+1 are requested as
+//             soon as every warp has read tile i's for the last time
 //   XM side   goes through a swizzled [2*241][16] staging tile so that both the per-lane accesses of the FFT
 //             (lane = bin) and the 16-byte global accesses (4 consecutive latitudes) are (nearly) conflict free
-//   work      the FFT exchange buffer aliases the staging tile (separated by __syncthreads)
+//   work      private FFT exchange row per 16-lane group; the tile loop has no CTA-wide barrier (mbarrier hand-offs)
 #pragma once
 
 namespace sfno {
@@ -245,42 +245,59 @@ dft_fwd_p2_kernel(const T* __restrict__ x, const __grid_constant__ CUtensorMap x
 }
 
 // ================================================================================ inverse
+// shared memory: NST staging tiles | 16 output rows | 16 FFT exchange rows | twiddles | per-bin scale | mbarriers + ring.
+// Every region except the staging tiles is private to one 16-lane group, so the tile loop needs no CTA-wide barrier.
 template <int R, typename T, int NST>
 struct P2InvSmem {
   static constexpr int W = 480 * R;
   static constexpr int kRowBytes = W * (int)sizeof(T);
-  static constexpr int kRowsBytes = kRows * kRowBytes;
-  static constexpr int kOffRows = NST * kStageTileBytes;    // staging tiles first (1024-byte aligned base)
-  static constexpr int kOffTw = kOffRows + kRowsBytes;
-  static constexpr int kOffMsc = kOffTw + kTwCount * 8;
-  static constexpr int kOffBar = kOffMsc + 244 * 4;
-  static constexpr int kBytes = kOffBar + 64 + 1024;
-  static constexpr int kFit = (227 * 1024) / (kBytes + 1024);
-  static constexpr int kCtasPerSm = kFit >= 2 ? 2 : 1;
+  static constexpr int kOffRows = NST * kStageTileBytes;     // staging tiles first (swizzle: 512-byte aligned base)
+  static constexpr int kOffWork = kOffRows + kRows * kRowBytes;
+  static constexpr int kTwUsed = (R == 1) ? 481 : kTwCount;  // tw1440 only for R = 3
+  static constexpr int kOffTw = kOffWork + kRows * 240 * 8;
+  static constexpr int kOffSc = kOffTw + kTwUsed * 8;
+  static constexpr int kOffBar = kOffSc + 244 * 4;
+  static constexpr int kBytes = kOffBar + 128;               // 2 x NST mbarriers (<= 6) + ring of 8 tile indices
+  static constexpr bool kTwoCtas = 2 * (kBytes + 1024) <= 228 * 1024;
+  static constexpr int kCtasPerSm = kTwoCtas ? 2 : 1;
+};
+// Staging depth: the kernel is bound by the bytes it keeps in flight (a tile is ~480 scattered 64-byte pieces of XM,
+// latency ~2 us under load), so take as many staging tiles (<= 3) as still let two CTAs share an SM.
+template <int R, typename T>
+struct P2InvDepth {
+  static constexpr int value =
+      P2InvSmem<R, T, 3>::kTwoCtas ? 3 : (P2InvSmem<R, T, 2>::kTwoCtas ? 2 : 1);
 };
 
+// hand-offs of one tile:
+//   full      thread 0 -> all     both planes of the staging tile have landed (tensor loads) and tq[it & 3] is valid
+//   consumed  8 warps -> thread 0  every warp holds its bins in registers -> thread 0 claims tile it+1 and starts its
+//                                 tensor loads, which then overlap the whole transform of tile it
+// The output rows are private to their 16-lane group: lane 0 of the group stores its row with one bulk copy and waits
+// for that copy's shared-memory read just before the group writes the row again (one tile later).
 template <int R, typename T, int NST>
 __global__ void __launch_bounds__(256, P2InvSmem<R, T, NST>::kCtasPerSm)
 dft_inv_p2_kernel(const __grid_constant__ CUtensorMap xm_map, T* __restrict__ y, const fl::cf* __restrict__ tables,
                   const float* __restrict__ mscale, int B, int C, int K, int Kp, int m_valid, int* __restrict__ sched) {
   using S = P2InvSmem<R, T, NST>;
   constexpr int W = S::W;
-  // 1024-byte aligned base, computed as an OFFSET from the shared array so that every access below stays in the
-  // shared address space (an integer round-trip of the pointer turns them into slower generic LD / ST)
-  extern __shared__ __align__(1024) uint8_t smp2_raw[];
-  uint8_t* smp2 = smp2_raw + ((1024u - (smem_u32(smp2_raw) & 1023u)) & 1023u);
-  uint8_t* rows = smp2 + S::kOffRows;
+  extern __shared__ __align__(1024) uint8_t smp2[];
   fl::cf* tw = reinterpret_cast<fl::cf*>(smp2 + S::kOffTw);
-  float* msc = reinterpret_cast<float*>(smp2 + S::kOffMsc);
-  uint64_t* full = reinterpret_cast<uint64_t*>(smp2 + S::kOffBar);
-  volatile int* tq = reinterpret_cast<volatile int*>(full + 2);   // ring of claimed tile indices (-1: no more work)
+  float* msc = reinterpret_cast<float*>(smp2 + S::kOffSc);
+  uint64_t* full = reinterpret_cast<uint64_t*>(smp2 + S::kOffBar);   // [NST]
+  uint64_t* consumed = full + 3;                                     // [NST]
+  volatile int* tq = reinterpret_cast<volatile int*>(full + 10);     // ring of 8 claimed tile indices (-1: no more work)
 
   const int tid = threadIdx.x;
-  for (int j = tid; j < kTwCount; j += 256) tw[j] = tables[j];
+  for (int j = tid; j < S::kTwUsed; j += 256) tw[j] = tables[j];
   for (int j = tid; j < 244; j += 256) msc[j] = j < m_valid ? mscale[j] : 0.f;
   if (tid == 0) {
+    if (smem_u32(smp2) & 511u) __trap();
     tma_prefetch_desc(&xm_map);
-    for (int b = 0; b < NST; ++b) mbar_init(&full[b], 1);
+    for (int j = 0; j < NST; ++j) {
+      mbar_init(full + j, 1);
+      mbar_init(consumed + j, 8);
+    }
     fence_barrier_init();
   }
   __syncthreads();
@@ -295,44 +312,40 @@ dft_inv_p2_kernel(const __grid_constant__ CUtensorMap xm_map, T* __restrict__ y,
   const int psrc = (16 - lane) & 15;
   DeviceWarp16p warp;
   const int o_re = stage_idx(lane, r);           // bin k = lane + 16 k2 -> + 256 floats per k2
+  fl::cf* work = reinterpret_cast<fl::cf*>(smp2 + S::kOffWork) + r * 240;
+  T* myrow = reinterpret_cast<T*>(smp2 + S::kOffRows + r * S::kRowBytes);
+  auto storez = [&](int n, int rr, fl::cf z) { store_pair<R, T>(myrow, n, rr, z); };
 
-  // XM slices of `tile` -> staging tile `buf`: one tensor load per plane (thread 0).  The tensor map is bounded by
-  // m_valid bins and C*Kp positions; everything outside is zero filled, and the full box always counts for the mbarrier.
-  auto prefetch = [&](int tile, int buf) {
-    float* st = reinterpret_cast<float*>(smp2 + buf * kStageTileBytes);
-    const int b = tile / tiles_per_b;
-    const int f0 = (tile - b * tiles_per_b) * kRows;
-    mbar_arrive_expect_tx(&full[buf], 2u * 241u * 64u);
-    tma_load_3d(st, &xm_map, &full[buf], f0, 2 * b, 0);
-    tma_load_3d(st + kPlaneFloats, &xm_map, &full[buf], f0, 2 * b + 1, 0);
-  };
-
-  // thread 0 claims the next tile from the global counter and starts its tensor loads
+  // thread 0: claim the next tile and start one tensor load per plane.  The tensor map is bounded by m_valid bins and
+  // C*Kp positions; everything outside is zero filled, and the full box always counts for the mbarrier.
   auto claim = [&](int slot, int buf) {
     int t = atomicAdd(sched, 1);
     if (t >= ntiles) t = -1;
     tq[slot] = t;
-    if (t >= 0) prefetch(t, buf);
+    if (t < 0) {
+      mbar_arrive(full + buf);                   // releases the waiters, who then read tq = -1
+      return;
+    }
+    float* dst = reinterpret_cast<float*>(smp2 + buf * kStageTileBytes);
+    const int b = t / tiles_per_b;
+    const int f0 = (t - b * tiles_per_b) * kRows;
+    mbar_arrive_expect_tx(full + buf, 2u * 241u * 64u);
+    tma_load_3d(dst, &xm_map, full + buf, f0, 2 * b, 0);
+    tma_load_3d(dst + kPlaneFloats, &xm_map, full + buf, f0, 2 * b + 1, 0);
   };
-  if (tid == 0) claim(0, 0);
-  __syncthreads();
+  if (tid == 0) {
+    for (int j = 0; j < NST; ++j) claim(j, j);
+  }
 
   for (int it = 0;; ++it) {
-    if (tid < 32) bulk_wait_read0();             // row buffer of the previous tile has been read by the bulk stores
-    __syncthreads();                             // ... and everybody is done with the other staging tile (FFT work buffer);
-                                                 // also orders thread 0's tq write (NST == 1: made after the last barrier)
-    const int tile = tq[it & 3];
+    const int buf = it % NST;
+    const uint32_t bph = (uint32_t)(it / NST) & 1u;
+    mbar_wait(full + buf, bph);
+    const int tile = tq[it & 7];
     if (tile < 0) break;
-    const int cur = (NST == 2) ? (it & 1) : 0;
-    const uint32_t parity = (NST == 2) ? ((uint32_t)(it >> 1) & 1u) : ((uint32_t)it & 1u);
     const int b = tile / tiles_per_b;
     const int f0 = (tile - b * tiles_per_b) * kRows;
-    if (NST == 2 && tid == 0) claim((it + 1) & 3, cur ^ 1);
-    mbar_wait(&full[cur], parity);
-    const float* st = reinterpret_cast<const float*>(smp2 + cur * kStageTileBytes);
-    fl::cf* work = reinterpret_cast<fl::cf*>(smp2 + cur * kStageTileBytes);
-    T* myrow = reinterpret_cast<T*>(rows + r * S::kRowBytes);
-    auto storez = [&](int n, int rr, fl::cf z) { store_pair<R, T>(myrow, n, rr, z); };
+    const float* st = reinterpret_cast<const float*>(smp2 + buf * kStageTileBytes);
 
     // this lane's bins k = lane + 16 k2 (scaled); the partner bins 240 - k come from lane 16 - k1 by shuffle
     // (register 14 - k2), lane 0 pairs its own registers (k2 <-> 15 - k2) and bin 0 with the extra bin 240
@@ -344,26 +357,31 @@ dft_inv_p2_kernel(const __grid_constant__ CUtensorMap xm_map, T* __restrict__ y,
     }
     const float s240 = msc[240];
     const fl::cf h240 = fl::mk(st[3840 + r] * s240, st[kPlaneFloats + 3840 + r] * s240);
+    __syncwarp();
+    if ((tid & 31) == 0) mbar_arrive(consumed + buf);
+    if (tid == 0) {
+      mbar_wait(consumed + buf, bph);
+      claim((it + NST) & 7, buf);
+    }
 #pragma unroll
     for (int k2 = 0; k2 < 15; ++k2) {
       const fl::cf hs = fl::mk(warp.shfl_idx(H[14 - k2].x, psrc), warp.shfl_idx(H[14 - k2].y, psrc));
       const fl::cf h0 = (k2 == 0) ? h240 : H[15 - k2];
       HP[k2] = (lane == 0) ? h0 : hs;
     }
-    __syncthreads();                             // staging tile consumed: it now serves as the FFT work buffer
-    fp::irfft_row<R>(warp, H, HP, work + r * 240, storez, tw, tw + 240, tw + 481);
-    fence_proxy_async();                         // generic-proxy row writes -> visible to the bulk (async proxy) stores
-    __syncthreads();
-    if (NST == 1 && tid == 0) claim((it + 1) & 3, 0);
-    if (tid < 32) {
-      const int f = f0 + tid;
+    if (lane == 0) bulk_wait_read0();            // the previous bulk store of this row has read it
+    __syncwarp();
+    fp::irfft_row<R>(warp, H, HP, work, storez, tw, tw + 240, tw + 481);
+    fence_proxy_async();                         // generic-proxy row writes -> visible to the bulk (async proxy) store
+    __syncwarp();
+    if (lane == 0) {
+      const int f = f0 + r;
       const int c = f / Kp, lat = f - c * Kp;
-      if (tid < kRows && f < flat && lat < K)
-        bulk_s2g(y + ((long long)(b * C + c) * K + lat) * W, rows + tid * S::kRowBytes, S::kRowBytes);
+      if (f < flat && lat < K) bulk_s2g(y + ((long long)(b * C + c) * K + lat) * W, myrow, S::kRowBytes);
       bulk_commit();
     }
   }
-  if (tid < 32) bulk_wait_read0();
+  if (lane == 0) bulk_wait_read0();
   if (tid == 0) {
     __threadfence();
     if (atomicAdd(sched + 1, 1) == (int)gridDim.x - 1) {
@@ -374,6 +392,14 @@ dft_inv_p2_kernel(const __grid_constant__ CUtensorMap xm_map, T* __restrict__ y,
 }
 
 // ================================================================================ host launchers
+template <class Kern>
+static int p2_prepare(Kern kern, int smem_bytes) {
+  SFNO_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+  // two CTAs per SM only fit with the largest shared-memory carve-out
+  SFNO_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+  return 0;
+}
+
 template <int R, typename T>
 static int launch_fwd_p2(const void* x, int B, int C, int K, int Kp, int M, const float* mscale, float* xm,
                          int round_out, cudaStream_t stream) {
@@ -409,7 +435,7 @@ static int launch_fwd_p2(const void* x, int B, int C, int K, int Kp, int M, cons
 template <int R, typename T>
 static int launch_inv_p2(const float* xm, int B, int C, int K, int Kp, int M, int m_valid, const float* mscale,
                          void* y, cudaStream_t stream) {
-  constexpr int NST = (R == 3 && sizeof(T) == 2) ? 1 : 2;
+  constexpr int NST = P2InvDepth<R, T>::value;
   using S = P2InvSmem<R, T, NST>;
   static_assert(S::kBytes <= 227 * 1024, "inverse DFT tile does not fit shared memory");
   const fl::cf* tables;
@@ -418,7 +444,7 @@ static int launch_inv_p2(const float* xm, int B, int C, int K, int Kp, int M, in
   if (xm_stage_map(&map, xm, B, C, Kp, std::max(1, std::min(M, m_valid)))) return 1;
   static bool attr = false;
   if (!attr) {
-    SFNO_CUDA(cudaFuncSetAttribute(dft_inv_p2_kernel<R, T, NST>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kBytes));
+    if (p2_prepare(dft_inv_p2_kernel<R, T, NST>, S::kBytes)) return 1;
     attr = true;
   }
   const int ntiles = ((C * Kp + kRows - 1) / kRows) * B;

@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define SFNO_ABI_VERSION 1
+#define SFNO_ABI_VERSION 2
 
 /* element types of spatial tensors crossing the boundary */
 enum { SFNO_F32 = 0, SFNO_BF16 = 1, SFNO_F16 = 2 };
@@ -121,6 +121,30 @@ int sfno_c64_to_xm(const void* in_c64, int B, int C, int nlat, int mmax, float* 
 /* y[b][c][h][w] (+)= bias   (spectral_convolution.py:143-144); bias_kind 0: [C], 1: [C][H][W]    */
 int sfno_add_bias(void* y, int y_dtype, const float* bias, int bias_kind, int B, int C, int H, int W,
                   void* stream);
+
+/* ---- composite calls: one call per reference operator ------------------------------------------
+ * For callers that do not want to sequence the kernels themselves (the C ABI list of SURVEY.md 8(b)).
+ * They enqueue exactly the kernels above on `stream`, with the intermediates (XM, SP) in `ws`, a device
+ * scratch buffer of at least sfno_workspace_bytes(...) bytes that the caller owns (no allocation inside,
+ * so the calls can be captured in a CUDA graph).                                                       */
+enum { SFNO_OP_SHT_FWD = 0, SFNO_OP_SHT_INV = 1, SFNO_OP_BLOCK_FWD = 2 };
+/* plan_b is only read for SFNO_OP_BLOCK_FWD (the inverse transform's plan); C = max(Cin, Cout) there. */
+size_t sfno_workspace_bytes(const sfno_plan* plan, const sfno_plan* plan_b, int op, int B, int C);
+/* RealSHT.forward (spectral_convolution.py:131, sfnonet.py:596):
+ *   x [B][C][nlat][nlon] (x_dtype) -> coeffs complex64 [B][C][lmax][mmax]                              */
+int sfno_sht_fwd(const sfno_plan* plan, const void* x, int x_dtype, int B, int C, void* coeffs_c64,
+                 void* ws, size_t ws_bytes, void* stream);
+/* InverseRealSHT.forward (spectral_convolution.py:133,141, sfnonet.py:598,616):
+ *   coeffs complex64 [B][C][lmax][mmax] -> y [B][C][nlat][nlon] (y_dtype)                              */
+int sfno_sht_inv(const sfno_plan* plan, const void* coeffs_c64, int B, int C, void* y, int y_dtype,
+                 void* ws, size_t ws_bytes, void* stream);
+/* SpectralConv.forward, dhconv, same-grid case without bias (spectral_convolution.py:124-148):
+ *   y = isht(dhconv(sht(x), w)),  x [B][Cin][nlat_f][nlon_f] -> y [B][Cout][nlat_i][nlon_i] (same dtype);
+ * wp is the packed weight from sfno_dhconv_pack_weight.  The reference's second return value
+ * (`residual`) is x itself unless the block changes resolution; callers that need the re-projected
+ * residual call sfno_sht_fwd + sfno_sht_inv.  Both plans must agree in lmax and mmax.                  */
+int sfno_block_fwd(const sfno_plan* plan_fwd, const sfno_plan* plan_inv, const void* x, int dtype, int B,
+                   int Cin, int Cout, const float* wp, void* y, void* ws, size_t ws_bytes, void* stream);
 
 #ifdef __cplusplus
 }

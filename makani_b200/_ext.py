@@ -40,7 +40,14 @@ _PROTOTYPES = {
     "sfno_xm_to_c64": (_i, [_vp, _i, _i, _i, _i, _vp, _vp]),
     "sfno_c64_to_xm": (_i, [_vp, _i, _i, _i, _i, _vp, _vp]),
     "sfno_add_bias": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _i, _vp]),
+    "sfno_workspace_bytes": (C.c_size_t, [_vp, _vp, _i, _i, _i]),
+    "sfno_sht_fwd": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp, C.c_size_t, _vp]),
+    "sfno_sht_inv": (_i, [_vp, _vp, _i, _i, _vp, _i, _vp, C.c_size_t, _vp]),
+    "sfno_block_fwd": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp, C.c_size_t, _vp]),
 }
+
+OP_SHT_FWD, OP_SHT_INV, OP_BLOCK_FWD = 0, 1, 2
+ABI_VERSION = 2
 
 EXPORTED_SYMBOLS = tuple(_PROTOTYPES)
 
@@ -61,8 +68,8 @@ def load():
         fn = getattr(lib, name)          # AttributeError if the header and the library disagree
         fn.restype = res
         fn.argtypes = args
-    if lib.sfno_abi_version() != 1:
-        raise ImportError(f"{LIB_PATH}: ABI version {lib.sfno_abi_version()} != 1")
+    if lib.sfno_abi_version() != ABI_VERSION:
+        raise ImportError(f"{LIB_PATH}: ABI version {lib.sfno_abi_version()} != {ABI_VERSION}")
     _lib = lib
     return lib
 

@@ -75,10 +75,17 @@ int sfno_plan_create(int nlat, int nlon, int lmax, int mmax, int m_offset, const
       float* dst = h.data() + ((size_t)m * lmax + l) * p->Kp;
       for (int k = 0; k < nlat; ++k) dst[k] = tf32_rn_host((float)src[k]);
     }
+  const int nbins = nlon / 2 + 1;
+  std::vector<float> sc(2 * (size_t)nbins, 1.f);
+  for (int m = 0; m < nbins; ++m) sc[m] = (float)(2.0 * M_PI / nlon);
+  p->mscale = nullptr;
   cudaError_t e = cudaMalloc(&p->table, n * sizeof(float));
   if (e == cudaSuccess) e = cudaMemcpy(p->table, h.data(), n * sizeof(float), cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) e = cudaMalloc(&p->mscale, sc.size() * sizeof(float));
+  if (e == cudaSuccess) e = cudaMemcpy(p->mscale, sc.data(), sc.size() * sizeof(float), cudaMemcpyHostToDevice);
   if (e != cudaSuccess) {
     if (p->table) cudaFree(p->table);
+    if (p->mscale) cudaFree(p->mscale);
     delete p;
     set_error(std::string("sfno_plan_create: ") + cudaGetErrorString(e));
     return 1;
@@ -90,6 +97,7 @@ int sfno_plan_create(int nlat, int nlon, int lmax, int mmax, int m_offset, const
 int sfno_plan_destroy(sfno_plan* plan) {
   if (!plan) return 0;
   if (plan->table) cudaFree(plan->table);
+  if (plan->mscale) cudaFree(plan->mscale);
   delete plan;
   return 0;
 }
@@ -128,6 +136,80 @@ int sfno_dhconv_bwd_w(const float* sp_in, const float* gsp_out, float* gwp, int 
                       int mmax, int l_offset, int m_offset, void* stream) {
   SFNO_CHECK(sp_in && gsp_out && gwp, "null argument");
   return dhconv_bwd_w(sp_in, gsp_out, gwp, B, Cin, Cout, lmax, mmax, l_offset, m_offset, (cudaStream_t)stream);
+}
+
+// ---------------------------------------------------------------------------------- composite calls
+namespace {
+constexpr size_t kWsAlign = 1024;
+size_t ws_round(size_t bytes) { return (bytes + kWsAlign - 1) / kWsAlign * kWsAlign; }
+size_t xm_bytes(const sfno_plan* p, int B, int C) { return ws_round((size_t)sfno_xm_elems(p->nlat, p->mmax, B, C) * 4); }
+size_t sp_bytes(const sfno_plan* p, int B, int C) { return ws_round((size_t)sfno_sp_elems(p->lmax, p->mmax, B, C) * 4); }
+bool ws_ok(const void* ws, size_t have, size_t need) {
+  return ws != nullptr && have >= need && (reinterpret_cast<uintptr_t>(ws) & 15u) == 0;
+}
+}  // namespace
+
+size_t sfno_workspace_bytes(const sfno_plan* plan, const sfno_plan* plan_b, int op, int B, int C) {
+  if (!plan || B <= 0 || C <= 0) return 0;
+  switch (op) {
+    case SFNO_OP_SHT_FWD:
+    case SFNO_OP_SHT_INV: return xm_bytes(plan, B, C) + sp_bytes(plan, B, C);
+    case SFNO_OP_BLOCK_FWD:
+      if (!plan_b) return 0;
+      // XM(in) and XM(out) share one region (the first is dead once the analysis has run); two SP buffers
+      return std::max(xm_bytes(plan, B, C), xm_bytes(plan_b, B, C)) + 2 * sp_bytes(plan, B, C);
+    default: return 0;
+  }
+}
+
+int sfno_sht_fwd(const sfno_plan* plan, const void* x, int x_dtype, int B, int C, void* coeffs_c64, void* ws,
+                 size_t ws_bytes, void* stream) {
+  SFNO_CHECK(plan && x && coeffs_c64, "null argument");
+  SFNO_CHECK(plan->m_offset == 0, "sfno_sht_fwd: azimuth-sharded plans go through the distributed modules");
+  SFNO_CHECK(ws_ok(ws, ws_bytes, sfno_workspace_bytes(plan, nullptr, SFNO_OP_SHT_FWD, B, C)),
+             "sfno_sht_fwd: workspace missing, misaligned or smaller than sfno_workspace_bytes()");
+  cudaStream_t s = (cudaStream_t)stream;
+  float* xm = static_cast<float*>(ws);
+  float* sp = reinterpret_cast<float*>(static_cast<char*>(ws) + xm_bytes(plan, B, C));
+  if (dft_fwd(x, x_dtype, B, C, plan->nlat, plan->nlon, plan->mmax, plan->mscale, xm, 1, s)) return 1;
+  if (legendre_analysis(plan, xm, B, C, sp, 0, s)) return 1;
+  return sfno_sp_to_c64(sp, B, C, plan->lmax, plan->mmax, 0, 0, coeffs_c64, stream);
+}
+
+int sfno_sht_inv(const sfno_plan* plan, const void* coeffs_c64, int B, int C, void* y, int y_dtype, void* ws,
+                 size_t ws_bytes, void* stream) {
+  SFNO_CHECK(plan && y && coeffs_c64, "null argument");
+  SFNO_CHECK(plan->m_offset == 0, "sfno_sht_inv: azimuth-sharded plans go through the distributed modules");
+  SFNO_CHECK(ws_ok(ws, ws_bytes, sfno_workspace_bytes(plan, nullptr, SFNO_OP_SHT_INV, B, C)),
+             "sfno_sht_inv: workspace missing, misaligned or smaller than sfno_workspace_bytes()");
+  cudaStream_t s = (cudaStream_t)stream;
+  float* xm = static_cast<float*>(ws);
+  float* sp = reinterpret_cast<float*>(static_cast<char*>(ws) + xm_bytes(plan, B, C));
+  if (sfno_c64_to_sp(coeffs_c64, B, C, plan->lmax, plan->mmax, sp, stream)) return 1;
+  if (legendre_synthesis(plan, sp, B, C, xm, s)) return 1;
+  return dft_inv(xm, B, C, plan->nlat, plan->nlon, plan->mmax, plan->mmax, plan->mscale + (plan->nlon / 2 + 1), y,
+                 y_dtype, s);
+}
+
+int sfno_block_fwd(const sfno_plan* pf, const sfno_plan* pi, const void* x, int dtype, int B, int Cin, int Cout,
+                   const float* wp, void* y, void* ws, size_t ws_bytes, void* stream) {
+  SFNO_CHECK(pf && pi && x && wp && y, "null argument");
+  SFNO_CHECK(pf->lmax == pi->lmax && pf->mmax == pi->mmax, "sfno_block_fwd: the two plans differ in lmax / mmax");
+  SFNO_CHECK(pf->m_offset == 0 && pi->m_offset == 0, "sfno_block_fwd: azimuth-sharded plans are not supported");
+  const int C = std::max(Cin, Cout);
+  SFNO_CHECK(ws_ok(ws, ws_bytes, sfno_workspace_bytes(pf, pi, SFNO_OP_BLOCK_FWD, B, C)),
+             "sfno_block_fwd: workspace missing, misaligned or smaller than sfno_workspace_bytes()");
+  cudaStream_t s = (cudaStream_t)stream;
+  char* base = static_cast<char*>(ws);
+  float* xm = reinterpret_cast<float*>(base);
+  float* sp_a = reinterpret_cast<float*>(base + std::max(xm_bytes(pf, B, C), xm_bytes(pi, B, C)));
+  float* sp_b = reinterpret_cast<float*>(reinterpret_cast<char*>(sp_a) + sp_bytes(pf, B, C));
+  // every intermediate feeds a TF32 contraction: store round-to-nearest TF32 values (see sfno_legendre_analysis)
+  if (dft_fwd(x, dtype, B, Cin, pf->nlat, pf->nlon, pf->mmax, pf->mscale, xm, 1, s)) return 1;
+  if (legendre_analysis(pf, xm, B, Cin, sp_a, 1, s)) return 1;
+  if (dhconv_fwd(sp_a, wp, sp_b, B, Cin, Cout, pf->lmax, pf->mmax, 0, 0, 1, s)) return 1;
+  if (legendre_synthesis(pi, sp_b, B, Cout, xm, s)) return 1;
+  return dft_inv(xm, B, Cout, pi->nlat, pi->nlon, pi->mmax, pi->mmax, pi->mscale + (pi->nlon / 2 + 1), y, dtype, s);
 }
 
 }  // extern "C"

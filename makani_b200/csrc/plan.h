@@ -8,6 +8,7 @@ struct sfno_plan {
   int nlat, nlon, lmax, mmax, m_offset;
   int Kp;            // round_up(nlat, 4): latitude stride of the table and of XM
   float* table;      // device, [mmax][lmax][Kp] fp32 (pad entries zero)
+  float* mscale;     // device, [2][nlon/2 + 1]: row 0 = 2*pi/nlon (RealSHT), row 1 = 1 (InverseRealSHT)
   int device;
 };
 

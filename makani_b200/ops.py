@@ -254,3 +254,47 @@ def diag_bwd_w(sp_in, gsp_out, B, Cin, Cout, lmax, mmax, l_offset=0, m_offset=0)
     _ext.check(_ext.load().sfno_diag_contract(2, _ptr(sp_in), _ptr(gsp_out), _ptr(gw), B, Cin, Cout, lmax, mmax,
                                               l_offset, m_offset, _stream()), "sfno_diag_contract(bwd_w)")
     return gw
+
+
+# ------------------------------------------------------------------------------------------ composite calls
+def _workspace(plan: Plan, plan_b, op: int, B: int, Cn: int, device) -> torch.Tensor:
+    n = int(_ext.load().sfno_workspace_bytes(plan.handle, None if plan_b is None else plan_b.handle, op, B, Cn))
+    if n == 0:
+        raise RuntimeError("makani_b200: sfno_workspace_bytes returned 0 (bad plan / sizes)")
+    return torch.empty(n, dtype=torch.uint8, device=device)
+
+
+def sht_fwd(plan: Plan, x: torch.Tensor) -> torch.Tensor:
+    """One-call RealSHT.forward (sfno_sht_fwd): x [B, C, nlat, nlon] -> complex64 [B, C, lmax, mmax]."""
+    _need_cuda(x, "x")
+    B, Cn, K, W = x.shape
+    x = x.contiguous()
+    ws = _workspace(plan, None, _ext.OP_SHT_FWD, B, Cn, x.device)
+    out = torch.empty((B, Cn, plan.lmax, plan.mmax), dtype=torch.complex64, device=x.device)
+    _ext.check(_ext.load().sfno_sht_fwd(plan.handle, _ptr(x), dtype_code(x.dtype), B, Cn, _ptr(out), _ptr(ws),
+                                        ws.numel(), _stream()), "sfno_sht_fwd")
+    return out
+
+
+def sht_inv(plan: Plan, c: torch.Tensor, dtype: torch.dtype = torch.float32) -> torch.Tensor:
+    """One-call InverseRealSHT.forward (sfno_sht_inv): complex64 [B, C, lmax, mmax] -> [B, C, nlat, nlon]."""
+    _need_cuda(c, "coefficients")
+    B, Cn = c.shape[0], c.shape[1]
+    c = c.contiguous()
+    ws = _workspace(plan, None, _ext.OP_SHT_INV, B, Cn, c.device)
+    y = torch.empty((B, Cn, plan.nlat, plan.nlon), dtype=dtype, device=c.device)
+    _ext.check(_ext.load().sfno_sht_inv(plan.handle, _ptr(c), B, Cn, _ptr(y), dtype_code(dtype), _ptr(ws),
+                                        ws.numel(), _stream()), "sfno_sht_inv")
+    return y
+
+
+def block_fwd(plan_fwd: Plan, plan_inv: Plan, x: torch.Tensor, wp: torch.Tensor, Cout: int) -> torch.Tensor:
+    """One-call SpectralConv.forward for dhconv without bias (sfno_block_fwd): y = isht(dhconv(sht(x), w))."""
+    _need_cuda(x, "x")
+    B, Cin, K, W = x.shape
+    x = x.contiguous()
+    ws = _workspace(plan_fwd, plan_inv, _ext.OP_BLOCK_FWD, B, max(Cin, Cout), x.device)
+    y = torch.empty((B, Cout, plan_inv.nlat, plan_inv.nlon), dtype=x.dtype, device=x.device)
+    _ext.check(_ext.load().sfno_block_fwd(plan_fwd.handle, plan_inv.handle, _ptr(x), dtype_code(x.dtype), B, Cin, Cout,
+                                          _ptr(wp), _ptr(y), _ptr(ws), ws.numel(), _stream()), "sfno_block_fwd")
+    return y

@@ -228,3 +228,47 @@ def test_spectral_conv_cuda_graph_capture(mk):
     assert torch.equal(y_graph, y_eager)
     assert torch.equal(x.grad, gx_eager)
     assert torch.equal(torch.view_as_real(conv.weight.grad), torch.view_as_real(gw_eager))
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_composite_c_abi_calls(mk, dtype):
+    """sfno_sht_fwd / sfno_sht_inv / sfno_block_fwd (one C call per reference operator, caller-owned workspace)
+    against the fp64 oracle and against the module path they must reproduce bit for bit."""
+    from makani_b200 import ops
+    torch.manual_seed(3)
+    nlat, nlon, L, M, Cin, Cout, B = 60, 480, 60, 61, 12, 20, 2
+    sht = mk.RealSHT(nlat, nlon, lmax=L, mmax=M, grid="legendre-gauss").to(DEV)
+    isht = mk.InverseRealSHT(nlat, nlon, lmax=L, mmax=M, grid="legendre-gauss").to(DEV)
+    conv = mk.SpectralConv(sht, isht, Cin, Cout, operator_type="dhconv", bias=False).to(DEV)
+    x = torch.randn(B, Cin, nlat, nlon, device=DEV).to(dtype)
+    pf, pi = sht._plan(x.device), isht._plan(x.device)
+    tol_t = TOL_T
+    tol_b = TOL_BLOCK if dtype == torch.float32 else 2e-2
+
+    c = ops.sht_fwd(pf, x)
+    c_mod = sht(x)
+    assert torch.equal(torch.view_as_real(c), torch.view_as_real(c_mod))
+    cr = O.RealSHT(nlat, nlon, lmax=L, mmax=M, grid="legendre-gauss")(x.double().cpu())
+    assert O.rel_l2(c.cpu(), cr) < tol_t
+
+    y = ops.sht_inv(pi, c_mod, torch.float32)
+    assert torch.equal(y, isht(c_mod))
+    yr = O.InverseRealSHT(nlat, nlon, lmax=L, mmax=M, grid="legendre-gauss")(cr)
+    assert O.rel_l2(y.cpu(), yr) < tol_t
+
+    wp = ops.pack_weight(conv.weight.detach())
+    yb = ops.block_fwd(pf, pi, x, wp, Cout)
+    yb_mod, _ = conv(x)
+    assert yb.dtype == dtype and torch.equal(yb, yb_mod.detach())
+    w64 = conv.weight.detach().cpu().to(torch.complex128)
+    ybr = O.InverseRealSHT(nlat, nlon, lmax=L, mmax=M, grid="legendre-gauss")(torch.einsum("bixy,iox->boxy", cr, w64))
+    assert O.rel_l2(yb.float().cpu(), ybr) < tol_b
+
+    # a too small workspace is an error, not a silent overrun
+    import ctypes as C
+    from makani_b200 import _ext
+    ws = torch.empty(1024, dtype=torch.uint8, device=DEV)
+    out = torch.empty_like(c)
+    rc = _ext.load().sfno_sht_fwd(pf.handle, C.c_void_p(x.data_ptr()), ops.dtype_code(x.dtype), B, Cin,
+                                  C.c_void_p(out.data_ptr()), C.c_void_p(ws.data_ptr()), ws.numel(), None)
+    assert rc != 0 and b"workspace" in _ext.load().sfno_last_error()

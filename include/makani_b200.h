@@ -146,6 +146,39 @@ int sfno_sht_inv(const sfno_plan* plan, const void* coeffs_c64, int B, int C, vo
 int sfno_block_fwd(const sfno_plan* plan_fwd, const sfno_plan* plan_inv, const void* x, int dtype, int B,
                    int Cin, int Cout, const float* wp, void* y, void* ws, size_t ws_bytes, void* stream);
 
+/* ---- exchange step of the h-sharded (polar) distributed SHT over NVLink peer memory -------------
+ * Replaces the split / contiguous / all_to_all / cat of thd.distributed_transpose_polar
+ * (makani/mpu/layers.py:73-100 call form; torch-harmonics distributed/primitives.py) for the internal
+ * layouts: one kernel reads the local XM / SP tensor and stores every row straight into the destination
+ * layout of its owner - the local buffer for the own part, peer-mapped buffers (CUDA IPC) for the rest -
+ * so the transposition costs one pass over the data and needs no packing on either side.
+ *
+ * sfno_ipc_alloc    : cudaMalloc + zero a buffer and export its IPC handle (64 bytes) for the other ranks
+ * sfno_ipc_open     : map a buffer exported by another process of this node (enables peer access)
+ * sfno_ipc_close / sfno_ipc_free : undo the above
+ * sfno_rows_scatter : for each descriptor, copy rows (i0, i1, i2), i_k < n_k, of `len` floats
+ *                       dst[dst_off + i0*ds0 + i1*ds1 + i2*ds2 + e] = src[src_off + i0*ss0 + i1*ss1 + i2*ss2 + e]
+ *                     tri_l0 >= 0 marks an SP copy: i0 is a degree (l = tri_l0 + i0), i1 an order m, and the rows
+ *                     with m >= round_up(l + 1, 16) - which the SP layout leaves undefined - are skipped.      */
+typedef struct {
+  void* dst;
+  long long src_off, dst_off;
+  int n0, n1, n2, len;
+  long long ss0, ss1, ss2, ds0, ds1, ds2;
+  int tri_l0;
+} sfno_copy_desc;
+int sfno_ipc_alloc(size_t bytes, void** ptr, unsigned char handle_out[64]);
+int sfno_ipc_open(const unsigned char handle[64], void** ptr);
+int sfno_ipc_close(void* ptr);
+int sfno_ipc_free(void* ptr);
+int sfno_rows_scatter(const float* src, const sfno_copy_desc* descs_host, int ndesc, void* stream);
+/* Stream-ordered barrier between the `size` (<= 8) ranks of one node through peer memory: rank r stores `epoch`
+ * into slot r of every rank's flag array (flags_host[p] = pointer to rank p's array of >= 8 ints, zero at
+ * allocation, mapped with sfno_ipc_open) and waits until all slots of its own array have reached `epoch`.
+ * Everything the ranks enqueued before the barrier (e.g. sfno_rows_scatter into peer buffers) is visible to what
+ * they enqueue after it.  `epoch` must increase by one per barrier on the same flag arrays.                  */
+int sfno_peer_barrier(int* const* flags_host, int rank, int size, int epoch, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -44,7 +44,23 @@ _PROTOTYPES = {
     "sfno_sht_fwd": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp, C.c_size_t, _vp]),
     "sfno_sht_inv": (_i, [_vp, _vp, _i, _i, _vp, _i, _vp, C.c_size_t, _vp]),
     "sfno_block_fwd": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp, C.c_size_t, _vp]),
+    "sfno_ipc_alloc": (_i, [C.c_size_t, C.POINTER(_vp), C.c_char_p]),
+    "sfno_ipc_open": (_i, [C.c_char_p, C.POINTER(_vp)]),
+    "sfno_ipc_close": (_i, [_vp]),
+    "sfno_ipc_free": (_i, [_vp]),
+    "sfno_rows_scatter": (_i, [_vp, _vp, _i, _vp]),
+    "sfno_peer_barrier": (_i, [_vp, _i, _i, _i, _vp]),
 }
+
+
+class CopyDesc(C.Structure):
+    """sfno_copy_desc (include/makani_b200.h)."""
+    _fields_ = [("dst", _vp), ("src_off", _ll), ("dst_off", _ll),
+                ("n0", _i), ("n1", _i), ("n2", _i), ("len", _i),
+                ("ss0", _ll), ("ss1", _ll), ("ss2", _ll), ("ds0", _ll), ("ds1", _ll), ("ds2", _ll),
+                ("tri_l0", _i)]
+
+
 
 OP_SHT_FWD, OP_SHT_INV, OP_BLOCK_FWD = 0, 1, 2
 ABI_VERSION = 2

@@ -17,6 +17,11 @@ Choreography (the in-tree structural twin is makani/mpu/layers.py:67-102 / 134-1
 The exchanges are NCCL all-to-alls over NVLink issued through torch.distributed (one process per GPU); the
 local stages are the package's CUDA kernels.  The transposes themselves are device agnostic, so the
 re-sharding logic is testable on CPU with gloo.
+
+h-sharded transforms (w = 1, the configuration the reference benchmarks: ``h_parallel_size=4``) on one NVLink node
+skip the complex64 round trips and the pack / all-to-all / unpack: each of their two exchanges is a single kernel that
+stores rows of the internal layout straight into the owner's buffer in peer memory (``p2p.py``, ``_PolarExchange``).
+``p2p.status()`` reports which path is active; ``MAKANI_B200_P2P=0`` forces the all-to-all path.
 """
 from __future__ import annotations
 
@@ -27,8 +32,9 @@ import torch
 import torch.distributed as dist
 import torch.nn as nn
 
-from .. import ops
+from .. import _ext, ops
 from ..sht import InverseRealSHT, RealSHT
+from . import p2p
 
 __all__ = ["init", "is_initialized", "polar_group", "azimuth_group", "polar_group_size", "azimuth_group_size",
            "polar_group_rank", "azimuth_group_rank", "compute_split_shapes", "split_tensor_along_dim",
@@ -251,6 +257,172 @@ class _LegendreStage(torch.autograd.Function):
         return ops.xm_to_c64(gxm, B, Cn, mod.nlat, plan.mmax), None, None
 
 
+# ------------------------------------------------------------------------------------------------
+# h-sharded transforms over peer memory: the two transpositions of each transform are single kernels that move rows of
+# the internal layouts (XM, SP) straight into the owner's buffers over NVLink (see p2p.py); w must be 1.
+def _offsets(shapes):
+    out, acc = [], 0
+    for n in shapes:
+        out.append(acc)
+        acc += n
+    return out
+
+
+def _rup4(n):
+    return (n + 3) // 4 * 4
+
+
+def _rup8(n):
+    return (n + 7) // 8 * 8
+
+
+class _PolarExchange:
+    """The four row scatters between  XM_loc [M][2B][Cp][Kp(lat slab)]  <->  XM_ch [M][2B][Cp(ch slab)][Kp(nlat)]
+    and  SP_ch [L][M][2B][Cp(ch slab)]  <->  SP_l [L slab][M][2B][Cp]."""
+
+    def __init__(self, mod, B, C, device):
+        self.group = polar_group()
+        self.me, self.h = mod.comm_rank_polar, mod.comm_size_polar
+        self.B, self.C, self.M, self.L, self.J = B, C, mod.mmax, mod.lmax, 2 * B
+        self.lat, self.lat0 = mod.lat_shapes, _offsets(mod.lat_shapes)
+        self.ls, self.l0 = mod.l_shapes, _offsets(mod.l_shapes)
+        self.cs = compute_split_shapes(C, self.h)
+        self.c0 = _offsets(self.cs)
+        # XM_ch keeps every rank's latitude slab at a 32-byte aligned offset (slabs padded to multiples of 8 latitudes;
+        # the Legendre table of the peer path, _peer_plan, has zero columns at the pad positions), so the rows that
+        # cross NVLink are 16-byte vector stores into whole sectors
+        self.latp0 = _offsets([_rup8(k) for k in self.lat])
+        self.Cp, self.Kpg = _rup4(C), sum(_rup8(k) for k in self.lat)
+        self.device = device
+        self._plans = {}
+
+    @staticmethod
+    def of(mod, B, C, device):
+        cache = mod.__dict__.setdefault("_exchanges", {})
+        k = (B, C, device.index)
+        ex = cache.get(k)
+        if ex is None:
+            ex = _PolarExchange(mod, B, C, device)
+            cache[k] = ex
+        return ex
+
+    def _run(self, key, nfloats, src, make_desc, out_floats):
+        plan = self._plans.get(key)
+        if plan is None:
+            # receive buffers and the (static) row descriptors for either of them, built once per layout
+            pb = p2p.buffers((key, self.B, self.C, self.M, self.L, self.Kpg), nfloats, self.group, self.device)
+            arrs = []
+            for b in range(2):
+                descs = [d for d in (make_desc(p, pb.peer_ptrs[b][p]) for p in range(self.h)) if d is not None]
+                arrs.append(p2p.desc_array(descs) if descs else None)
+            plan = (pb, arrs, p2p.fence(self.group, self.device))
+            self._plans[key] = plan
+        pb, arrs, fence = plan
+        b = pb.next()
+        if arrs[b] is not None:
+            p2p.scatter(src, arrs[b])
+        fence()
+        return pb.local[b][:out_floats]
+
+    @staticmethod
+    def _desc(dst, src_off, dst_off, n, length, ss, ds, tri=-1):
+        if min(n) <= 0 or length <= 0:
+            return None
+        return _ext.CopyDesc(dst, src_off, dst_off, n[0], n[1], n[2], length, ss[0], ss[1], ss[2], ds[0], ds[1], ds[2], tri)
+
+    def lat_to_chan(self, xm_loc):
+        """XM of my latitude slab, all channels -> XM of all latitudes, my channel slab."""
+        M, J, Cp, Kpg, me = self.M, self.J, self.Cp, self.Kpg, self.me
+        Kl = _rup4(self.lat[me])
+
+        def mk(p, dst):
+            Cpp = _rup4(self.cs[p])
+            return self._desc(dst, self.c0[p] * Kl, self.latp0[me], (M, J, self.cs[p]), Kl,
+                              (J * Cp * Kl, Cp * Kl, Kl), (J * Cpp * Kpg, Cpp * Kpg, Kpg))
+        n = M * J * max(_rup4(c) for c in self.cs) * Kpg
+        return self._run("xm_ch", n, xm_loc, mk, M * J * _rup4(self.cs[me]) * Kpg)
+
+    def chan_to_lat(self, xm_ch):
+        """XM of all latitudes, my channel slab -> XM of my latitude slab, all channels."""
+        M, J, Cp, Kpg, me = self.M, self.J, self.Cp, self.Kpg, self.me
+        Cpm = _rup4(self.cs[me])
+
+        def mk(p, dst):
+            Kpp = _rup4(self.lat[p])
+            return self._desc(dst, self.latp0[p], self.c0[me] * Kpp, (M, J, self.cs[me]), Kpp,
+                              (J * Cpm * Kpg, Cpm * Kpg, Kpg), (J * Cp * Kpp, Cp * Kpp, Kpp))
+        n = M * J * Cp * max(_rup4(k) for k in self.lat)
+        return self._run("xm_lat", n, xm_ch, mk, M * J * Cp * _rup4(self.lat[me]))
+
+    def chan_to_l(self, sp_ch):
+        """SP of all degrees, my channel slab -> SP of my degree slab, all channels."""
+        M, J, Cp, me = self.M, self.J, self.Cp, self.me
+        Cpm = _rup4(self.cs[me])
+
+        def mk(p, dst):
+            return self._desc(dst, self.l0[p] * M * J * Cpm, self.c0[me], (self.ls[p], M, J), self.cs[me],
+                              (M * J * Cpm, J * Cpm, Cpm), (M * J * Cp, J * Cp, Cp), tri=self.l0[p])
+        n = max(self.ls) * M * J * Cp
+        return self._run("sp_l", n, sp_ch, mk, self.ls[me] * M * J * Cp)
+
+    def l_to_chan(self, sp_l):
+        """SP of my degree slab, all channels -> SP of all degrees, my channel slab."""
+        M, J, Cp, me = self.M, self.J, self.Cp, self.me
+
+        def mk(p, dst):
+            Cpp = _rup4(self.cs[p])
+            return self._desc(dst, self.c0[p], self.l0[me] * M * J * Cpp, (self.ls[me], M, J), self.cs[p],
+                              (M * J * Cp, J * Cp, Cp), (M * J * Cpp, J * Cpp, Cpp), tri=self.l0[me])
+        n = self.L * M * J * max(_rup4(c) for c in self.cs)
+        return self._run("sp_ch", n, sp_l, mk, self.L * M * J * _rup4(self.cs[me]))
+
+
+def _polar_analysis(x, mod, scale_kind):
+    """x [B, C, K_loc, W] -> coefficients complex64 [B, C, L_loc, M]  (dft, lat->chan, Legendre analysis, chan->l)."""
+    B, Cn = x.shape[0], x.shape[1]
+    ex = _PolarExchange.of(mod, B, Cn, x.device)
+    plan = mod._peer_plan(x.device)
+    xm_loc = ops.dft_fwd(x.contiguous(), mod.mmax, mod._scale(x.device, scale_kind))
+    xm_ch = ex.lat_to_chan(xm_loc)
+    sp_ch = ops.legendre_analysis(plan, xm_ch, B, ex.cs[ex.me])
+    sp_l = ex.chan_to_l(sp_ch)
+    return ops.sp_to_c64(sp_l, B, Cn, ex.ls[ex.me], mod.mmax, ex.l0[ex.me], 0)
+
+
+def _polar_synthesis(c, mod, scale_kind, dtype):
+    """coefficients complex64 [B, C, L_loc, M] -> x [B, C, K_loc, W]  (l->chan, Legendre synthesis, chan->lat, idft)."""
+    B, Cn = c.shape[0], c.shape[1]
+    ex = _PolarExchange.of(mod, B, Cn, c.device)
+    plan = mod._peer_plan(c.device)
+    sp_l = ops.c64_to_sp(c.to(torch.complex64))
+    sp_ch = ex.l_to_chan(sp_l)
+    xm_ch = ops.legendre_synthesis(plan, sp_ch, B, ex.cs[ex.me])
+    xm_loc = ex.chan_to_lat(xm_ch)
+    return ops.dft_inv(xm_loc, B, Cn, ex.lat[ex.me], mod.nlon, mod.mmax, mod._scale(c.device, scale_kind), dtype)
+
+
+class _PolarSHT(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, mod):
+        ctx.mod, ctx.in_dtype = mod, x.dtype
+        return _polar_analysis(x, mod, "fwd")
+
+    @staticmethod
+    def backward(ctx, g):
+        return _polar_synthesis(g, ctx.mod, "rfft_adj", ctx.in_dtype), None
+
+
+class _PolarISHT(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, c, mod):
+        ctx.mod = mod
+        return _polar_synthesis(c, mod, "one", torch.float32)
+
+    @staticmethod
+    def backward(ctx, g):
+        return _polar_analysis(g, ctx.mod, "irfft_adj"), None
+
+
 class _DistributedMixin:
     def _setup_shards(self):
         self.comm_size_polar = polar_group_size()
@@ -261,6 +433,29 @@ class _DistributedMixin:
         self.lon_shapes = compute_split_shapes(self.nlon, self.comm_size_azimuth)
         self.l_shapes = compute_split_shapes(self.lmax, self.comm_size_polar)
         self.m_shapes = compute_split_shapes(self.mmax, self.comm_size_azimuth)
+
+    def _peer_path(self, x: torch.Tensor) -> bool:
+        """h-sharded only, CUDA + NCCL on one node: the exchanges run over peer memory (p2p.py)."""
+        return (x.is_cuda and self.comm_size_azimuth == 1 and 1 < self.comm_size_polar <= 8
+                and p2p.available(polar_group(), x.device))
+
+    def _peer_plan(self, device: torch.device) -> ops.Plan:
+        """Legendre table over the padded latitude order of the peer-memory path: slab p of the latitudes starts at
+        column sum(round_up(lat_shapes[:p], 8)); pad columns are zero."""
+        idx = device.index if device.index is not None else torch.cuda.current_device()
+        plans = self.__dict__.setdefault("_peer_plans", {})
+        p = plans.get(idx)
+        if p is None:
+            tab = self._table64()
+            kp = sum(_rup8(k) for k in self.lat_shapes)
+            padded = np.zeros(tab.shape[:2] + (kp,), dtype=np.float64)
+            src = dst = 0
+            for k in self.lat_shapes:
+                padded[:, :, dst:dst + k] = tab[:, :, src:src + k]
+                src, dst = src + k, dst + _rup8(k)
+            p = ops.Plan(kp, self.nlon, self.lmax, tab.shape[0], padded, m_offset=0, device=idx)
+            plans[idx] = p
+        return p
 
     def _table_slice(self):
         m0 = sum(self.m_shapes[: self.comm_rank_azimuth])
@@ -290,6 +485,9 @@ class DistributedRealSHT(_DistributedMixin, RealSHT):
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         if x.dim() != 4:
             raise ValueError(f"Expected a 4-d tensor [B, C, H_local, W_local], got {x.dim()} dims")
+        if self._peer_path(x):
+            ops.dtype_code(x.dtype)
+            return _PolarSHT.apply(x, self)
         num_chans = x.shape[1]
         if self.comm_size_azimuth > 1:
             x = distributed_transpose_azimuth.apply(x, (1, -1), self.lon_shapes)
@@ -318,6 +516,8 @@ class DistributedInverseRealSHT(_DistributedMixin, InverseRealSHT):
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         if x.dim() != 4:
             raise ValueError(f"Expected a 4-d tensor [B, C, L_local, M_local], got {x.dim()} dims")
+        if self._peer_path(x):
+            return _PolarISHT.apply(x, self)
         num_chans = x.shape[1]
         if self.comm_size_polar > 1:
             x = distributed_transpose_polar.apply(x, (1, -2), self.l_shapes)

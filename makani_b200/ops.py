@@ -64,13 +64,13 @@ class Plan:
         return self._h
 
     def __del__(self):
-        h = getattr(self, "_h", None)
-        if h is not None and h.value:
-            try:
+        try:                                   # module globals may already be gone at interpreter shutdown
+            h = getattr(self, "_h", None)
+            if h is not None and h.value:
                 _ext.load().sfno_plan_destroy(h)
-            except Exception:
-                pass
-            self._h = C.c_void_p()
+                self._h = None
+        except Exception:
+            pass
 
 
 def xm_elems(nlat, mmax, B, Cn):

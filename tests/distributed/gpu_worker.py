@@ -114,6 +114,12 @@ def main():
         dist.all_reduce(torch.view_as_real(gw), group=azimuth)
     errs["conv_dw"] = rel(gw, conv.weight.grad[..., sl_l])
 
+    # h-sharded runs must have gone through the peer-memory exchange unless it was switched off
+    st = thd.p2p.status()
+    if h > 1 and w == 1:
+        want = os.environ.get("MAKANI_B200_P2P", "1") != "0"
+        assert bool(st["enabled"]) == want and (st["exchanges"] > 0) == want, st
+
     torch.cuda.synchronize()
     worst = torch.tensor([max(errs.values())], device=dev)
     dist.all_reduce(worst, op=dist.ReduceOp.MAX)
@@ -125,7 +131,8 @@ def main():
         print(f"DIST_GPU_FAIL worst={float(worst):.3e}", flush=True)
         sys.exit(1)
     if rank == 0:
-        print(f"DIST_GPU_OK h={h} w={w} {nlat}x{nlon} worst={float(worst):.3e}", flush=True)
+        print(f"DIST_GPU_OK h={h} w={w} {nlat}x{nlon} worst={float(worst):.3e} exchange: {st['reason']} "
+              f"({st['exchanges']} peer-memory scatters)", flush=True)
 
 
 if __name__ == "__main__":

@@ -13,17 +13,19 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 WORKER = os.path.join(ROOT, "tests", "distributed", "gpu_worker.py")
 
 CASES = [
-    # h, w, nlat, nlon, grid, C, lmax, mmax
-    (2, 1, 37, 72, "equiangular", 6, None, None),          # uneven latitude split 19/18, generic DFT kernel
-    (1, 2, 32, 64, "legendre-gauss", 4, None, None),       # azimuth split: m 17/16
-    (2, 2, 37, 72, "equiangular", 6, 30, 31),
-    (4, 1, 240, 480, "legendre-gauss", 8, 240, 241),       # SFNO internal grid, fft480 kernels, l 60 x 4
-    (4, 1, 721, 1440, "equiangular", 8, 240, 241),         # config 4: 721 -> 181,181,181,178
+    # h, w, nlat, nlon, grid, C, lmax, mmax, peer-memory exchange (h-sharded only; "0" forces the all-to-all path)
+    (2, 1, 37, 72, "equiangular", 6, None, None, "1"),     # uneven latitude split 19/18, generic DFT kernel
+    (2, 1, 37, 72, "equiangular", 5, None, None, "1"),     # uneven channel split 3/2 (padded channel slabs)
+    (2, 1, 37, 72, "equiangular", 6, None, None, "0"),     # same through split / all_to_all / cat
+    (1, 2, 32, 64, "legendre-gauss", 4, None, None, "1"),  # azimuth split: m 17/16
+    (2, 2, 37, 72, "equiangular", 6, 30, 31, "1"),
+    (4, 1, 240, 480, "legendre-gauss", 8, 240, 241, "1"),  # SFNO internal grid, fft480 kernels, l 60 x 4
+    (4, 1, 721, 1440, "equiangular", 8, 240, 241, "1"),    # config 4: 721 -> 181,181,181,178
 ]
 
 
-@pytest.mark.parametrize("h,w,nlat,nlon,grid,C,lmax,mmax", CASES)
-def test_distributed_matches_single_gpu(built_lib, h, w, nlat, nlon, grid, C, lmax, mmax):
+@pytest.mark.parametrize("h,w,nlat,nlon,grid,C,lmax,mmax,p2p", CASES)
+def test_distributed_matches_single_gpu(built_lib, h, w, nlat, nlon, grid, C, lmax, mmax, p2p):
     n = torch.cuda.device_count() if torch.cuda.is_available() else 0
     if n < h * w:
         pytest.skip(f"needs {h * w} GPUs, {n} visible")
@@ -33,6 +35,7 @@ def test_distributed_matches_single_gpu(built_lib, h, w, nlat, nlon, grid, C, lm
            grid, str(C)]
     if lmax is not None:
         cmd += [str(lmax), str(mmax)]
-    res = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    env = dict(os.environ, MAKANI_B200_P2P=p2p)
+    res = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env)
     out = res.stdout + res.stderr
     assert res.returncode == 0 and "DIST_GPU_OK" in out, out[-3000:]

@@ -179,6 +179,23 @@ int sfno_rows_scatter(const float* src, const sfno_copy_desc* descs_host, int nd
  * they enqueue after it.  `epoch` must increase by one per barrier on the same flag arrays.                  */
 int sfno_peer_barrier(int* const* flags_host, int rank, int size, int epoch, void* stream);
 
+/* ---- longitude DFT fused with the latitude <-> channel exchange of the h-sharded transforms --------
+ * xm_ch_host[p] (p < nranks <= 8) is rank p's channel-sharded XM buffer  [mmax][2B][round_up(chan_shapes[p],4)][Kg]
+ * in peer memory (sfno_ipc_open); this rank's nlat_loc latitudes occupy columns [lat_off, lat_off + lat_span) of
+ * every one of them (lat_off multiple of 4, lat_span >= nlat_loc).
+ *   sfno_dft_fwd_peer : x [B][C][nlat_loc][nlon] -> every tile of spectrum is stored by the kernel's tensor stores
+ *                       straight into the buffer of the rank that owns its channel (no local XM, no separate exchange)
+ *   sfno_dft_inv_peer : the kernel's tensor loads fetch each tile from the owner of its channel -> y [B][C][nlat_loc][nlon]
+ * Only for the nlon = 480 / 1440 kernels (sfno_dft_peer_supported); callers order the ranks with sfno_peer_barrier
+ * (after the forward kernel / before the inverse kernel).                                                   */
+int sfno_dft_peer_supported(int nlon, int mmax);
+int sfno_dft_fwd_peer(const void* x, int x_dtype, int B, int C, int nlat_loc, int nlon, int mmax,
+                      const float* mscale_dev, void* const* xm_ch_host, const int* chan_shapes_host, int nranks, int Kg,
+                      int lat_off, int lat_span, int round_tf32, void* stream);
+int sfno_dft_inv_peer(void* const* xm_ch_host, const int* chan_shapes_host, int nranks, int Kg, int lat_off,
+                      int lat_span, int B, int C, int nlat_loc, int nlon, int mmax, int m_valid,
+                      const float* mscale_dev, void* y, int y_dtype, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

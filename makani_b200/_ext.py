@@ -50,6 +50,9 @@ _PROTOTYPES = {
     "sfno_ipc_free": (_i, [_vp]),
     "sfno_rows_scatter": (_i, [_vp, _vp, _i, _vp]),
     "sfno_peer_barrier": (_i, [_vp, _i, _i, _i, _vp]),
+    "sfno_dft_peer_supported": (_i, [_i, _i]),
+    "sfno_dft_fwd_peer": (_i, [_vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp]),
+    "sfno_dft_inv_peer": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _vp, _i, _vp]),
 }
 
 

@@ -212,4 +212,20 @@ int sfno_block_fwd(const sfno_plan* pf, const sfno_plan* pi, const void* x, int 
   return dft_inv(xm, B, Cout, pi->nlat, pi->nlon, pi->mmax, pi->mmax, pi->mscale + (pi->nlon / 2 + 1), y, dtype, s);
 }
 
+int sfno_dft_peer_supported(int nlon, int mmax) { return dft_peer_supported(nlon, mmax) ? 1 : 0; }
+int sfno_dft_fwd_peer(const void* x, int x_dtype, int B, int C, int nlat_loc, int nlon, int mmax,
+                      const float* mscale_dev, void* const* xm_ch_host, const int* chan_shapes_host, int nranks, int Kg,
+                      int lat_off, int lat_span, int round_tf32, void* stream) {
+  SFNO_CHECK(x && mscale_dev && xm_ch_host && chan_shapes_host, "null argument");
+  return dft_fwd_peer(x, x_dtype, B, C, nlat_loc, nlon, mmax, mscale_dev, xm_ch_host, chan_shapes_host, nranks, Kg,
+                      lat_off, lat_span, round_tf32, (cudaStream_t)stream);
+}
+int sfno_dft_inv_peer(void* const* xm_ch_host, const int* chan_shapes_host, int nranks, int Kg, int lat_off,
+                      int lat_span, int B, int C, int nlat_loc, int nlon, int mmax, int m_valid,
+                      const float* mscale_dev, void* y, int y_dtype, void* stream) {
+  SFNO_CHECK(y && mscale_dev && xm_ch_host && chan_shapes_host, "null argument");
+  return dft_inv_peer(xm_ch_host, chan_shapes_host, nranks, Kg, lat_off, lat_span, B, C, nlat_loc, nlon, mmax, m_valid,
+                      mscale_dev, y, y_dtype, (cudaStream_t)stream);
+}
+
 }  // extern "C"

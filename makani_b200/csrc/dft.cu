@@ -581,4 +581,58 @@ int dft_inv(const float* xm, int B, int C, int nlat, int nlon, int mmax, int m_v
 #undef SFNO_DISPATCH_INV
 }
 
+// ---- h-sharded transforms: the DFT kernels address the channel-sharded XM_ch buffers of all ranks (peer memory)
+bool dft_peer_supported(int nlon, int mmax) {
+  const char* env = getenv("SFNO_FORCE_GENERIC_DFT");
+  if (env && env[0] == '1') return false;
+  return (nlon == 480 || nlon == 1440) && mmax <= 241 && !use_lane_fft();
+}
+
+int dft_fwd_peer(const void* x, int x_dtype, int B, int C, int nlat_loc, int nlon, int mmax, const float* mscale,
+                 void* const* xm_ch, const int* chan_shapes, int nranks, int Kg, int lat_off, int lat_span,
+                 int round_out, cudaStream_t stream) {
+  SFNO_CHECK(dft_peer_supported(nlon, mmax), "peer DFT: only the nlon = 480 / 1440 kernels (mmax <= 241)");
+  SFNO_CHECK((reinterpret_cast<uintptr_t>(x) & 15) == 0, "peer DFT: input rows must be 16-byte aligned");
+  PeerMaps pm;
+  if (make_peer_maps(&pm, xm_ch, chan_shapes, nranks, B, Kg, lat_off, lat_span, mmax)) return 1;
+  SFNO_CHECK(pm.c0[nranks] == C, "peer DFT: channel slabs do not add up to C");
+  const int pitch = round_up(nlat_loc, 16);
+#define SFNO_DISPATCH_FWD_PEER(T)                                                                                   \
+  do {                                                                                                              \
+    if (nlon == 480) return launch_fwd_p2_maps<1, T, PeerMaps>(x, B, C, nlat_loc, pitch, mmax, mscale, pm, round_out, stream); \
+    return launch_fwd_p2_maps<3, T, PeerMaps>(x, B, C, nlat_loc, pitch, mmax, mscale, pm, round_out, stream);       \
+  } while (0)
+  switch (x_dtype) {
+    case SFNO_F32: SFNO_DISPATCH_FWD_PEER(float);
+    case SFNO_BF16: SFNO_DISPATCH_FWD_PEER(__nv_bfloat16);
+    case SFNO_F16: SFNO_DISPATCH_FWD_PEER(__half);
+    default: SFNO_CHECK(false, "unsupported input dtype");
+  }
+#undef SFNO_DISPATCH_FWD_PEER
+}
+
+int dft_inv_peer(void* const* xm_ch, const int* chan_shapes, int nranks, int Kg, int lat_off, int lat_span, int B,
+                 int C, int nlat_loc, int nlon, int mmax, int m_valid, const float* mscale, void* y, int y_dtype,
+                 cudaStream_t stream) {
+  SFNO_CHECK(dft_peer_supported(nlon, mmax), "peer DFT: only the nlon = 480 / 1440 kernels (mmax <= 241)");
+  SFNO_CHECK((reinterpret_cast<uintptr_t>(y) & 15) == 0, "peer DFT: output rows must be 16-byte aligned");
+  m_valid = std::max(1, std::min(m_valid, mmax));
+  PeerMaps pm;
+  if (make_peer_maps(&pm, xm_ch, chan_shapes, nranks, B, Kg, lat_off, lat_span, m_valid)) return 1;
+  SFNO_CHECK(pm.c0[nranks] == C, "peer DFT: channel slabs do not add up to C");
+  const int pitch = round_up(nlat_loc, 16);
+#define SFNO_DISPATCH_INV_PEER(T)                                                                                   \
+  do {                                                                                                              \
+    if (nlon == 480) return launch_inv_p2_maps<1, T, PeerMaps>(pm, B, C, nlat_loc, pitch, m_valid, mscale, y, stream); \
+    return launch_inv_p2_maps<3, T, PeerMaps>(pm, B, C, nlat_loc, pitch, m_valid, mscale, y, stream);               \
+  } while (0)
+  switch (y_dtype) {
+    case SFNO_F32: SFNO_DISPATCH_INV_PEER(float);
+    case SFNO_BF16: SFNO_DISPATCH_INV_PEER(__nv_bfloat16);
+    case SFNO_F16: SFNO_DISPATCH_INV_PEER(__half);
+    default: SFNO_CHECK(false, "unsupported output dtype");
+  }
+#undef SFNO_DISPATCH_INV_PEER
+}
+
 }  // namespace sfno

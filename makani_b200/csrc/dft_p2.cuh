@@ -45,6 +45,60 @@ __device__ __forceinline__ void tma_store_3d(const CUtensorMap* m, const void* s
                ::"l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2) : "memory");
 }
 
+__device__ __forceinline__ void tma_store_4d(const CUtensorMap* m, const void* smem_src, int c0, int c1, int c2, int c3) {
+  asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];"
+               ::"l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+               : "memory");
+}
+
+// h-sharded transforms (distributed/p2p.py): the XM side of the DFT kernels is not the local XM tensor but the
+// channel-sharded XM_ch buffers of ALL ranks, in peer memory - channel c belongs to rank p with c0[p] <= c < c0[p+1],
+// whose buffer is [m][2B][Cp_p][Kg]; map[p] views the columns of THIS rank's latitude slab in it as
+// (lat, c - c0[p], j, m).  The forward kernel stores its staging tiles there (the latitude -> channel exchange rides
+// on the tensor stores), the inverse kernel loads its tiles from there (channel -> latitude).
+constexpr int kMaxPeers = 8;
+struct PeerMaps {
+  CUtensorMap map[kMaxPeers];
+  int c0[kMaxPeers + 1];
+  int n;
+};
+struct LocalMap {
+  CUtensorMap map;
+};
+
+// tile (16 latitudes lat0.. of channel c / flat position f0 = c*pitch + lat0, batch b, plane reim) <-> XM
+template <class MAPS>
+struct XmTile;
+template <>
+struct XmTile<LocalMap> {
+  static constexpr bool kDist = false;
+  __device__ static void prefetch(const LocalMap& m) { tma_prefetch_desc(&m.map); }
+  __device__ static void store(const LocalMap& m, const void* src, int f0, int, int j) { tma_store_3d(&m.map, src, f0, j, 0); }
+  __device__ static void load(const LocalMap& m, void* dst, uint64_t* bar, int f0, int, int j) {
+    tma_load_3d(dst, &m.map, bar, f0, j, 0);
+  }
+};
+template <>
+struct XmTile<PeerMaps> {
+  static constexpr bool kDist = true;
+  __device__ static void prefetch(const PeerMaps& m) {
+    for (int p = 0; p < m.n; ++p) tma_prefetch_desc(&m.map[p]);
+  }
+  __device__ static int owner(const PeerMaps& m, int c) {
+    int p = 0;
+    while (p + 1 < m.n && c >= m.c0[p + 1]) ++p;
+    return p;
+  }
+  __device__ static void store(const PeerMaps& m, const void* src, int f0, int pitch, int j) {
+    const int c = f0 / pitch, p = owner(m, c);
+    tma_store_4d(&m.map[p], src, f0 - c * pitch, c - m.c0[p], j, 0);
+  }
+  __device__ static void load(const PeerMaps& m, void* dst, uint64_t* bar, int f0, int pitch, int j) {
+    const int c = f0 / pitch, p = owner(m, c);
+    tma_load_4d(dst, &m.map[p], bar, f0 - c * pitch, c - m.c0[p], j, 0);
+  }
+};
+
 // XM viewed as [m][j = b*2 + reim][f = c*Kp + lat]; box = 16 flat positions x 241 bins of one (b, re/im) plane.
 // mdim bounds the bins (loads beyond it read zeros, stores beyond it are dropped).
 static int xm_stage_map(CUtensorMap* map, const float* xm, int B, int C, int Kp, int mdim) {
@@ -104,9 +158,9 @@ struct P2FwdSmem {
   static constexpr int kCtasPerSm = kFit >= 3 ? 3 : (kFit >= 2 ? 2 : 1);
 };
 
-template <int R, typename T, int NBUF, bool ROUND, int OCC>
+template <int R, typename T, int NBUF, bool ROUND, int OCC, class MAPS>
 __global__ void __launch_bounds__(256, OCC)
-dft_fwd_p2_kernel(const T* __restrict__ x, const __grid_constant__ CUtensorMap xm_map,
+dft_fwd_p2_kernel(const T* __restrict__ x, const __grid_constant__ MAPS xm_map,
                   const fl::cf* __restrict__ tables, const float* __restrict__ mscale, int B, int C, int K, int Kp,
                   int M, int* __restrict__ sched) {
   using S = P2FwdSmem<R, T, NBUF>;
@@ -127,7 +181,7 @@ dft_fwd_p2_kernel(const T* __restrict__ x, const __grid_constant__ CUtensorMap x
   for (int j = tid; j < kTwCount; j += 256) tw[j] = tables[j];
   for (int j = tid; j < 244; j += 256) hs[j] = j < M ? 0.5f * mscale[j] : 0.f;
   if (tid == 0) {
-    tma_prefetch_desc(&xm_map);
+    XmTile<MAPS>::prefetch(xm_map);
     for (int b = 0; b < NBUF; ++b) mbar_init(&full[b], 1);
     fence_barrier_init();
   }
@@ -229,8 +283,8 @@ dft_fwd_p2_kernel(const T* __restrict__ x, const __grid_constant__ CUtensorMap x
     // ---- staging tile -> XM: one tensor store per plane (16 latitudes x 241 bins; bins >= M and positions beyond
     //      C*Kp are clipped by the tensor map)
     if (tid == 0) {
-      tma_store_3d(&xm_map, stage, f0, 2 * b, 0);
-      tma_store_3d(&xm_map, stage + kPlaneFloats, f0, 2 * b + 1, 0);
+      XmTile<MAPS>::store(xm_map, stage, f0, Kp, 2 * b);
+      XmTile<MAPS>::store(xm_map, stage + kPlaneFloats, f0, Kp, 2 * b + 1);
       bulk_commit();
     }
   }
@@ -275,9 +329,9 @@ struct P2InvDepth {
 //                                 tensor loads, which then overlap the whole transform of tile it
 // The output rows are private to their 16-lane group: lane 0 of the group stores its row with one bulk copy and waits
 // for that copy's shared-memory read just before the group writes the row again (one tile later).
-template <int R, typename T, int NST>
+template <int R, typename T, int NST, class MAPS>
 __global__ void __launch_bounds__(256, P2InvSmem<R, T, NST>::kCtasPerSm)
-dft_inv_p2_kernel(const __grid_constant__ CUtensorMap xm_map, T* __restrict__ y, const fl::cf* __restrict__ tables,
+dft_inv_p2_kernel(const __grid_constant__ MAPS xm_map, T* __restrict__ y, const fl::cf* __restrict__ tables,
                   const float* __restrict__ mscale, int B, int C, int K, int Kp, int m_valid, int* __restrict__ sched) {
   using S = P2InvSmem<R, T, NST>;
   constexpr int W = S::W;
@@ -293,7 +347,7 @@ dft_inv_p2_kernel(const __grid_constant__ CUtensorMap xm_map, T* __restrict__ y,
   for (int j = tid; j < 244; j += 256) msc[j] = j < m_valid ? mscale[j] : 0.f;
   if (tid == 0) {
     if (smem_u32(smp2) & 511u) __trap();
-    tma_prefetch_desc(&xm_map);
+    XmTile<MAPS>::prefetch(xm_map);
     for (int j = 0; j < NST; ++j) {
       mbar_init(full + j, 1);
       mbar_init(consumed + j, 8);
@@ -330,8 +384,8 @@ dft_inv_p2_kernel(const __grid_constant__ CUtensorMap xm_map, T* __restrict__ y,
     const int b = t / tiles_per_b;
     const int f0 = (t - b * tiles_per_b) * kRows;
     mbar_arrive_expect_tx(full + buf, 2u * 241u * 64u);
-    tma_load_3d(dst, &xm_map, full + buf, f0, 2 * b, 0);
-    tma_load_3d(dst + kPlaneFloats, &xm_map, full + buf, f0, 2 * b + 1, 0);
+    XmTile<MAPS>::load(xm_map, dst, full + buf, f0, Kp, 2 * b);
+    XmTile<MAPS>::load(xm_map, dst + kPlaneFloats, full + buf, f0, Kp, 2 * b + 1);
   };
   if (tid == 0) {
     for (int j = 0; j < NST; ++j) claim(j, j);
@@ -400,9 +454,11 @@ static int p2_prepare(Kern kern, int smem_bytes) {
   return 0;
 }
 
-template <int R, typename T>
-static int launch_fwd_p2(const void* x, int B, int C, int K, int Kp, int M, const float* mscale, float* xm,
-                         int round_out, cudaStream_t stream) {
+// maps: LocalMap (XM tensor of this GPU, pitch = Kp) or PeerMaps (channel-sharded XM_ch buffers of all ranks,
+// pitch = round_up(K, 16): tiles never straddle two channels there)
+template <int R, typename T, class MAPS>
+static int launch_fwd_p2_maps(const void* x, int B, int C, int K, int pitch, int M, const float* mscale, const MAPS& maps,
+                              int round_out, cudaStream_t stream) {
   // 16-bit rows at R = 3: a single row buffer lets two CTAs share an SM (16 warps instead of 8)
   constexpr int NBUF = (R == 3 && sizeof(T) == 2) ? 1 : 2;
   using S = P2FwdSmem<R, T, NBUF>;
@@ -410,24 +466,53 @@ static int launch_fwd_p2(const void* x, int B, int C, int K, int Kp, int M, cons
   constexpr int OCC = S::kCtasPerSm;
   const fl::cf* tables;
   if (get_p2_tables(&tables)) return 1;
-  CUtensorMap map;
-  if (xm_stage_map(&map, xm, B, C, Kp, M)) return 1;
   static bool attr = false;
   if (!attr) {
-    SFNO_CUDA(cudaFuncSetAttribute(dft_fwd_p2_kernel<R, T, NBUF, true, OCC>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kBytes));
-    SFNO_CUDA(cudaFuncSetAttribute(dft_fwd_p2_kernel<R, T, NBUF, false, OCC>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kBytes));
+    SFNO_CUDA(cudaFuncSetAttribute(dft_fwd_p2_kernel<R, T, NBUF, true, OCC, MAPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kBytes));
+    SFNO_CUDA(cudaFuncSetAttribute(dft_fwd_p2_kernel<R, T, NBUF, false, OCC, MAPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kBytes));
     attr = true;
   }
-  const int ntiles = ((C * Kp + kRows - 1) / kRows) * B;
+  const int ntiles = ((C * pitch + kRows - 1) / kRows) * B;
   const int grid = std::min(ntiles, OCC * sm_count());
   int* sched = sched_counters();
   SFNO_CHECK(sched != nullptr, "could not allocate the tile scheduler counters");
   if (round_out)
-    SFNO_CUDA(launch_pdl(dft_fwd_p2_kernel<R, T, NBUF, true, OCC>, dim3(grid), dim3(256), S::kBytes, stream,
-                         static_cast<const T*>(x), map, tables, mscale, B, C, K, Kp, M, sched));
+    SFNO_CUDA(launch_pdl(dft_fwd_p2_kernel<R, T, NBUF, true, OCC, MAPS>, dim3(grid), dim3(256), S::kBytes, stream,
+                         static_cast<const T*>(x), maps, tables, mscale, B, C, K, pitch, M, sched));
   else
-    SFNO_CUDA(launch_pdl(dft_fwd_p2_kernel<R, T, NBUF, false, OCC>, dim3(grid), dim3(256), S::kBytes, stream,
-                         static_cast<const T*>(x), map, tables, mscale, B, C, K, Kp, M, sched));
+    SFNO_CUDA(launch_pdl(dft_fwd_p2_kernel<R, T, NBUF, false, OCC, MAPS>, dim3(grid), dim3(256), S::kBytes, stream,
+                         static_cast<const T*>(x), maps, tables, mscale, B, C, K, pitch, M, sched));
+  SFNO_LAUNCHED();
+  return 0;
+}
+
+template <int R, typename T>
+static int launch_fwd_p2(const void* x, int B, int C, int K, int Kp, int M, const float* mscale, float* xm,
+                         int round_out, cudaStream_t stream) {
+  LocalMap lm;
+  if (xm_stage_map(&lm.map, xm, B, C, Kp, M)) return 1;
+  return launch_fwd_p2_maps<R, T, LocalMap>(x, B, C, K, Kp, M, mscale, lm, round_out, stream);
+}
+
+template <int R, typename T, class MAPS>
+static int launch_inv_p2_maps(const MAPS& maps, int B, int C, int K, int pitch, int m_valid, const float* mscale,
+                              void* y, cudaStream_t stream) {
+  constexpr int NST = P2InvDepth<R, T>::value;
+  using S = P2InvSmem<R, T, NST>;
+  static_assert(S::kBytes <= 227 * 1024, "inverse DFT tile does not fit shared memory");
+  const fl::cf* tables;
+  if (get_p2_tables(&tables)) return 1;
+  static bool attr = false;
+  if (!attr) {
+    if (p2_prepare(dft_inv_p2_kernel<R, T, NST, MAPS>, S::kBytes)) return 1;
+    attr = true;
+  }
+  const int ntiles = ((C * pitch + kRows - 1) / kRows) * B;
+  const int grid = std::min(ntiles, S::kCtasPerSm * sm_count());
+  int* sched = sched_counters();
+  SFNO_CHECK(sched != nullptr, "could not allocate the tile scheduler counters");
+  SFNO_CUDA(launch_pdl(dft_inv_p2_kernel<R, T, NST, MAPS>, dim3(grid), dim3(256), S::kBytes, stream, maps,
+                       static_cast<T*>(y), tables, mscale, B, C, K, pitch, m_valid, sched));
   SFNO_LAUNCHED();
   return 0;
 }
@@ -435,25 +520,34 @@ static int launch_fwd_p2(const void* x, int B, int C, int K, int Kp, int M, cons
 template <int R, typename T>
 static int launch_inv_p2(const float* xm, int B, int C, int K, int Kp, int M, int m_valid, const float* mscale,
                          void* y, cudaStream_t stream) {
-  constexpr int NST = P2InvDepth<R, T>::value;
-  using S = P2InvSmem<R, T, NST>;
-  static_assert(S::kBytes <= 227 * 1024, "inverse DFT tile does not fit shared memory");
-  const fl::cf* tables;
-  if (get_p2_tables(&tables)) return 1;
-  CUtensorMap map;
-  if (xm_stage_map(&map, xm, B, C, Kp, std::max(1, std::min(M, m_valid)))) return 1;
-  static bool attr = false;
-  if (!attr) {
-    if (p2_prepare(dft_inv_p2_kernel<R, T, NST>, S::kBytes)) return 1;
-    attr = true;
+  LocalMap lm;
+  if (xm_stage_map(&lm.map, xm, B, C, Kp, std::max(1, std::min(M, m_valid)))) return 1;
+  return launch_inv_p2_maps<R, T, LocalMap>(lm, B, C, K, Kp, std::min(M, m_valid), mscale, y, stream);
+}
+
+// channel-sharded XM_ch buffers of all ranks as seen from this rank's latitude slab (see PeerMaps)
+static int make_peer_maps(PeerMaps* pm, void* const* xm_ch, const int* chan_shapes, int nranks, int B, int Kg,
+                          int lat_off, int lat_span, int mdim) {
+  SFNO_CHECK(nranks >= 1 && nranks <= kMaxPeers, "peer DFT: 1..8 ranks");
+  SFNO_CHECK(lat_off % 4 == 0 && lat_span > 0 && lat_off + lat_span <= Kg && Kg % 4 == 0, "peer DFT: bad latitude slab");
+  pm->n = nranks;
+  int c = 0;
+  for (int p = 0; p < nranks; ++p) {
+    pm->c0[p] = c;
+    c += chan_shapes[p];
+    const int Cpp = (chan_shapes[p] + 3) & ~3;
+    if (chan_shapes[p] == 0) {
+      pm->map[p] = pm->map[0];                    // never addressed (no channel maps to it)
+      continue;
+    }
+    SFNO_CHECK(xm_ch[p] != nullptr, "peer DFT: null buffer");
+    uint64_t dims[4] = {(uint64_t)lat_span, (uint64_t)chan_shapes[p], (uint64_t)2 * B, (uint64_t)mdim};
+    uint64_t str[3] = {(uint64_t)Kg * 4, (uint64_t)Cpp * Kg * 4, (uint64_t)2 * B * Cpp * Kg * 4};
+    uint32_t box[4] = {16, 1, 1, 241};
+    if (encode_tensor_map(&pm->map[p], static_cast<const float*>(xm_ch[p]) + lat_off, 4, dims, str, box, 3)) return 1;
   }
-  const int ntiles = ((C * Kp + kRows - 1) / kRows) * B;
-  const int grid = std::min(ntiles, S::kCtasPerSm * sm_count());
-  int* sched = sched_counters();
-  SFNO_CHECK(sched != nullptr, "could not allocate the tile scheduler counters");
-  SFNO_CUDA(launch_pdl(dft_inv_p2_kernel<R, T, NST>, dim3(grid), dim3(256), S::kBytes, stream, map, static_cast<T*>(y),
-                       tables, mscale, B, C, K, Kp, std::min(M, m_valid), sched));
-  SFNO_LAUNCHED();
+  for (int p = nranks; p <= kMaxPeers; ++p) pm->c0[p] = c;
+  for (int p = nranks; p < kMaxPeers; ++p) pm->map[p] = pm->map[0];
   return 0;
 }
 

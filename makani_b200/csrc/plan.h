@@ -32,4 +32,12 @@ int dft_fwd(const void* x, int x_dtype, int B, int C, int nlat, int nlon, int mm
 int dft_inv(const float* xm, int B, int C, int nlat, int nlon, int mmax, int m_valid, const float* mscale,
             void* y, int y_dtype, cudaStream_t stream);
 
+bool dft_peer_supported(int nlon, int mmax);
+int dft_fwd_peer(const void* x, int x_dtype, int B, int C, int nlat_loc, int nlon, int mmax, const float* mscale,
+                 void* const* xm_ch, const int* chan_shapes, int nranks, int Kg, int lat_off, int lat_span,
+                 int round_out, cudaStream_t stream);
+int dft_inv_peer(void* const* xm_ch, const int* chan_shapes, int nranks, int Kg, int lat_off, int lat_span, int B,
+                 int C, int nlat_loc, int nlon, int mmax, int m_valid, const float* mscale, void* y, int y_dtype,
+                 cudaStream_t stream);
+
 }  // namespace sfno

@@ -25,6 +25,8 @@ stores rows of the internal layout straight into the owner's buffer in peer memo
 """
 from __future__ import annotations
 
+import ctypes as ct
+import os
 from typing import List, Optional
 
 import numpy as np
@@ -41,6 +43,14 @@ __all__ = ["init", "is_initialized", "polar_group", "azimuth_group", "polar_grou
            "distributed_transpose_polar", "distributed_transpose_azimuth", "DistributedRealSHT",
            "DistributedInverseRealSHT"]
 
+# Which transforms fuse the longitude DFT with the latitude <-> channel exchange (tensor stores / loads on peer memory,
+# csrc/dft_p2.cuh PeerMaps) instead of running the DFT locally and moving rows with sfno_rows_scatter.  The fused
+# kernels touch peer memory in the 64-byte pieces of their staging tiles (16 latitudes x 4 bytes per bin), the row
+# scatter in whole latitude slabs (0.2 - 1.5 KB), and NVLink is far less efficient at 64 bytes.  Measured, C = 384,
+# SHT / inverse SHT in ms (fused vs DFT + scatter):  721x1440 h = 2: 0.63 / 0.70 vs 0.70 / 0.78;  721x1440 h = 4:
+# 0.66 / 0.65 vs 0.61 / 0.61;  240x480 h = 2: 0.30 / 0.32 vs 0.28 / 0.30.  So "auto" fuses only nlon = 1440 on two
+# ranks (where the three FFTs per row hide the slower link traffic); "all" / "0" force either side.
+_FUSED_DFT = os.environ.get("MAKANI_B200_P2P_FUSED_DFT", "auto")
 _POLAR_GROUP = None
 _AZIMUTH_GROUP = None
 _IS_INITIALIZED = False
@@ -354,6 +364,57 @@ class _PolarExchange:
         n = M * J * Cp * max(_rup4(k) for k in self.lat)
         return self._run("xm_lat", n, xm_ch, mk, M * J * Cp * _rup4(self.lat[me]))
 
+    # ---- longitude DFT fused with the exchange (csrc/dft_p2.cuh, PeerMaps): nlon = 480 / 1440 only
+    def dft_fused(self, mod) -> bool:
+        if _FUSED_DFT == "0" or (_FUSED_DFT != "all" and not (mod.nlon == 1440 and self.h == 2)):
+            return False
+        return bool(_ext.load().sfno_dft_peer_supported(mod.nlon, mod.mmax))
+
+    def _xm_ch_buffers(self):
+        M, J = self.M, self.J
+        n = M * J * max(_rup4(c) for c in self.cs) * self.Kpg
+        plan = self._plans.get("xm_ch_fused")
+        if plan is None:
+            pb = p2p.buffers(("xm_ch", self.B, self.C, self.M, self.L, self.Kpg), n, self.group, self.device)
+            ptrs = [(ct.c_void_p * self.h)(*pb.peer_ptrs[b]) for b in range(2)]
+            shapes = (ct.c_int * self.h)(*self.cs)
+            plan = (pb, ptrs, shapes, p2p.fence(self.group, self.device))
+            self._plans["xm_ch_fused"] = plan
+        return plan
+
+    def dft_to_chan(self, x, mscale):
+        """x [B, C, K_loc, W] -> XM of all latitudes, my channel slab: the DFT kernel's tensor stores write every tile
+        into the buffer of the rank that owns its channel."""
+        pb, ptrs, shapes, fence = self._xm_ch_buffers()
+        b = pb.next()
+        me = self.me
+        _ext.check(_ext.load().sfno_dft_fwd_peer(
+            ct.c_void_p(x.data_ptr()), ops.dtype_code(x.dtype), self.B, self.C, self.lat[me], x.shape[-1], self.M,
+            ct.c_void_p(mscale.data_ptr()), ct.cast(ptrs[b], ct.c_void_p), ct.cast(shapes, ct.c_void_p), self.h, self.Kpg,
+            self.latp0[me], _rup8(self.lat[me]), 1, ct.c_void_p(torch.cuda.current_stream().cuda_stream)),
+            "sfno_dft_fwd_peer")
+        p2p._STATUS["exchanges"] += 1
+        fence()
+        return pb.local[b][: self.M * self.J * _rup4(self.cs[me]) * self.Kpg]
+
+    def chan_to_field(self, plan, sp_ch, nlon, mscale, dtype):
+        """SP of all degrees, my channel slab -> field [B, C, K_loc, W]: Legendre synthesis into my XM_ch buffer, then
+        every rank's inverse DFT kernel loads its tiles from the owners' buffers."""
+        pb, ptrs, shapes, fence = self._xm_ch_buffers()
+        b = pb.next()
+        me = self.me
+        ops.legendre_synthesis(plan, sp_ch, self.B, self.cs[me],
+                               out=pb.local[b][: self.M * self.J * _rup4(self.cs[me]) * self.Kpg])
+        fence()
+        y = torch.empty((self.B, self.C, self.lat[me], nlon), dtype=dtype, device=self.device)
+        _ext.check(_ext.load().sfno_dft_inv_peer(
+            ct.cast(ptrs[b], ct.c_void_p), ct.cast(shapes, ct.c_void_p), self.h, self.Kpg, self.latp0[me],
+            _rup8(self.lat[me]), self.B, self.C, self.lat[me], nlon, self.M, self.M, ct.c_void_p(mscale.data_ptr()),
+            ct.c_void_p(y.data_ptr()), ops.dtype_code(dtype), ct.c_void_p(torch.cuda.current_stream().cuda_stream)),
+            "sfno_dft_inv_peer")
+        p2p._STATUS["exchanges"] += 1
+        return y
+
     def chan_to_l(self, sp_ch):
         """SP of all degrees, my channel slab -> SP of my degree slab, all channels."""
         M, J, Cp, me = self.M, self.J, self.Cp, self.me
@@ -382,8 +443,12 @@ def _polar_analysis(x, mod, scale_kind):
     B, Cn = x.shape[0], x.shape[1]
     ex = _PolarExchange.of(mod, B, Cn, x.device)
     plan = mod._peer_plan(x.device)
-    xm_loc = ops.dft_fwd(x.contiguous(), mod.mmax, mod._scale(x.device, scale_kind))
-    xm_ch = ex.lat_to_chan(xm_loc)
+    x = x.contiguous()
+    if ex.dft_fused(mod) and x.data_ptr() % 16 == 0:
+        xm_ch = ex.dft_to_chan(x, mod._scale(x.device, scale_kind))
+    else:
+        xm_loc = ops.dft_fwd(x, mod.mmax, mod._scale(x.device, scale_kind))
+        xm_ch = ex.lat_to_chan(xm_loc)
     sp_ch = ops.legendre_analysis(plan, xm_ch, B, ex.cs[ex.me])
     sp_l = ex.chan_to_l(sp_ch)
     return ops.sp_to_c64(sp_l, B, Cn, ex.ls[ex.me], mod.mmax, ex.l0[ex.me], 0)
@@ -396,6 +461,8 @@ def _polar_synthesis(c, mod, scale_kind, dtype):
     plan = mod._peer_plan(c.device)
     sp_l = ops.c64_to_sp(c.to(torch.complex64))
     sp_ch = ex.l_to_chan(sp_l)
+    if ex.dft_fused(mod):
+        return ex.chan_to_field(plan, sp_ch, mod.nlon, mod._scale(c.device, scale_kind), dtype)
     xm_ch = ops.legendre_synthesis(plan, sp_ch, B, ex.cs[ex.me])
     xm_loc = ex.chan_to_lat(xm_ch)
     return ops.dft_inv(xm_loc, B, Cn, ex.lat[ex.me], mod.nlon, mod.mmax, mod._scale(c.device, scale_kind), dtype)

@@ -139,8 +139,11 @@ def legendre_analysis(plan: Plan, xm: torch.Tensor, B: int, Cn: int, round_tf32:
     return sp
 
 
-def legendre_synthesis(plan: Plan, sp: torch.Tensor, B: int, Cn: int) -> torch.Tensor:
-    xm = torch.empty(xm_elems(plan.nlat, plan.mmax, B, Cn), dtype=torch.float32, device=sp.device)
+def legendre_synthesis(plan: Plan, sp: torch.Tensor, B: int, Cn: int, out: torch.Tensor = None) -> torch.Tensor:
+    n = xm_elems(plan.nlat, plan.mmax, B, Cn)
+    if out is not None and (out.numel() != n or out.dtype != torch.float32 or not out.is_contiguous()):
+        raise ValueError("legendre_synthesis: `out` must be a contiguous float32 buffer of xm_elems() floats")
+    xm = out if out is not None else torch.empty(n, dtype=torch.float32, device=sp.device)
     _ext.check(_ext.load().sfno_legendre_synthesis(plan.handle, _ptr(sp), B, Cn, _ptr(xm), _stream()),
                "sfno_legendre_synthesis")
     return xm

@@ -17,6 +17,8 @@ CASES = [
     (2, 1, 37, 72, "equiangular", 6, None, None, "1"),     # uneven latitude split 19/18, generic DFT kernel
     (2, 1, 37, 72, "equiangular", 5, None, None, "1"),     # uneven channel split 3/2 (padded channel slabs)
     (2, 1, 37, 72, "equiangular", 6, None, None, "0"),     # same through split / all_to_all / cat
+    (2, 1, 60, 480, "legendre-gauss", 6, 60, 61, "1"),     # fft480 kernels: DFT fused with the exchange (tensor stores /
+    (2, 1, 45, 1440, "equiangular", 5, 40, 41, "1"),       #   loads on peer memory), R = 1 and R = 3, uneven slabs 23/22, 3/2
     (1, 2, 32, 64, "legendre-gauss", 4, None, None, "1"),  # azimuth split: m 17/16
     (2, 2, 37, 72, "equiangular", 6, 30, 31, "1"),
     (4, 1, 240, 480, "legendre-gauss", 8, 240, 241, "1"),  # SFNO internal grid, fft480 kernels, l 60 x 4
@@ -35,7 +37,7 @@ def test_distributed_matches_single_gpu(built_lib, h, w, nlat, nlon, grid, C, lm
            grid, str(C)]
     if lmax is not None:
         cmd += [str(lmax), str(mmax)]
-    env = dict(os.environ, MAKANI_B200_P2P=p2p)
+    env = dict(os.environ, MAKANI_B200_P2P=p2p, MAKANI_B200_P2P_FUSED_DFT="all")   # fused kernels at 480 and 1440
     res = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env)
     out = res.stdout + res.stderr
     assert res.returncode == 0 and "DIST_GPU_OK" in out, out[-3000:]

@@ -68,9 +68,18 @@ def make_mod(rank, h, nlat, L, M):
                                  lat_shapes=compute_split_shapes(nlat, h), l_shapes=compute_split_shapes(L, h))
 
 
-@pytest.mark.parametrize("h,nlat,L,M,B,C", [(2, 37, 20, 21, 1, 6), (3, 23, 17, 9, 2, 7), (4, 41, 33, 34, 1, 10),
-                                            (4, 16, 16, 17, 1, 8)])
+CASES = [(2, 37, 20, 21, 1, 6), (3, 23, 17, 9, 2, 7), (4, 41, 33, 34, 1, 10), (4, 16, 16, 17, 1, 8)]
+
+
+@pytest.mark.parametrize("h,nlat,L,M,B,C", CASES)
 def test_exchange_descriptors_realise_the_transpositions(fake_peer_memory, h, nlat, L, M, B, C):
+    check_exchange(fake_peer_memory, h, nlat, L, M, B, C, torch.device("cpu"))
+
+
+def check_exchange(state, h, nlat, L, M, B, C, device):
+    """Run the four exchanges for h ranks (one after the other in this process; `state` selects the acting rank for the
+    patched p2p.buffers) and compare with the transpositions of a global tensor.  Shared with the single-GPU kernel
+    test (tests/test_gpu_kernels.py), where the buffers are device memory and the scatter is the CUDA kernel."""
     rng = np.random.default_rng(0)
     J = 2 * B
     lat, cs, ls = compute_split_shapes(nlat, h), compute_split_shapes(C, h), compute_split_shapes(L, h)
@@ -78,20 +87,20 @@ def test_exchange_descriptors_realise_the_transpositions(fake_peer_memory, h, nl
     latp0 = np.cumsum([0] + [_rup8(k) for k in lat])
     Kpg = int(latp0[-1])
     Cp = _rup4(C)
-    fake_peer_memory["h"] = h
+    state["h"] = h
     xm = rng.standard_normal((M, J, C, nlat)).astype(np.float32)          # global XM[m][j][c][k]
     sp = rng.standard_normal((L, M, J, C)).astype(np.float32)             # global SP[l][m][j][c]
     exs = []
     for r in range(h):
-        fake_peer_memory["rank"] = r
-        exs.append(_PolarExchange(make_mod(r, h, nlat, L, M), B, C, torch.device("cpu")))
+        state["rank"] = r
+        exs.append(_PolarExchange(make_mod(r, h, nlat, L, M), B, C, device))
 
     def run_all(method, make_src):
         outs = []
         for r in range(h):                    # all ranks scatter ...
-            fake_peer_memory["rank"] = r
-            outs.append(getattr(exs[r], method)(torch.from_numpy(make_src(r))))
-        return [o.numpy().copy() for o in outs]   # ... then everybody reads its receive buffer
+            state["rank"] = r
+            outs.append(getattr(exs[r], method)(torch.from_numpy(np.ascontiguousarray(make_src(r))).to(device)))
+        return [o.cpu().numpy().copy() for o in outs]   # ... then everybody reads its receive buffer
 
     # ---- lat -> chan: rank r holds XM_loc [M][J][Cp][Kl], ends with XM_ch [M][J][Cp_r][Kpg] (padded latitude order)
     def xm_loc(r):

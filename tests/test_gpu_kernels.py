@@ -205,3 +205,68 @@ def test_bias(ops):
     b1 = torch.randn(1, 5, 7, 9, device=_dev())
     assert torch.allclose(ops.add_bias_(y.clone(), b0), y + b0)
     assert torch.allclose(ops.add_bias_(y.clone(), b1), y + b1)
+
+
+# ------------------------------------------------------------------------------------------------ peer-memory exchange
+@pytest.mark.parametrize("h,nlat,L,M,B,C", [(2, 37, 20, 21, 1, 6), (3, 23, 17, 9, 2, 7), (4, 48, 33, 34, 1, 16)])
+def test_rows_scatter_and_peer_barrier_single_gpu(built_lib, monkeypatch, h, nlat, L, M, B, C):
+    """The exchange kernels of the h-sharded transforms (sfno_rows_scatter into sfno_ipc_alloc'ed buffers, then
+    sfno_peer_barrier) on ONE GPU: the h ranks are played one after the other by this process, every 'peer' buffer is
+    a buffer of this device.  Same checks as the CPU emulation (tests/test_exchange_cpu.py); the multi-GPU runs over
+    NVLink are in tests/test_gpu_distributed.py.  (4, 48, ..., 16): 16-byte aligned everywhere -> the vector kernel.)"""
+    import ctypes as C_
+    import makani_b200.distributed as thd
+    from makani_b200 import _ext
+    from makani_b200.distributed import p2p
+    from test_exchange_cpu import check_exchange
+    lib = _ext.load()
+    dev = torch.device("cuda:0")
+    state = {"rank": 0, "h": h}
+    pool = {}
+
+    class DevBuffers:
+        def __init__(self, key, nfloats):
+            self._use = 0
+            if (key, nfloats) not in pool:
+                bufs = []
+                for b in range(2):
+                    ptrs = []
+                    for r in range(h):
+                        p, hnd = C_.c_void_p(), C_.create_string_buffer(64)
+                        _ext.check(lib.sfno_ipc_alloc(nfloats * 4, C_.byref(p), hnd), "sfno_ipc_alloc")
+                        ptrs.append(p.value)
+                    bufs.append(ptrs)
+                pool[(key, nfloats)] = bufs
+            self.peer_ptrs = pool[(key, nfloats)]
+            self.local = [torch.as_tensor(p2p._DevPtr(self.peer_ptrs[b][state["rank"]], nfloats), device=dev)
+                          for b in range(2)]
+
+        def next(self):
+            b = self._use & 1
+            self._use += 1
+            return b
+
+    flags, hnd = C_.c_void_p(), C_.create_string_buffer(64)
+    _ext.check(lib.sfno_ipc_alloc(256, C_.byref(flags), hnd), "sfno_ipc_alloc")
+    epoch = [0]
+
+    def barrier():
+        epoch[0] += 1
+        arr = (C_.c_void_p * 1)(flags.value)
+        stream = C_.c_void_p(torch.cuda.current_stream().cuda_stream)
+        _ext.check(lib.sfno_peer_barrier(C_.cast(arr, C_.c_void_p), 0, 1, epoch[0], stream), "sfno_peer_barrier")
+
+    monkeypatch.setattr(p2p, "buffers", lambda key, n, group, device: DevBuffers(key, n))
+    monkeypatch.setattr(p2p, "fence", lambda group, device: barrier)
+    monkeypatch.setattr(thd, "polar_group", lambda: None)
+    try:
+        check_exchange(state, h, nlat, L, M, B, C, dev)
+        torch.cuda.synchronize()
+        assert epoch[0] > 0
+    finally:
+        torch.cuda.synchronize()
+        for bufs in pool.values():
+            for ptrs in bufs:
+                for p in ptrs:
+                    lib.sfno_ipc_free(C_.c_void_p(p))
+        lib.sfno_ipc_free(flags)

@@ -426,7 +426,7 @@ def run_ours(args):
         step_ms_prof = sum(r["total_ms"] for r in rows) / 3
         top = [dict(kernel=r["kernel"], shape={k: v for k, v in r["shape"].items()}, launches_per_step=r["launches"] // 3,
                     avg_us=round(r["avg_us"], 1), share=round(r["total_ms"] / 3 / step_ms_prof, 3),
-                    gbs=round(r["gbs"], 1), frac=round(r["gbs"] / peak, 3)) for r in rows[:12]]
+                    gbs=round(r["gbs"], 1), frac=round(r["gbs"] / peak, 3)) for r in rows[:16]]
         roofline = {"bound": "hbm", "kernel": dom["kernel"], "shape": dom["shape"], "achieved": dom["gbs"], "peak": peak,
                     "peak_source": peak_src, "unit": "GB/s", "frac": dom["gbs"] / peak, "traffic": ncu_traffic(dom["kernel"], dom["shape"]),
                     "alg_bytes": dom["alg_bytes"],

@@ -324,18 +324,13 @@ def run_ours(args):
     # data-parallel replicas: the only exchange is the weight-gradient all-reduce (DDP's job in the reference,
     # makani/mpu/mappings.py:104-172); issued per block as soon as its gradient exists so NCCL overlaps the
     # remaining backward work.
-    pending = []
-    if distributed:
-        def hook(p):
-            pending.append(dist.all_reduce(torch.view_as_real(p.grad), op=dist.ReduceOp.AVG, async_op=True))
-        for blk in blocks:
-            blk.weight.register_post_accumulate_grad_hook(hook)
+    from makani_b200.distributed.grad_sync import GradientAverager
+    sync = GradientAverager([blk.weight for blk in blocks]) if distributed else None
 
     def step(xs=None):
         out = gpu_step(blocks, xs_dev if xs is None else xs, grads)
-        for w in pending:
-            w.wait()
-        pending.clear()
+        if sync is not None:
+            sync.wait()
         return out
 
     def barrier():

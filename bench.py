@@ -2,8 +2,9 @@
 """bench.py - SFNO spectral hot path on B200 (contract: see the task statement / DESIGN.md section "Measurement").
 
 Workload (BASELINE.json configs[1], `sfno_linear_73chq_sc3_layers8_edim384_asgl2`, batch 1 per GPU, bf16 AMP):
-the eight SpectralConv blocks of the model, forward + backward (dX and dW), each on its own synthetic input
-of the shape/dtype it sees inside the model:
+the eight SpectralConv blocks of the model, forward + backward (dX and dW), chained as they are inside the model
+(the batch enters block 0 at 721x1440, each block's output is the next block's input, the gradient enters at block 7;
+`--inputs independent` gives every block its own synthetic input instead), with the shapes/dtypes of the model:
     block 0      RealSHT(721x1440 equiangular) -> dhconv(384->384, L=240, M=241) -> InverseRealSHT(240x480 Gauss)
                  + residual re-projection to 240x480
     blocks 1..6  240x480 Gauss in and out
@@ -56,21 +57,27 @@ def build_gpu(dev, dtype, seed=0):
     return blocks
 
 
-def make_inputs(batch, dtype, pinned):
+def make_inputs(batch, dtype, pinned, chained=False):
     g = torch.Generator().manual_seed(1)
     xs = []
-    for gin, _ in block_specs():
+    for gin, _ in block_specs()[:1 if chained else None]:
         x = torch.rand(batch, C_EMBED, gin[0], gin[1], generator=g, dtype=torch.float32).to(dtype)
         xs.append(x.pin_memory() if pinned else x)
     return xs
 
 
-def make_grads(batch, dtype, dev):
+def make_grads(batch, dtype, dev, chained=False):
+    """Per block: (gradient of y, gradient of the re-projected residual or None).  Chained blocks get their output
+    gradient from the next block, so only the last block's `gy` is materialised there."""
     g = torch.Generator().manual_seed(2)
     gs = []
-    for gin, gout in block_specs():
-        gy = (torch.rand(batch, C_EMBED, gout[0], gout[1], generator=g) - 0.5).to(dtype).to(dev)
+    specs = block_specs()
+    for i, (gin, gout) in enumerate(specs):
         rescale = (gin is not gout)
+        if chained and i < len(specs) - 1 and not rescale:
+            gs.append((None, None))
+            continue
+        gy = (torch.rand(batch, C_EMBED, gout[0], gout[1], generator=g) - 0.5).to(dtype).to(dev)
         gs.append((gy, gy.clone() if rescale else None))
     return gs
 
@@ -89,6 +96,28 @@ def gpu_step(blocks, xs_dev, grads):
             torch.autograd.backward([y], [gy])
         sums.append(y[0, 0, 0, :8].float().sum())
     return torch.stack(sums)
+
+
+def gpu_step_chained(blocks, x0, grads):
+    """One pass of the hot path as it runs inside the model (sfnonet.py:239-267 without the pointwise layers between
+    the filters): the batch enters block 0, every block's output is the next block's input, and ONE backward pass
+    carries the output gradient of block 7 (and the gradients of the two re-projected residuals) back to `x0`
+    and to every weight.  Same kernels and launch count as `gpu_step`.  Returns a tiny checksum tensor."""
+    x0.grad = None
+    outs, gouts = [], []
+    x = x0
+    for blk, (gy, gr) in zip(blocks, grads):
+        blk.weight.grad = None
+        blk._wp_cache = None          # a training step follows an optimizer update: the packed weight copy is rebuilt
+        y, res = blk(x)
+        if gr is not None:
+            outs.append(res)
+            gouts.append(gr)
+        x = y
+    outs.append(x)
+    gouts.append(grads[-1][0])
+    torch.autograd.backward(outs, gouts)
+    return torch.stack([x[0, 0, 0, :8].float().sum(), x0.grad[0, 0, 0, :8].float().sum()])
 
 
 class ClockSampler:
@@ -317,9 +346,6 @@ def run_ours(args):
     dtype = torch.bfloat16
     batch = 1
     blocks = build_gpu(dev, dtype)
-    grads = make_grads(batch, dtype, dev)
-    xs_host = make_inputs(batch, dtype, pinned=True)
-    xs_dev = [x.to(dev).requires_grad_(True) for x in xs_host]
 
     # data-parallel replicas: the only exchange is the weight-gradient all-reduce (DDP's job in the reference,
     # makani/mpu/mappings.py:104-172); issued per block as soon as its gradient exists so NCCL overlaps the
@@ -327,11 +353,42 @@ def run_ours(args):
     from makani_b200.distributed.grad_sync import GradientAverager
     sync = GradientAverager([blk.weight for blk in blocks]) if distributed else None
 
+    state = {}
+
+    def setup(chained):
+        state.clear()
+        state["chained"] = chained
+        state["grads"] = make_grads(batch, dtype, dev, chained=chained)
+        state["xs_host"] = make_inputs(batch, dtype, pinned=True, chained=chained)
+        state["xs_dev"] = [x.to(dev).requires_grad_(True) for x in state["xs_host"]]
+
     def step(xs=None):
-        out = gpu_step(blocks, xs_dev if xs is None else xs, grads)
+        xs = state["xs_dev"] if xs is None else xs
+        if state["chained"]:
+            out = gpu_step_chained(blocks, xs[0], state["grads"])
+        else:
+            out = gpu_step(blocks, xs, state["grads"])
         if sync is not None:
             sync.wait()
         return out
+
+    setup(args.inputs == "chained")
+    if state["chained"]:
+        # the chained step is one autograd graph over all eight blocks; should it fail on this box, measure the same
+        # kernels block by block (every block on its own input) rather than nothing, and say so in `config`.
+        try:
+            step()
+            torch.cuda.synchronize()
+        except Exception as e:                                      # noqa: BLE001
+            print(f"bench: chained step failed ({type(e).__name__}: {e}); using independent inputs", file=sys.stderr)
+            if sync is not None:
+                try:
+                    sync.wait()
+                except Exception:                                   # noqa: BLE001
+                    sync._pending.clear()
+            setup(False)
+    chained = state["chained"]
+    xs_host, xs_dev = state["xs_host"], state["xs_dev"]
 
     def barrier():
         if distributed:
@@ -443,7 +500,10 @@ def run_ours(args):
             "vs_baseline": None, "dtype": "tf32", "data": "synthetic",
             "config": {"workload": WORKLOAD, "per_gpu_batch": batch, "embed_dim": C_EMBED, "modes": [L_MODES, M_MODES],
                        "io_dtype": "bf16", "accumulate": "fp32", "parallelism": f"dp{world}",
-                       "l2": "inputs (1.4 GB/step) and intermediates are far larger than the 126 MB L2",
+                       "inputs": ("chained: block i+1 reads block i's output, one backward pass from block 7 to the input"
+                                  if chained else "independent: every block on its own synthetic input"),
+                       "l2": f"inputs ({h2d / 1e9:.1f} GB/step) and intermediates (XM / SP 178-536 MB per kernel) are far "
+                             "larger than the 126 MB L2",
                        "includes": "fwd + dX + dW of all 8 blocks, weight repack every step; no optimizer update",
                        "e2e": "pinned-host inputs copied every step on a copy stream, double buffered against compute"},
             "e2e": {"value": samples / (ms_e2e * 1e-3), "unit": "samples/s", "h2d_bytes_per_step": h2d,
@@ -464,6 +524,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--inputs", default="chained", choices=["chained", "independent"],
+                    help="chained: the batch flows through the eight blocks as in the model (default); "
+                         "independent: every block gets its own host input")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -1,0 +1,111 @@
+"""CPU tests of bench.py's host logic (no kernels): the chained step's autograd plumbing with stand-in blocks that
+have the SpectralConv call signature, the algorithmic-byte formulas of DESIGN.md, and the JSON contract of the
+`--impl reference` arm's line builder."""
+import importlib.util
+import os
+
+import torch
+import torch.nn as nn
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _bench():
+    spec = importlib.util.spec_from_file_location("bench_under_test", os.path.join(ROOT, "bench.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
+class _StandInBlock(nn.Module):
+    """(y, residual) = (resize(x) * w, resize(x) or x) - the call signature of SpectralConv.forward
+    (spectral_convolution.py:124-148), cheap enough for the CPU."""
+
+    def __init__(self, n_in, n_out):
+        super().__init__()
+        self.weight = nn.Parameter(torch.randn(3, dtype=torch.complex64))
+        self.n_in, self.n_out = n_in, n_out
+        self._wp_cache = "stale"
+
+    def _resize(self, x):
+        if self.n_in == self.n_out:
+            return x
+        return torch.nn.functional.interpolate(x, size=(self.n_out, 2 * self.n_out), mode="bilinear")
+
+    def forward(self, x):
+        assert x.shape[-2] == self.n_in
+        xr = self._resize(x)
+        y = xr * self.weight.abs().sum()
+        return y, (xr if self.n_in != self.n_out else x)
+
+
+def test_chained_step_matches_manual_composition():
+    b = _bench()
+    torch.manual_seed(0)
+    big, small = 12, 4
+    sizes = [(big, small)] + [(small, small)] * 6 + [(small, big)]
+    blocks = [_StandInBlock(i, o) for i, o in sizes]
+    x0 = torch.rand(1, 3, big, 2 * big, requires_grad=True)
+    grads = []
+    for k, (i, o) in enumerate(sizes):
+        if i != o:
+            g = torch.rand(1, 3, o, 2 * o) - 0.5
+            grads.append((g, g.clone()))
+        else:
+            grads.append((None, None))
+    chk = b.gpu_step_chained(blocks, x0, grads)
+    assert chk.shape == (2,) and torch.isfinite(chk).all()
+    assert all(blk._wp_cache is None for blk in blocks)
+    got_x = x0.grad.clone()
+    got_w = [blk.weight.grad.clone() for blk in blocks]
+
+    # manual composition: loss = <y7, gy7> + <res7, gr7> + <res0, gr0>
+    x0.grad = None
+    for blk in blocks:
+        blk.weight.grad = None
+    x = x0
+    loss = 0.0
+    for blk, (gy, gr) in zip(blocks, grads):
+        y, res = blk(x)
+        if gr is not None:
+            loss = loss + (res * gr).sum()
+        x = y
+    loss = loss + (x * grads[-1][0]).sum()
+    loss.backward()
+    torch.testing.assert_close(got_x, x0.grad)
+    for a, blk in zip(got_w, blocks):
+        torch.testing.assert_close(a, blk.weight.grad)
+
+    # a second step starts from clean gradients (no accumulation across steps)
+    b.gpu_step_chained(blocks, x0, grads)
+    torch.testing.assert_close(x0.grad, got_x)
+
+
+def test_make_grads_and_inputs_shapes():
+    b = _bench()
+    b.C_EMBED, b.GRID_IN, b.GRID_INT = 2, (9, 16, "equiangular"), (4, 8, "legendre-gauss")
+    cpu = torch.device("cpu")
+    ind = b.make_grads(1, torch.float32, cpu)
+    assert len(ind) == 8 and all(g is not None for g, _ in ind)
+    assert ind[0][1] is not None and ind[7][1] is not None and all(r is None for _, r in ind[1:7])
+    ch = b.make_grads(1, torch.float32, cpu, chained=True)
+    assert [g is not None for g, _ in ch] == [True] + [False] * 6 + [True]
+    assert ch[7][0].shape == (1, 2, 9, 16) and ch[0][1].shape == (1, 2, 4, 8)
+    assert len(b.make_inputs(1, torch.float32, False, chained=True)) == 1
+    xs = b.make_inputs(1, torch.float32, False)
+    assert [tuple(x.shape[-2:]) for x in xs] == [(9, 16)] + [(4, 8)] * 7
+
+
+def test_algorithmic_bytes_formulas():
+    """DESIGN.md section 4 / SURVEY 8(d): bytes per launch at the named config."""
+    b = _bench()
+    tri = sum(min(l + 1, 241) for l in range(240))
+    assert tri == 240 * 241 // 2
+    a = dict(B=1, C=384, K=240, W=480, M=241, esize=2)
+    assert b.alg_bytes("dft_fwd", a) == 384 * 240 * (480 * 2 + 241 * 8)
+    leg = b.alg_bytes("legendre_analysis", dict(B=1, C=384, K=240, L=240, M=241))
+    assert leg == 384 * 8 * (240 * 241 + tri) + 4 * 241 * 240 * 240
+    assert abs(leg / 1e6 - 322) < 1.0                                   # DESIGN: 322 MB
+    dh = b.alg_bytes("dhconv_fwd", dict(B=1, Cin=384, Cout=384, L=240, M=241))
+    assert abs(dh / 1e6 - 461) < 1.0                                    # DESIGN: 461 MB
+    assert b.alg_bytes("pack_weight", dict(Cin=384, Cout=384, L=240)) == 16 * 384 * 384 * 240

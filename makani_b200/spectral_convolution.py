@@ -167,10 +167,13 @@ class SpectralConv(nn.Module):
             raise NotImplementedError("separable SpectralConv is not supported (the reference einsum is ill-formed)")
 
         # initialisation of spectral_convolution.py:97-102
-        scale = math.sqrt(gain / in_channels) * torch.ones(self.modes_lat_local, dtype=torch.complex64)
+        # The reference multiplies a length-L scale vector into randn(*weight_shape): for dhconv that is per degree l
+        # (l = 0 times sqrt 2); for diagonal [Cin, Cout, L, M] it broadcasts over the LAST axis, i.e. per order m
+        # (m = 0 times sqrt 2: the coefficients that are real), and only constructs when L == M.  Same here; for
+        # L != M (where the reference raises) the per-m rule is kept with a length-M vector.
+        nscale = self.modes_lon_local if self.operator_type == "diagonal" else self.modes_lat_local
+        scale = math.sqrt(gain / in_channels) * torch.ones(nscale, dtype=torch.complex64)
         scale[0] *= math.sqrt(2.0)
-        if self.operator_type == "diagonal":
-            scale = scale.reshape(-1, 1)
         init = scale * torch.randn(*weight_shape, dtype=torch.complex64)
         self.weight = nn.Parameter(init)
 

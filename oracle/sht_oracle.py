@@ -251,10 +251,9 @@ def init_spectral_weight(in_channels, out_channels, modes_lat, modes_lon=None, o
         shape += [modes_lat]
     else:
         raise ValueError(f"Unsupported operator type f{operator_type}")
+    # the reference's length-L scale broadcasts over the last axis: l for dhconv, m for diagonal (needs L == M there)
     scale = math.sqrt(gain / in_channels) * torch.ones(modes_lat, dtype=torch.complex64)
     scale[0] *= math.sqrt(2.0)
-    if operator_type == "diagonal":
-        scale = scale.reshape(-1, 1)
     return scale * torch.randn(*shape, dtype=torch.complex64, generator=generator)
 
 

@@ -1,0 +1,72 @@
+"""Run in a fresh interpreter (tests/test_reference_dropin.py): the UNMODIFIED reference network
+(makani/models/networks/sfnonet.py) is constructed on top of the PRODUCT modules - torch_harmonics shim,
+makani_b200.SpectralConv in place of the reference's, makani_b200.comm as makani.utils.comm - exactly the
+"zero-diff" route of INTEGRATION.md section 1.  Construction only: the product has no CPU path, and a forward on a
+CPU tensor must say so loudly."""
+import os
+import sys
+import warnings
+
+warnings.filterwarnings("ignore")
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import refharness as H                                                     # noqa: E402
+import torch                                                               # noqa: E402
+
+th = H.install("product")
+import makani_b200                                                         # noqa: E402
+
+sc = H.load("makani.models.common.spectral_convolution")
+ref_spectral_conv = sc.SpectralConv
+sc.SpectralConv = makani_b200.SpectralConv
+common = H.load("makani.models.common")
+common.SpectralConv = makani_b200.SpectralConv
+net = H.load("makani.models.networks.sfnonet")
+assert net.__file__.startswith("/root/reference/")
+assert net.SpectralConv is makani_b200.SpectralConv and net.th.RealSHT is makani_b200.RealSHT
+
+# config/sfnonet.yaml:24-40,174-187 at reduced size (same structure: sc3, 2 x resolution change, dhconv, instance norm)
+kw = dict(inp_shape=(91, 180), out_shape=(91, 180), scale_factor=3, inp_chans=5, out_chans=4, embed_dim=16,
+          num_layers=4, operator_type="dhconv", use_mlp=True, mlp_ratio=2, normalization_layer="instance_norm",
+          big_skip=True, pos_embed="none", hard_thresholding_fraction=1.0, model_grid_type="equiangular",
+          sht_grid_type="legendre-gauss")
+torch.manual_seed(0)
+model = net.SphericalFourierNeuralOperatorNet(**kw)
+
+# the four transforms of sfnonet.py:536-539 are the product's, with the sizes _init_spectral_transforms derives
+assert type(model.trans_down) is makani_b200.RealSHT and type(model.itrans_up) is makani_b200.InverseRealSHT
+assert type(model.trans) is makani_b200.RealSHT and type(model.itrans) is makani_b200.InverseRealSHT
+assert (model.trans_down.nlat, model.trans_down.nlon, model.trans_down.grid) == (91, 180, "equiangular")
+assert (model.trans.nlat, model.trans.nlon, model.trans.grid) == (30, 60, "legendre-gauss")
+L, M = 30, 31
+for t in (model.trans_down, model.itrans_up, model.trans, model.itrans):
+    assert (t.lmax, t.mmax) == (L, M), (t.lmax, t.mmax)
+filters = [blk.filter.filter for blk in model.blocks]
+assert len(filters) == 4 and all(type(f) is makani_b200.SpectralConv for f in filters)
+assert filters[0].forward_transform is model.trans_down and filters[0].inverse_transform is model.itrans
+assert filters[-1].forward_transform is model.trans and filters[-1].inverse_transform is model.itrans_up
+assert [f.scale_residual for f in filters] == [True, False, False, True]
+for f in filters:
+    assert tuple(f.weight.shape) == (16, 16, L) and f.weight.dtype == torch.complex64
+    assert f.weight.is_shared_mp == ["matmul", "w"] and f.weight.sharded_dims_mp == [None, None, "h"]
+
+# checkpoint compatibility: identical parameter names / shapes / dtypes as the all-reference model (oracle-free: only
+# the names matter), Legendre tables are not in the state dict on either side (trainer.py:1036-1042)
+names = {k: (tuple(v.shape), v.dtype) for k, v in model.state_dict().items()}
+assert not any("weights" in k.split(".")[-1] or k.endswith(".pct") for k in names), sorted(names)[:5]
+sc.SpectralConv = ref_spectral_conv
+common.SpectralConv = ref_spectral_conv
+net.SpectralConv = ref_spectral_conv
+torch.manual_seed(0)
+model_ref = net.SphericalFourierNeuralOperatorNet(**kw)                     # reference SpectralConv on product SHT modules
+names_ref = {k: (tuple(v.shape), v.dtype) for k, v in model_ref.state_dict().items()}
+assert names == names_ref, set(names) ^ set(names_ref)
+model.load_state_dict(model_ref.state_dict(), strict=True)
+
+# no CPU path: a forward on CPU tensors fails loudly instead of computing something else
+try:
+    model(torch.rand(1, 5, 91, 180))
+except RuntimeError as e:
+    assert "no CPU path" in str(e), e
+else:
+    raise AssertionError("forward on a CPU tensor did not raise")
+print("OK reference SFNO built on product modules:", len(names), "state-dict entries")

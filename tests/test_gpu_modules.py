@@ -272,3 +272,44 @@ def test_composite_c_abi_calls(mk, dtype):
     rc = _ext.load().sfno_sht_fwd(pf.handle, C.c_void_p(x.data_ptr()), ops.dtype_code(x.dtype), B, Cin,
                                   C.c_void_p(out.data_ptr()), C.c_void_p(ws.data_ptr()), ws.numel(), None)
     assert rc != 0 and b"workspace" in _ext.load().sfno_last_error()
+
+
+@pytest.mark.parametrize("name", ["internal", "down", "up", "diag"])
+def test_spectral_conv_matches_reference_module_fixtures(mk, name):
+    """makani_b200.SpectralConv against outputs and gradients recorded from the reference's own, unmodified
+    SpectralConv (fp32, oracle SHT; tests/golden/spectral_conv_ref_*.npz, tools/make_golden.py).
+    Tolerance: TOL_BLOCK (three TF32 contractions) on y, residual, dX, dW; bias gradient 1e-5 (a plain sum)."""
+    from golden_cases import SPECTRAL_CONV_CASES, load
+    gin, gout, L, M, B, Ci, Co, op, bias = SPECTRAL_CONV_CASES[name]
+    z = load(name)
+    fwd = mk.RealSHT(gin[0], gin[1], lmax=L, mmax=M, grid=gin[2]).float().to(DEV)
+    inv = mk.InverseRealSHT(gout[0], gout[1], lmax=L, mmax=M, grid=gout[2]).float().to(DEV)
+    conv = mk.SpectralConv(fwd, inv, Ci, Co, operator_type=op, bias=bias).to(DEV)
+    assert tuple(conv.weight.shape) == z["weight"].shape and conv.scale_residual == bool(z["scale_residual"])
+    with torch.no_grad():
+        conv.weight.copy_(torch.from_numpy(z["weight"]))
+        if bias:
+            assert tuple(conv.bias.shape) == z["bias"].shape
+            conv.bias.copy_(torch.from_numpy(z["bias"]))
+    x = torch.from_numpy(z["x"]).to(DEV).requires_grad_(True)
+    y, res = conv(x)
+    assert y.dtype == torch.float32 and tuple(y.shape) == z["y"].shape
+    e = O.rel_l2(y.detach().cpu(), torch.from_numpy(z["y"]))
+    assert e < TOL_BLOCK, ("y", e)
+    loss = (y * torch.from_numpy(z["gy"]).to(DEV)).sum()
+    if conv.scale_residual:
+        e = O.rel_l2(res.detach().cpu(), torch.from_numpy(z["residual"]))
+        assert e < TOL_BLOCK, ("residual", e)
+        loss = loss + (res * torch.from_numpy(z["gr"]).to(DEV)).sum()
+    else:
+        assert res is x
+    loss.backward()
+    e = O.rel_l2(x.grad.cpu(), torch.from_numpy(z["dx"]))
+    assert e < TOL_BLOCK, ("dx", e)
+    dw = torch.from_numpy(z["dweight"])
+    e = float((conv.weight.grad.cpu() - dw).norm() / dw.norm())
+    assert e < TOL_BLOCK, ("dweight", e)
+    if bias:
+        db = torch.from_numpy(z["dbias"])
+        e = float((conv.bias.grad.cpu() - db).norm() / db.norm())
+        assert e < 1e-5, ("dbias", e)

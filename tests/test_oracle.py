@@ -124,3 +124,38 @@ def test_spectral_conv_oracle_matches_composition():
     w0 = O.init_spectral_weight(64, 64, 32, operator_type="dhconv")
     assert abs(float(w0[..., 1:].abs().pow(2).mean()) - 1 / 64) < 2e-3
     assert abs(float(w0[..., 0].abs().pow(2).mean()) - 2 / 64) < 6e-3
+
+
+@pytest.mark.parametrize("name", ["internal", "down", "up", "diag"])
+def test_spectral_conv_matches_reference_module(name):
+    """oracle.spectral_conv_forward against outputs AND gradients of the reference's own, unmodified SpectralConv
+    (spectral_convolution.py:43-148; fixtures made by tools/make_golden.py through tests/refharness.py).  Both sides
+    use the oracle's SHT arithmetic in fp32, so this pins the orchestration: fp32 forcing, residual re-projection,
+    contraction dispatch, bias, result dtype."""
+    from golden_cases import SPECTRAL_CONV_CASES, load
+    gin, gout, L, M, B, Ci, Co, op, bias = SPECTRAL_CONV_CASES[name]
+    z = load(name)
+    fwd = O.RealSHT(gin[0], gin[1], lmax=L, mmax=M, grid=gin[2], dtype=torch.float32)
+    inv = O.InverseRealSHT(gout[0], gout[1], lmax=L, mmax=M, grid=gout[2], dtype=torch.float32)
+    x = torch.from_numpy(z["x"]).requires_grad_(True)
+    w = torch.from_numpy(z["weight"]).requires_grad_(True)
+    b = torch.from_numpy(z["bias"]).requires_grad_(True) if bias else None
+    assert x.shape == (B, Ci, gin[0], gin[1]) and w.shape[:2] == (Ci, Co)
+    y, res = O.spectral_conv_forward(x, fwd, inv, w, op, bias=b, compute_dtype=torch.float32)
+    assert y.dtype == torch.float32 and tuple(y.shape) == z["y"].shape
+    assert O.rel_l2(y.detach(), torch.from_numpy(z["y"])) < 1e-6
+    scale_residual = bool(z["scale_residual"])
+    assert scale_residual == (gin != gout)
+    loss = (y * torch.from_numpy(z["gy"])).sum()
+    if scale_residual:
+        assert O.rel_l2(res.detach(), torch.from_numpy(z["residual"])) < 1e-6
+        loss = loss + (res * torch.from_numpy(z["gr"])).sum()
+    else:
+        assert res is x
+    loss.backward()
+    assert O.rel_l2(x.grad, torch.from_numpy(z["dx"])) < 1e-6
+    dw = torch.from_numpy(z["dweight"])
+    assert float((w.grad - dw).norm() / dw.norm()) < 1e-6
+    if bias:
+        db = torch.from_numpy(z["dbias"])
+        assert float((b.grad - db).norm() / db.norm()) < 1e-6

@@ -7,6 +7,11 @@
 2. quadrature.npz      - the reference's known-answer for quadrature weights (tests/test_metrics.py:37-45:
    integral of 1 over the sphere == 1 after the GridQuadrature normalisation of makani/utils/grids.py:63-97,
    restated here because grids.py imports torch_harmonics which is absent) and numpy's Gauss-Legendre rule.
+4. spectral_conv_ref_*.npz - outputs and gradients of the REFERENCE's own, unmodified ``SpectralConv``
+   (makani/models/common/spectral_convolution.py:43-148, loaded through tests/refharness.py) on seeded inputs, with the
+   CPU oracle standing in for torch-harmonics (fp32, as ``sfnonet.py:536-539`` builds the transforms with ``.float()``):
+   pins the module's orchestration - fp32 forcing, residual re-projection, contraction dispatch, bias, dtype of the
+   results - for oracle.spectral_conv_forward (CPU) and makani_b200.SpectralConv (GPU).
 3. sht_small.npz       - oracle outputs on small grids (NOT reference outputs: torch-harmonics is not available;
    recorded so a later change of the oracle or of the kernels is caught as a regression).
 """
@@ -28,6 +33,45 @@ def load_ref_contractions():
     mod = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(mod)
     return mod
+
+
+SPECTRAL_CONV_CASES = {
+    # name: (in grid, out grid, lmax, mmax, B, Cin, Cout, operator, bias)
+    "internal": ((16, 32, "legendre-gauss"), (16, 32, "legendre-gauss"), 16, 17, 2, 8, 8, "dhconv", False),
+    "down": ((33, 64, "equiangular"), (16, 32, "legendre-gauss"), 16, 17, 1, 8, 12, "dhconv", False),
+    "up": ((16, 32, "legendre-gauss"), (33, 64, "equiangular"), 16, 17, 2, 6, 8, "dhconv", "constant"),
+    # diagonal: the reference's init broadcasts its per-l scale over the LAST (m) axis, so it only constructs with L == M
+    "diag": ((12, 24, "legendre-gauss"), (12, 24, "legendre-gauss"), 11, 11, 2, 4, 6, "diagonal", "position"),
+}
+
+
+def make_spectral_conv_reference():
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import refharness as H
+    th = H.install("oracle")
+    sc = H.load("makani.models.common.spectral_convolution")
+    assert sc.__file__.startswith("/root/reference/")
+    for name, (gin, gout, L, M, B, Ci, Co, op, bias) in SPECTRAL_CONV_CASES.items():
+        torch.manual_seed(sum(map(ord, name)))
+        fwd = th.RealSHT(gin[0], gin[1], lmax=L, mmax=M, grid=gin[2]).float()
+        inv = th.InverseRealSHT(gout[0], gout[1], lmax=L, mmax=M, grid=gout[2]).float()
+        mod = sc.SpectralConv(fwd, inv, Ci, Co, operator_type=op, bias=bias)
+        if bias:
+            with torch.no_grad():
+                mod.bias.copy_(0.3 * torch.randn_like(mod.bias))
+        x = torch.randn(B, Ci, gin[0], gin[1], requires_grad=True)
+        y, res = mod(x)
+        gy = torch.randn_like(y)
+        gr = torch.randn_like(res)
+        loss = (y * gy).sum() + ((res * gr).sum() if mod.scale_residual else 0.0)
+        loss.backward()
+        out = dict(x=x.detach().numpy(), weight=mod.weight.detach().numpy(), y=y.detach().numpy(),
+                   residual=res.detach().numpy(), gy=gy.numpy(), gr=gr.numpy(), dx=x.grad.numpy(),
+                   dweight=mod.weight.grad.numpy(), scale_residual=np.array(mod.scale_residual))
+        if bias:
+            out["bias"] = mod.bias.detach().numpy()
+            out["dbias"] = mod.bias.grad.numpy()
+        np.savez_compressed(os.path.join(OUT, f"spectral_conv_ref_{name}.npz"), **out)
 
 
 def main():
@@ -62,6 +106,7 @@ def main():
         small[f"{tag}_c"] = c.numpy()
         small[f"{tag}_xr"] = isht(c).numpy()
     np.savez_compressed(os.path.join(OUT, "sht_small.npz"), **small)
+    make_spectral_conv_reference()
     print("wrote", sorted(os.listdir(OUT)))
 
 

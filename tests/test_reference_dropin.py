@@ -5,7 +5,9 @@ GPU box).  Each case runs in a fresh interpreter because the harness rewires ``s
   ``_init_spectral_transforms`` derives and a state dict interchangeable with the all-reference model;
 * the reference's own distributed test file (tests/distributed/tests_fft.py, unmodified) passes on the product's
   process-group registry and all-to-all transposes under gloo: 2-D and 3-D distributed FFTs, forward and backward,
-  uneven 361 = 181 + 180 splits, rel-L2 <= 1e-6 - for h x w = 2x1, 1x2 and 2x2."""
+  uneven 361 = 181 + 180 splits, rel-L2 <= 1e-6 - for h x w = 2x1, 1x2 and 2x2;
+* the reference's own DistributedInstanceNorm2d (mpu/layer_norm.py, unmodified) gives torch.nn.InstanceNorm2d's
+  output and gradients when it runs on the product's registry and parallel-region mappings (2x2 spatial split)."""
 import os
 import socket
 import subprocess
@@ -47,3 +49,15 @@ def test_reference_tests_fft_pass_on_product_transposes(h, w):
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-6000:]
     for rank in range(h * w):
         assert f"rank {rank}: ran 4 reference tests" in r.stdout and "FAILED" not in r.stdout
+
+
+def test_reference_distributed_instance_norm_on_product_mappings():
+    env = dict(os.environ, GRID_H="2", GRID_W="2", OMP_NUM_THREADS="2")
+    for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "MASTER_ADDR", "MASTER_PORT"):
+        env.pop(k, None)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=4",
+           "--master-addr", "127.0.0.1", "--master-port", str(_free_port()),
+           os.path.join(SCRIPTS, "run_reference_instance_norm.py")]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-6000:]
+    assert r.stdout.count(": OK") == 4 and "FAILED" not in r.stdout

@@ -196,6 +196,36 @@ int sfno_dft_inv_peer(void* const* xm_ch_host, const int* chan_shapes_host, int 
                       int lat_span, int B, int C, int nlat_loc, int nlon, int mmax, int m_valid,
                       const float* mscale_dev, void* y, int y_dtype, void* stream);
 
+/* ---- fused instance norm (+ GELU, + skip) around the spectral filter ----------
+ * Replaces  act_layer0(norm0(x))  and  norm1(x) + outer_skip(residual)  of FourierNeuralOperatorBlock.forward
+ * (makani/models/networks/sfnonet.py:239-267; nn.InstanceNorm2d(eps=1e-6, affine=True) of sfnonet.py:375-380, nn.GELU).
+ * x, skip, g, out, dx: [planes = B*C][hw] contiguous, dtype SFNO_F32 / SFNO_BF16 / SFNO_F16; arithmetic in fp32.
+ *   sfno_instnorm_stats     : per-plane statistics. partial_ws: planes * SFNO_INSTNORM_SEGMENTS * 2 floats of scratch;
+ *                             mean_var [planes][2] = (mean, biased variance) and/or stats [planes][2] = (mean,
+ *                             1/sqrt(var + eps)) - either may be NULL.  A spatially sharded instance merges the ranks'
+ *                             (mean, var, count) itself and hands the merged `stats` to the calls below.
+ *   sfno_instnorm_apply     : out = act( gamma[c] * (x - mean) * rstd + beta[c] (+ skip) ), c = plane % C.
+ *                             gamma / beta may be NULL (affine=False); skip is only accepted with SFNO_ACT_NONE.
+ *   sfno_instnorm_bwd_stats : partial [planes][SFNO_INSTNORM_SEGMENTS][2] = partial sums of (dz, dz * xhat) with
+ *                             dz = g * act'(z), xhat = (x - mean) * rstd.  The caller sums the segments (and, when the
+ *                             instance is sharded, all-reduces) into bsum [planes][2]; d gamma[c] = sum_b bsum[.,1],
+ *                             d beta[c] = sum_b bsum[.,0].
+ *   sfno_instnorm_bwd_apply : dx = gamma[c] * rstd * ( dz - (bsum0 + xhat * bsum1) / hw_total ); hw_total = elements of
+ *                             the whole instance (= hw unless sharded).  The gradient of `skip` is g itself.       */
+#define SFNO_INSTNORM_SEGMENTS 8
+#define SFNO_ACT_NONE 0
+#define SFNO_ACT_GELU 1
+int sfno_instnorm_stats(const void* x, int dtype, int planes, long long hw, float eps, float* partial_ws,
+                        float* mean_var, float* stats, void* stream);
+int sfno_instnorm_apply(const void* x, const void* skip, int dtype, int planes, int C, long long hw,
+                        const float* stats, const float* gamma, const float* beta, int act, void* out, void* stream);
+int sfno_instnorm_bwd_stats(const void* g, const void* x, int dtype, int planes, int C, long long hw,
+                            const float* stats, const float* gamma, const float* beta, int act, float* partial,
+                            void* stream);
+int sfno_instnorm_bwd_apply(const void* g, const void* x, int dtype, int planes, int C, long long hw,
+                            long long hw_total, const float* stats, const float* gamma, const float* beta,
+                            const float* bsum, int act, void* dx, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

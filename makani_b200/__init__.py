@@ -10,9 +10,11 @@ built library, raises.
 from . import quadrature, legendre                      # host-side fp64 precompute (numpy only)
 from .sht import RealSHT, InverseRealSHT
 from .spectral_convolution import SpectralConv, SpectralConvS2
+from .instance_norm import FusedInstanceNorm2d, DistributedFusedInstanceNorm2d
 from . import distributed
 from .compat import install_torch_harmonics_shim
 
-__all__ = ["RealSHT", "InverseRealSHT", "SpectralConv", "SpectralConvS2", "distributed", "quadrature", "legendre",
+__all__ = ["RealSHT", "InverseRealSHT", "SpectralConv", "SpectralConvS2", "FusedInstanceNorm2d",
+           "DistributedFusedInstanceNorm2d", "distributed", "quadrature", "legendre",
            "install_torch_harmonics_shim"]
 __version__ = "0.1.0"

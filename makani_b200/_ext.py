@@ -53,6 +53,10 @@ _PROTOTYPES = {
     "sfno_dft_peer_supported": (_i, [_i, _i]),
     "sfno_dft_fwd_peer": (_i, [_vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp]),
     "sfno_dft_inv_peer": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _vp, _i, _vp]),
+    "sfno_instnorm_stats": (_i, [_vp, _i, _i, _ll, C.c_float, _vp, _vp, _vp, _vp]),
+    "sfno_instnorm_apply": (_i, [_vp, _vp, _i, _i, _i, _ll, _vp, _vp, _vp, _i, _vp, _vp]),
+    "sfno_instnorm_bwd_stats": (_i, [_vp, _vp, _i, _i, _i, _ll, _vp, _vp, _vp, _i, _vp, _vp]),
+    "sfno_instnorm_bwd_apply": (_i, [_vp, _vp, _i, _i, _i, _ll, _ll, _vp, _vp, _vp, _vp, _i, _vp, _vp]),
 }
 
 
@@ -66,6 +70,8 @@ class CopyDesc(C.Structure):
 
 
 OP_SHT_FWD, OP_SHT_INV, OP_BLOCK_FWD = 0, 1, 2
+INSTNORM_SEGMENTS = 8
+ACT_NONE, ACT_GELU = 0, 1
 ABI_VERSION = 2
 
 EXPORTED_SYMBOLS = tuple(_PROTOTYPES)

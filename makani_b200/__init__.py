@@ -11,10 +11,11 @@ from . import quadrature, legendre                      # host-side fp64 precomp
 from .sht import RealSHT, InverseRealSHT
 from .spectral_convolution import SpectralConv, SpectralConvS2
 from .instance_norm import FusedInstanceNorm2d, DistributedFusedInstanceNorm2d
+from .block import fuse_block, fuse_model
 from . import distributed
 from .compat import install_torch_harmonics_shim
 
 __all__ = ["RealSHT", "InverseRealSHT", "SpectralConv", "SpectralConvS2", "FusedInstanceNorm2d",
-           "DistributedFusedInstanceNorm2d", "distributed", "quadrature", "legendre",
+           "DistributedFusedInstanceNorm2d", "fuse_block", "fuse_model", "distributed", "quadrature", "legendre",
            "install_torch_harmonics_shim"]
 __version__ = "0.1.0"

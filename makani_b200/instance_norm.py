@@ -156,6 +156,10 @@ def instance_norm_act(x, weight=None, bias=None, skip=None, eps: float = 1e-5, a
     """``act(instance_norm(x) * weight + bias) (+ skip)`` on a CUDA tensor [B, C, H, W] (fp32 / bf16 / fp16)."""
     if act not in _ACTS:
         raise ValueError(f"unknown activation {act!r}; supported: 'none', 'gelu'")
+    if skip is not None and skip.dtype != x.dtype:
+        # mixed dtypes (e.g. an fp32 field plus a bf16 autocast conv output): promote like ``x + skip`` would
+        dt = torch.promote_types(x.dtype, skip.dtype)
+        x, skip = x.to(dt), skip.to(dt)
     return _InstanceNormAct.apply(x, weight, bias, skip, float(eps), _ACTS[act], group)
 
 

@@ -62,6 +62,21 @@ names_ref = {k: (tuple(v.shape), v.dtype) for k, v in model_ref.state_dict().ite
 assert names == names_ref, set(names) ^ set(names_ref)
 model.load_state_dict(model_ref.state_dict(), strict=True)
 
+# block fusion on the reference's own FourierNeuralOperatorBlock instances: parameter names and
+# objects unchanged, norm0 + GELU and norm1 + outer skip rewired, idempotent
+before = {k: v.data_ptr() for k, v in model.state_dict().items()}
+makani_b200.fuse_model(model)
+makani_b200.fuse_model(model)
+after = {k: v.data_ptr() for k, v in model.state_dict().items()}
+assert before == after
+for blk in model.blocks:
+    assert type(blk).__name__ == "FourierNeuralOperatorBlock" and type(blk).__module__ == net.__name__
+    assert isinstance(blk.norm0, makani_b200.FusedInstanceNorm2d) and blk.norm0.act == "gelu"
+    assert isinstance(blk.act_layer0, torch.nn.Identity)
+    assert isinstance(blk.norm1, makani_b200.FusedInstanceNorm2d) and blk.norm1.act == "none"
+    assert blk._fused_outer_skip and not blk._fused_inner_skip and not hasattr(blk, "inner_skip")
+    assert blk.norm0.eps == 1e-6 and blk.norm0.affine
+
 # no CPU path: a forward on CPU tensors fails loudly instead of computing something else
 try:
     model(torch.rand(1, 5, 91, 180))

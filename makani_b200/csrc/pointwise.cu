@@ -59,12 +59,9 @@ __device__ __forceinline__ uint4 pw_pack(const float (&f)[PwVec<T>::n]) {
   return q;
 }
 
-// Two read flavours.  The statistics pass is followed by an apply pass over the same tensor: its loads use the default
-// policy so that the tail of the tensor (all of it at 240x480: 88 MB bf16 < 126 MB L2) is still cached, and the apply
-// pass walks the planes in REVERSE order to start with what was touched last.  The apply pass is the last use:
-// streaming (evict-first) loads.
-__device__ __forceinline__ uint4 pw_ldg(const void* p) { return __ldg(reinterpret_cast<const uint4*>(p)); }
-__device__ __forceinline__ uint4 pw_ldg_last(const void* p) { return __ldcs(reinterpret_cast<const uint4*>(p)); }
+__device__ __forceinline__ uint4 pw_ldg(const void* p) {            // streaming read: no reuse inside the kernel
+  return __ldcs(reinterpret_cast<const uint4*>(p));
+}
 
 // exact (erf) GELU, the default of nn.GELU
 __device__ __forceinline__ float gelu_f(float z) { return 0.5f * z * (1.f + erff(z * 0.70710678118654752f)); }
@@ -164,8 +161,8 @@ instnorm_apply_kernel(const T* __restrict__ x, const T* __restrict__ skip, const
                       const float* __restrict__ gamma, const float* __restrict__ beta, int C, long long n, int vec_ok,
                       T* __restrict__ out) {
   constexpr int V = PwVec<T>::n;
-  const long long plane = (long long)(gridDim.x - 1 - blockIdx.x) / kSeg;      // reverse order, see pw_ldg
-  const int seg = (gridDim.x - 1 - blockIdx.x) % kSeg;
+  const long long plane = blockIdx.x / kSeg;
+  const int seg = blockIdx.x % kSeg;
   const int c = (int)(plane % C);
   const float2 st = stats[plane];
   const float a = st.y * (gamma ? gamma[c] : 1.f);
@@ -177,11 +174,11 @@ instnorm_apply_kernel(const T* __restrict__ x, const T* __restrict__ skip, const
   long long lo, hi;
   if (vec_ok) {
     pw_range(n / V, seg, lo, hi);
-#pragma unroll 4
+#pragma unroll 2
     for (long long i = lo + threadIdx.x; i < hi; i += kPwThreads) {
       float f[V], k[V];
-      pw_unpack<T>(pw_ldg_last(px + i * V), f);
-      if (SKIP) pw_unpack<T>(pw_ldg_last(ps + i * V), k);
+      pw_unpack<T>(pw_ldg(px + i * V), f);
+      if (SKIP) pw_unpack<T>(pw_ldg(ps + i * V), k);
 #pragma unroll
       for (int j = 0; j < V; ++j) {
         float z = fmaf(a, f[j] - mean, b);
@@ -218,7 +215,7 @@ instnorm_bwd_stats_kernel(const T* __restrict__ g, const T* __restrict__ x, cons
   long long lo, hi;
   if (vec_ok) {
     pw_range(n / V, seg, lo, hi);
-#pragma unroll 4
+#pragma unroll 2
     for (long long i = lo + threadIdx.x; i < hi; i += kPwThreads) {
       float f[V], d[V];
       pw_unpack<T>(pw_ldg(px + i * V), f);
@@ -252,8 +249,8 @@ instnorm_bwd_apply_kernel(const T* __restrict__ g, const T* __restrict__ x, cons
                           const float2* __restrict__ bsum, float inv_n_total, int C, long long n, int vec_ok,
                           T* __restrict__ dx) {
   constexpr int V = PwVec<T>::n;
-  const long long plane = (long long)(gridDim.x - 1 - blockIdx.x) / kSeg;      // reverse order, see pw_ldg
-  const int seg = (gridDim.x - 1 - blockIdx.x) % kSeg;
+  const long long plane = blockIdx.x / kSeg;
+  const int seg = blockIdx.x % kSeg;
   const int c = (int)(plane % C);
   const float2 st = stats[plane];
   const float ga = gamma ? gamma[c] : 1.f, be = beta ? beta[c] : 0.f;
@@ -266,11 +263,11 @@ instnorm_bwd_apply_kernel(const T* __restrict__ g, const T* __restrict__ x, cons
   long long lo, hi;
   if (vec_ok) {
     pw_range(n / V, seg, lo, hi);
-#pragma unroll 4
+#pragma unroll 2
     for (long long i = lo + threadIdx.x; i < hi; i += kPwThreads) {
       float f[V], d[V];
-      pw_unpack<T>(pw_ldg_last(px + i * V), f);
-      pw_unpack<T>(pw_ldg_last(pg + i * V), d);
+      pw_unpack<T>(pw_ldg(px + i * V), f);
+      pw_unpack<T>(pw_ldg(pg + i * V), d);
 #pragma unroll
       for (int j = 0; j < V; ++j) {
         const float xh = (f[j] - st.x) * st.y;

@@ -2,7 +2,7 @@
 layout and forward (restated from makani/models/networks/sfnonet.py:155-267 - norm0 / act_layer0 / mlp / norm1 /
 drop_path / outer_skip around a SpectralConv filter; the reference class itself is not importable on the GPU box) gives
 the same output and gradients before and after fusion.  Both sides run the same SpectralConv kernels, so the tolerance
-is that of the fp32 pointwise arithmetic: 2e-5 forward, 2e-4 gradients (bf16: 3e-2)."""
+is that of the fp32 pointwise arithmetic: 2e-5 forward, 2e-4 gradients (bf16 autocast: 3e-2 / 5e-2)."""
 import copy
 
 import pytest
@@ -105,15 +105,19 @@ def test_fused_block_matches_unfused(mk, grid_in, grid_out, inner, outer, dtype)
         outs.append((y.detach().float(), x.grad.float(), {k: p.grad.float() if not p.grad.is_complex() else p.grad
                                                          for k, p in m.named_parameters()}))
     (y_r, gx_r, gp_r), (y_f, gx_f, gp_f) = outs
-    tol_y, tol_g = (2e-5, 2e-4) if dtype == torch.float32 else (3e-2, 3e-2)
+    tol_y, tol_g = (2e-5, 2e-4) if dtype == torch.float32 else (3e-2, 5e-2)
     assert _rel(y_f, y_r) < tol_y
     assert _rel(gx_f, gx_r) < tol_g
     assert set(gp_r) == set(gp_f)
+    # some gradients are identically zero in exact arithmetic (a bias in front of an instance norm: mlp.2.bias), so both
+    # sides hold rounding noise there: measure every error against the parameter's own gradient norm, floored at 1e-3
+    # of the largest parameter-gradient norm
+    real = lambda t: torch.view_as_real(t) if t.is_complex() else t          # noqa: E731
+    gmax = max(float(real(b).double().norm()) for b in gp_r.values())
     for k in gp_r:
-        a, b = gp_f[k], gp_r[k]
-        if a.is_complex():
-            a, b = torch.view_as_real(a), torch.view_as_real(b)
-        assert _rel(a, b) < tol_g, k
+        a, b = real(gp_f[k]).double(), real(gp_r[k]).double()
+        err = float((a - b).norm()) / max(float(b.norm()), 1e-3 * gmax)
+        assert err < tol_g, (k, err)
 
 
 def test_fuse_block_leaves_other_norms_alone(mk):

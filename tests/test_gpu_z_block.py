@@ -109,21 +109,23 @@ def test_fused_block_matches_unfused(mk, grid_in, grid_out, inner, outer, dtype)
     assert _rel(y_f, y_r) < tol_y
     assert _rel(gx_f, gx_r) < tol_g
     assert set(gp_r) == set(gp_f)
-    # some gradients are identically zero in exact arithmetic (a bias in front of an instance norm: mlp.2.bias), so both
-    # sides hold rounding noise there: measure every error against the parameter's own gradient norm, floored at 1e-3
-    # of the largest parameter-gradient norm
+    # mlp.2.bias sits in front of an instance norm: its gradient is identically zero in exact arithmetic and both sides
+    # hold summation noise there - require "tiny" instead of "equal"
     real = lambda t: torch.view_as_real(t) if t.is_complex() else t          # noqa: E731
     gmax = max(float(real(b).double().norm()) for b in gp_r.values())
     for k in gp_r:
         a, b = real(gp_f[k]).double(), real(gp_r[k]).double()
-        err = float((a - b).norm()) / max(float(b.norm()), 1e-3 * gmax)
+        if k == "mlp.2.bias":
+            assert float(a.norm()) < 1e-2 * gmax and float(b.norm()) < 1e-2 * gmax, k
+            continue
+        err = float((a - b).norm()) / float(b.norm())
         assert err < tol_g, (k, err)
 
 
 def test_fuse_block_leaves_other_norms_alone(mk):
     blk = _Block(mk, 8, LG, LG, False, True).to(DEV)
     blk.norm0 = nn.Identity()
-    blk.norm1 = nn.InstanceNorm2d(8, track_running_stats=True)
+    blk.norm1 = nn.InstanceNorm2d(8, track_running_stats=True).to(DEV)
     mk.fuse_block(blk)
     assert isinstance(blk.norm0, nn.Identity) and isinstance(blk.norm1, nn.InstanceNorm2d)
     assert isinstance(blk.act_layer0, nn.GELU) and not blk._fused_outer_skip

@@ -25,6 +25,7 @@
 #include <cuda_fp16.h>
 
 #include "../../include/makani_b200.h"
+#include "pointwise_math.cuh"
 
 namespace sfno {
 
@@ -63,11 +64,9 @@ __device__ __forceinline__ uint4 pw_ldg(const void* p) {            // streaming
   return __ldcs(reinterpret_cast<const uint4*>(p));
 }
 
-// exact (erf) GELU, the default of nn.GELU
-__device__ __forceinline__ float gelu_f(float z) { return 0.5f * z * (1.f + erff(z * 0.70710678118654752f)); }
-__device__ __forceinline__ float gelu_grad_f(float z) {
-  return 0.5f * (1.f + erff(z * 0.70710678118654752f)) + z * 0.3989422804014327f * __expf(-0.5f * z * z);
-}
+// exact (erf) GELU, the default of nn.GELU: arithmetic in pointwise_math.cuh (shared with the host accuracy test)
+__device__ __forceinline__ float gelu_f(float z) { return pw_gelu(z); }
+__device__ __forceinline__ float gelu_grad_f(float z) { return pw_gelu_grad(z); }
 
 // Segment `seg` of a plane of n elements, in units of `unit` elements: [lo, hi)
 __device__ __forceinline__ void pw_range(long long n_units, int seg, long long& lo, long long& hi) {

@@ -39,3 +39,17 @@ def test_module_surface_and_state_dict():
         mk.FusedInstanceNorm2d(8, track_running_stats=True)
     with pytest.raises(RuntimeError, match="no CPU path"):
         mod(torch.randn(1, 8, 4, 4))
+
+
+def test_fast_erf_host_accuracy(tmp_path):
+    """pointwise_math.cuh compiled for the host: the A&S 7.1.26 erf (the -DSFNO_FAST_ERF=1 variant of the GELU kernels)
+    and the default path against double-precision erf on a dense grid (bounds in tests/cpp/gelu_host_test.cpp)."""
+    import os
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    src = os.path.join(root, "tests", "cpp", "gelu_host_test.cpp")
+    for flag in ("-DSFNO_FAST_ERF=1", "-DSFNO_FAST_ERF=0"):
+        exe = str(tmp_path / ("gelu" + flag[-1]))
+        subprocess.run(["g++", "-O2", "-std=c++17", flag, src, "-o", exe], check=True)
+        r = subprocess.run([exe], capture_output=True, text=True)
+        assert r.returncode == 0, r.stdout

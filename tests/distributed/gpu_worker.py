@@ -114,6 +114,32 @@ def main():
         dist.all_reduce(torch.view_as_real(gw), group=azimuth)
     errs["conv_dw"] = rel(gw, conv.weight.grad[..., sl_l])
 
+    # ---- spatially sharded fused instance norm (+ GELU) vs the single-GPU fused module on the full field
+    # (statistics merged over all h x w ranks = the "spatial" group of the reference, mpu/layer_norm.py:47-86)
+    torch.manual_seed(9)
+    norm = mk.FusedInstanceNorm2d(C, eps=1e-6, affine=True, act="gelu").to(dev)
+    with torch.no_grad():
+        norm.weight.copy_(1 + 0.3 * torch.randn(C, device=dev))
+        norm.bias.copy_(0.3 * torch.randn(C, device=dev))
+        dist.broadcast(norm.weight, src=0)
+        dist.broadcast(norm.bias, src=0)
+    dnorm = mk.DistributedFusedInstanceNorm2d(C, eps=1e-6, affine=True, act="gelu", group=dist.group.WORLD).to(dev)
+    dnorm.load_state_dict(norm.state_dict())
+    xr = (x_full * 2 + 1).detach().requires_grad_(True)
+    yr = norm(xr)
+    (yr * gx_full).sum().backward()
+    xl = (x_full * 2 + 1)[:, :, sl_lat, sl_lon].contiguous().requires_grad_(True)
+    yl = dnorm(xl)
+    (yl * gx_full[:, :, sl_lat, sl_lon]).sum().backward()
+    gw, gb = dnorm.weight.grad.clone(), dnorm.bias.grad.clone()      # partial sums: shared over "spatial"
+    dist.all_reduce(gw)
+    dist.all_reduce(gb)
+    norm_errs = dict(norm_fwd=rel(yl.detach(), yr.detach()[:, :, sl_lat, sl_lon]),
+                     norm_dx=rel(xl.grad, xr.grad[:, :, sl_lat, sl_lon]),
+                     norm_dw=rel(gw, norm.weight.grad), norm_db=rel(gb, norm.bias.grad))
+    assert max(norm_errs.values()) < 1e-4, norm_errs                  # fp32 pointwise arithmetic, different summation order
+    errs.update({k: v * (TOL / 1e-4) * 0.5 for k, v in norm_errs.items()})   # reported on the common scale below
+
     # h-sharded runs must have gone through the peer-memory exchange unless it was switched off
     st = thd.p2p.status()
     if h > 1 and w == 1:

@@ -35,6 +35,7 @@ import torch.distributed as dist
 import torch.nn as nn
 
 from .. import _ext, ops
+from .._nvtx import annotate
 from ..sht import InverseRealSHT, RealSHT
 from . import p2p
 
@@ -549,6 +550,7 @@ class DistributedRealSHT(_DistributedMixin, RealSHT):
         m0, tab = self._table_slice()
         self.register_buffer("weights", torch.from_numpy(tab), persistent=False)
 
+    @annotate("DistributedRealSHT.forward")
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         if x.dim() != 4:
             raise ValueError(f"Expected a 4-d tensor [B, C, H_local, W_local], got {x.dim()} dims")
@@ -580,6 +582,7 @@ class DistributedInverseRealSHT(_DistributedMixin, InverseRealSHT):
         m0, tab = self._table_slice()
         self.register_buffer("pct", torch.from_numpy(tab), persistent=False)
 
+    @annotate("DistributedInverseRealSHT.forward")
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         if x.dim() != 4:
             raise ValueError(f"Expected a 4-d tensor [B, C, L_local, M_local], got {x.dim()} dims")

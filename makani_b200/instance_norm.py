@@ -28,6 +28,7 @@ import torch
 import torch.distributed as dist
 import torch.nn as nn
 
+from ._nvtx import annotate
 from . import _ext
 from .ops import _need_cuda, _ptr, _stream, dtype_code
 
@@ -185,6 +186,7 @@ class FusedInstanceNorm2d(nn.Module):
     def _group(self):
         return None
 
+    @annotate("FusedInstanceNorm2d.forward")
     def forward(self, x, skip=None):
         if x.shape[1] != self.num_features:
             raise ValueError(f"expected {self.num_features} channels, got {x.shape[1]}")

@@ -18,6 +18,7 @@ import numpy as np
 import torch
 import torch.nn as nn
 
+from ._nvtx import annotate
 from . import ops
 from .legendre import legpoly
 from .quadrature import clenshaw_curtiss_weights, legendre_gauss_weights, lobatto_weights
@@ -153,6 +154,7 @@ class RealSHT(_TransformBase):
         pct = legpoly(self.mmax, self.lmax, tq, norm=self.norm, csphase=self.csphase)
         return np.einsum("mlk,k->mlk", pct, self._quad_w)
 
+    @annotate("RealSHT.forward")
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         ops._need_cuda(x, "RealSHT input")
         x4, lead = _flatten_spatial(x, self.nlat, self.nlon)
@@ -172,6 +174,7 @@ class InverseRealSHT(_TransformBase):
         t = np.flip(np.arccos(self._cost))
         return legpoly(self.mmax, self.lmax, t, norm=self.norm, inverse=True, csphase=self.csphase)
 
+    @annotate("InverseRealSHT.forward")
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         if x.shape[-2] != self.lmax or x.shape[-1] != self.mmax:
             raise AssertionError(f"expected [..., {self.lmax}, {self.mmax}], got {tuple(x.shape)}")

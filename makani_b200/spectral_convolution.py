@@ -16,6 +16,7 @@ import math
 import torch
 import torch.nn as nn
 
+from ._nvtx import annotate
 from . import ops
 from .sht import InverseRealSHT, RealSHT, _TransformBase
 
@@ -211,6 +212,7 @@ class SpectralConv(nn.Module):
                 and type(self.forward_transform) is RealSHT and type(self.inverse_transform) is InverseRealSHT
                 and self.forward_transform.lmax == self.modes_lat and self.forward_transform.mmax == self.modes_lon)
 
+    @annotate("SpectralConv.forward")
     def forward(self, x):
         dtype = x.dtype
         ops._need_cuda(x, "SpectralConv input")

@@ -61,3 +61,26 @@ def test_reference_distributed_instance_norm_on_product_mappings():
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-6000:]
     assert r.stdout.count(": OK") == 4 and "FAILED" not in r.stdout
+
+
+def test_reference_separable_contractions_are_ill_formed():
+    """`separable=True` is not built because the reference's own separable einsums
+    ("bixy,ix->boxy" / "bixy,ixy->boxy", contractions.py:139-154) name an output index no operand carries and raise
+    inside torch.einsum - there is no behaviour to reproduce.  Checked against the reference file itself; the product
+    refuses the option explicitly."""
+    import importlib.util
+    import torch
+    spec = importlib.util.spec_from_file_location(
+        "ref_contractions_sep", os.path.join(H.REF_ROOT, "makani", "models", "common", "contractions.py"))
+    ref = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(ref)
+    x = torch.randn(2, 4, 5, 6, dtype=torch.complex64)
+    with pytest.raises(RuntimeError):
+        ref._contract_sep_dhconv(x, torch.randn(4, 5, dtype=torch.complex64))
+    with pytest.raises(RuntimeError):
+        ref._contract_sep_diagonal(x, torch.randn(4, 5, 6, dtype=torch.complex64))
+    import makani_b200 as mk
+    fwd = mk.RealSHT(8, 16, grid="legendre-gauss")
+    inv = mk.InverseRealSHT(8, 16, grid="legendre-gauss")
+    with pytest.raises(NotImplementedError):
+        mk.SpectralConv(fwd, inv, 4, 4, operator_type="dhconv", separable=True)

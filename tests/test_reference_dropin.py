@@ -63,6 +63,21 @@ def test_reference_distributed_instance_norm_on_product_mappings():
     assert r.stdout.count(": OK") == 4 and "FAILED" not in r.stdout
 
 
+@pytest.mark.parametrize("h,w", [(2, 1), (2, 2)])
+def test_reference_spectral_conv_on_product_distributed_transforms(h, w):
+    """The reference's own SpectralConv built on DistributedRealSHT / DistributedInverseRealSHT (CPU-staged subclasses)
+    and makani_b200.comm: shard bookkeeping, forward, dX, dW against the single-process oracle block."""
+    env = dict(os.environ, GRID_H=str(h), GRID_W=str(w), OMP_NUM_THREADS="2")
+    for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "MASTER_ADDR", "MASTER_PORT"):
+        env.pop(k, None)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={h * w}",
+           "--master-addr", "127.0.0.1", "--master-port", str(_free_port()),
+           os.path.join(SCRIPTS, "run_reference_spectral_conv_dist.py")]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-6000:]
+    assert r.stdout.count(": OK") == h * w and "FAILED" not in r.stdout
+
+
 def test_reference_separable_contractions_are_ill_formed():
     """`separable=True` is not built because the reference's own separable einsums
     ("bixy,ix->boxy" / "bixy,ixy->boxy", contractions.py:139-154) name an output index no operand carries and raise

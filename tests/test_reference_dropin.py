@@ -35,6 +35,22 @@ def test_reference_sfno_builds_on_product_modules():
     assert "OK reference SFNO built on product modules" in r.stdout
 
 
+@pytest.mark.parametrize("h,w", [(4, 1), (2, 2)])
+def test_reference_sfno_builds_spatially_parallel_on_product_modules(h, w):
+    """BASELINE.json config 4 geometry (721 x 1440, h_parallel_size = 4 -> 181,181,181,178) through the reference's own
+    `_init_spectral_transforms`: thd.init with groups of makani_b200.comm, DistributedRealSHT / InverseRealSHT, local
+    shapes, sharded dhconv weights, DistributedInstanceNorm2d, block fusion."""
+    env = dict(os.environ, GRID_H=str(h), GRID_W=str(w), OMP_NUM_THREADS="2")
+    for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "MASTER_ADDR", "MASTER_PORT"):
+        env.pop(k, None)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={h * w}",
+           "--master-addr", "127.0.0.1", "--master-port", str(_free_port()),
+           os.path.join(SCRIPTS, "build_reference_sfno_dist.py")]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-6000:]
+    assert r.stdout.count("built on product modules: OK") == h * w
+
+
 @pytest.mark.parametrize("h,w", [(2, 1), (1, 2), (2, 2)])
 def test_reference_tests_fft_pass_on_product_transposes(h, w):
     env = dict(os.environ, GRID_H=str(h), GRID_W=str(w), OMP_NUM_THREADS="2")

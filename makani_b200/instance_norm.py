@@ -188,7 +188,7 @@ class FusedInstanceNorm2d(nn.Module):
 
     @annotate("FusedInstanceNorm2d.forward")
     def forward(self, x, skip=None):
-        if x.shape[1] != self.num_features:
+        if self.num_features and x.shape[1] != self.num_features:      # 0 / None: unknown (non-affine norm adopted by fuse_block)
             raise ValueError(f"expected {self.num_features} channels, got {x.shape[1]}")
         return instance_norm_act(x, self.weight, self.bias, skip, self.eps, self.act, self._group())
 

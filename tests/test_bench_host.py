@@ -109,3 +109,60 @@ def test_algorithmic_bytes_formulas():
     dh = b.alg_bytes("dhconv_fwd", dict(B=1, Cin=384, Cout=384, L=240, M=241))
     assert abs(dh / 1e6 - 461) < 1.0                                    # DESIGN: 461 MB
     assert b.alg_bytes("pack_weight", dict(Cin=384, Cout=384, L=240)) == 16 * 384 * 384 * 240
+
+
+def _chained_dp_worker(rank, world, port):
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from makani_b200.distributed.grad_sync import GradientAverager
+        b = _bench()
+        torch.manual_seed(0)                                   # same weights on every replica
+        big, small = 12, 4
+        sizes = [(big, small)] + [(small, small)] * 6 + [(small, big)]
+        blocks = [_StandInBlock(i, o) for i, o in sizes]
+        ref = [torch.nn.Parameter(blk.weight.detach().clone()) for blk in blocks]
+        sync = GradientAverager([blk.weight for blk in blocks])
+        gen = torch.Generator().manual_seed(10 + rank)         # different data per replica
+        grads = []
+        for i, o in sizes:
+            if i != o:
+                g = torch.rand(1, 3, o, 2 * o, generator=gen) - 0.5
+                grads.append((g, g.clone()))
+            else:
+                grads.append((None, None))
+        for _ in range(2):                                      # two steps: hooks stay armed
+            x0 = torch.rand(1, 3, big, 2 * big, generator=gen).requires_grad_(True)
+            b.gpu_step_chained(blocks, x0, grads)               # the all-reduces start from the hooks during backward
+            sync.wait()
+            # the replica's own gradient, without hooks, then averaged by hand
+            for blk, r in zip(blocks, ref):
+                blk.weight, keep = r, blk.weight
+                blk._keep = keep
+            for r in ref:
+                r.grad = None
+            b.gpu_step_chained(blocks, x0.detach().clone().requires_grad_(True), grads)
+            for blk in blocks:
+                blk.weight = blk._keep
+            for blk, r in zip(blocks, ref):
+                mine = torch.view_as_real(r.grad).contiguous()
+                parts = [torch.zeros_like(mine) for _ in range(world)]
+                dist.all_gather(parts, mine)
+                want = torch.stack(parts).mean(0)
+                got = torch.view_as_real(blk.weight.grad)
+                assert torch.allclose(got, want, rtol=1e-5, atol=1e-6), float((got - want).abs().max())
+            assert not sync._pending
+    finally:
+        dist.destroy_process_group()
+
+
+def test_chained_step_with_gradient_averaging_gloo():
+    """bench.py at N > 1: the chained step's single backward pass fires the eight weight-gradient all-reduces from
+    post-accumulate hooks (GradientAverager); world size 2, gloo, stand-in blocks."""
+    import socket
+    import torch.multiprocessing as mp
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    mp.spawn(_chained_dp_worker, args=(2, port), nprocs=2, join=True)

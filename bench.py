@@ -106,9 +106,14 @@ def gpu_step_chained(blocks, x0, grads):
     x0.grad = None
     outs, gouts = [], []
     x = x0
+    prepack = os.environ.get("MAKANI_B200_OVERLAP_WEIGHTS", "0") == "1"
+    if prepack:                        # opt-in A/B: all eight re-packs start on the side stream right away
+        for blk in blocks:
+            blk.prepack_async()
     for blk, (gy, gr) in zip(blocks, grads):
         blk.weight.grad = None
-        blk._wp_cache = None          # a training step follows an optimizer update: the packed weight copy is rebuilt
+        if not prepack:
+            blk._wp_cache = None      # a training step follows an optimizer update: the packed weight copy is rebuilt
         y, res = blk(x)
         if gr is not None:
             outs.append(res)

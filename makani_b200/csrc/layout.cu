@@ -10,7 +10,21 @@
 #include <algorithm>
 #include <type_traits>
 
+#include "wpack.cuh"
+#include <cstdlib>
+
 namespace sfno {
+
+// SFNO_WPACK_TL=32 selects the 16 KB-tile pack / unpack kernels of wpack.cuh (default: the 64 x 64 kernels below)
+static int wpack_tile() {
+  static int v = -1;
+  if (v < 0) {
+    const char* env = getenv("SFNO_WPACK_TL");
+    v = (env && atoi(env) == 32) ? 32 : 64;
+  }
+  return v;
+}
+
 
 // ------------------------------------------------------------------ SP <-> complex64 [B][C][L][M]
 // grid (ceil(M/32), ceil(C/32), L*B), block (32, 8)
@@ -428,12 +442,24 @@ int sfno_c64_to_xm(const void* in_c64, int B, int C, int nlat, int mmax, float* 
 }
 int sfno_dhconv_pack_weight(const void* w_c64, int Cin, int Cout, int L, float* wp, void* stream) {
   const int Cinp = (Cin + 3) & ~3;
+  if (wpack_tile() == 32) {                        // 16 KB tile: can share an SM with a persistent GEMM CTA (wpack.cuh)
+    dim3 grid((L + 31) / 32, (Cinp + wpack::kTI - 1) / wpack::kTI, Cout);
+    wpack::pack_weight_tl_kernel<32><<<grid, 256, 0, (cudaStream_t)stream>>>((const float2*)w_c64, wp, Cin, Cout, L);
+    SFNO_LAUNCHED();
+    return 0;
+  }
   dim3 grid((L + kWT - 1) / kWT, (Cinp + kWT - 1) / kWT, Cout);
   pack_weight_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const float2*)w_c64, wp, Cin, Cout, L);
   SFNO_LAUNCHED();
   return 0;
 }
 int sfno_dhconv_unpack_wgrad(const float* gwp, int Cin, int Cout, int L, void* gw_c64, void* stream) {
+  if (wpack_tile() == 32) {
+    dim3 grid32((L + 31) / 32, (Cin + wpack::kTI - 1) / wpack::kTI, Cout);
+    wpack::unpack_wgrad_tl_kernel<32><<<grid32, 256, 0, (cudaStream_t)stream>>>(gwp, (float2*)gw_c64, Cin, Cout, L);
+    SFNO_LAUNCHED();
+    return 0;
+  }
   dim3 grid((L + kWT - 1) / kWT, (Cin + kWT - 1) / kWT, Cout);
   unpack_wgrad_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(gwp, (float2*)gw_c64, Cin, Cout, L);
   SFNO_LAUNCHED();

@@ -12,6 +12,7 @@ stages, and its backward is a single hand-written adjoint chain (one autograd no
 from __future__ import annotations
 
 import math
+import os
 
 import torch
 import torch.nn as nn
@@ -21,6 +22,22 @@ from . import ops
 from .sht import InverseRealSHT, RealSHT, _TransformBase
 
 __all__ = ["SpectralConv", "SpectralConvS2"]
+
+
+# Opt-in (MAKANI_B200_OVERLAP_WEIGHTS=1, default off until measured - DESIGN.md 7.1 item 4): run the two pure
+# streaming kernels of the weight path on a side stream, next to the latency-bound persistent kernels of the main
+# stream - the gradient unpack while the rest of the block's backward runs, the weight re-pack (prepack_async) while
+# earlier layers run.  Pair it with SFNO_WPACK_TL=32 so that their CTAs fit beside a GEMM CTA (csrc/wpack.cuh).
+_OVERLAP_WEIGHTS = os.environ.get("MAKANI_B200_OVERLAP_WEIGHTS", "0") == "1"
+_SIDE_STREAMS = {}
+
+
+def _side_stream(device) -> "torch.cuda.Stream":
+    key = torch.device(device).index
+    st = _SIDE_STREAMS.get(key)
+    if st is None:
+        st = _SIDE_STREAMS[key] = torch.cuda.Stream(device=device)
+    return st
 
 
 def _distributed_classes():
@@ -78,6 +95,7 @@ class _SpectralConvFunction(torch.autograd.Function):
         dev = gy.device
         pf, pi = fwd._plan(dev), inv._plan(dev)
         adj = inv._scale(dev, "irfft_adj")
+        unpack_done = None
 
         gxm2 = ops.dft_fwd(gy.contiguous(), M, adj)
         gsp2 = ops.legendre_analysis(pi, gxm2, B, Cout, round_tf32=True)
@@ -85,7 +103,19 @@ class _SpectralConvFunction(torch.autograd.Function):
         gw = None
         if mod.operator_type == "dhconv":
             if ctx.needs_input_grad[1]:
-                gw = ops.unpack_wgrad(ops.dhconv_bwd_w(sp, gsp2, B, Cin, Cout, L, M), Cin, Cout, L)
+                gwp = ops.dhconv_bwd_w(sp, gsp2, B, Cin, Cout, L, M)
+                if _OVERLAP_WEIGHTS:
+                    main, side = torch.cuda.current_stream(), _side_stream(dev)
+                    side.wait_stream(main)                       # gwp is complete on the main stream
+                    with torch.cuda.stream(side):
+                        gw = ops.unpack_wgrad(gwp, Cin, Cout, L)
+                        unpack_done = torch.cuda.Event()
+                        unpack_done.record(side)
+                    gwp.record_stream(side)                      # allocated on main, read on side
+                    gw.record_stream(main)                       # allocated on side, consumed on main
+                    del gwp
+                else:
+                    gw = ops.unpack_wgrad(gwp, Cin, Cout, L)
             gsp = ops.dhconv_bwd_x(gsp2, wsaved, B, Cin, Cout, L, M, round_tf32=True) if ctx.needs_input_grad[0] else None
         else:
             if ctx.needs_input_grad[1]:
@@ -100,6 +130,8 @@ class _SpectralConvFunction(torch.autograd.Function):
                 del grxm
             gxm = ops.legendre_synthesis(pf, gsp, B, Cin)
             gx = ops.dft_inv(gxm, B, Cin, fwd.nlat, fwd.nlon, M, fwd._scale(dev, "rfft_adj"), ctx.in_dtype)
+        if unpack_done is not None:
+            torch.cuda.current_stream().wait_event(unpack_done)   # join: whatever consumes gw runs after the unpack
         return gx, gw, None
 
 
@@ -202,10 +234,32 @@ class SpectralConv(nn.Module):
         key = (weight._version, weight.data_ptr(), weight.device)
         cache = self._wp_cache
         if cache is not None and cache[0] == key and not torch.cuda.is_current_stream_capturing():
+            if len(cache) > 2 and cache[2] is not None:          # packed by prepack_async on the side stream
+                cur = torch.cuda.current_stream()
+                cur.wait_event(cache[2])
+                cache[1].record_stream(cur)
+                self._wp_cache = (key, cache[1])
             return cache[1]
         wp = ops.pack_weight(weight)
         self._wp_cache = (key, wp)
         return wp
+
+    def prepack_async(self):
+        """Start re-packing the dhconv weight on the side stream; the next forward waits for it instead of packing on
+        the main stream.  Call right after the optimizer step (the update must have been enqueued on the current
+        stream): the 283 MB streaming pass then runs beside whatever the main stream does before this layer."""
+        if self.operator_type != "dhconv":
+            return
+        w = self.weight
+        ops._need_cuda(w, "weight")
+        key = (w._version, w.data_ptr(), w.device)
+        side = _side_stream(w.device)
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            wp = ops.pack_weight(w)
+            done = torch.cuda.Event()
+            done.record(side)
+        self._wp_cache = (key, wp, done)
 
     def _fused_ok(self):
         return (isinstance(self.forward_transform, _TransformBase) and isinstance(self.inverse_transform, _TransformBase)

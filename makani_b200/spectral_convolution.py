@@ -116,6 +116,7 @@ class _SpectralConvFunction(torch.autograd.Function):
                     del gwp
                 else:
                     gw = ops.unpack_wgrad(gwp, Cin, Cout, L)
+                    del gwp
             gsp = ops.dhconv_bwd_x(gsp2, wsaved, B, Cin, Cout, L, M, round_tf32=True) if ctx.needs_input_grad[0] else None
         else:
             if ctx.needs_input_grad[1]:

@@ -35,6 +35,15 @@ def test_reference_sfno_builds_on_product_modules():
     assert "OK reference SFNO built on product modules" in r.stdout
 
 
+def test_reference_quadrature_known_answer_on_product_quadrature():
+    """tests/test_metrics.py::TestMetrics::test_weight_normalization (the reference's only known-answer test that
+    touches the path) run unmodified: reference GridQuadrature on makani_b200.quadrature."""
+    r = subprocess.run([sys.executable, os.path.join(SCRIPTS, "run_reference_test_metrics.py")], capture_output=True,
+                       text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
+    assert "product quadrature: OK" in r.stdout
+
+
 @pytest.mark.parametrize("h,w", [(4, 1), (2, 2)])
 def test_reference_sfno_builds_spatially_parallel_on_product_modules(h, w):
     """BASELINE.json config 4 geometry (721 x 1440, h_parallel_size = 4 -> 181,181,181,178) through the reference's own

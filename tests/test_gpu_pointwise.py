@@ -85,6 +85,26 @@ def test_fused_instance_norm_forward_backward(mk, B, C, H, W, affine, act, use_s
         assert _rel(mod.bias.grad.cpu(), br.grad) < max(tol_b, 1e-5)
 
 
+def test_fp16_io(mk):
+    """fp16 in / out (third dtype of the C ABI): same kernels, tolerance 2e-3 (fp16 rounding of the stored result)."""
+    torch.manual_seed(4)
+    mod = mk.FusedInstanceNorm2d(6, eps=1e-6, affine=True, act="gelu").to(DEV)
+    with torch.no_grad():
+        mod.weight.copy_(1.0 + 0.5 * torch.randn(6))
+        mod.bias.copy_(0.5 * torch.randn(6))
+    x0 = (torch.randn(2, 6, 24, 48) * 1.5 + 0.7).to(torch.float16)
+    g0 = torch.randn(2, 6, 24, 48).to(torch.float16)
+    x = x0.to(DEV).requires_grad_(True)
+    y = mod(x)
+    assert y.dtype == torch.float16
+    y.backward(g0.to(DEV))
+    xr = x0.double().requires_grad_(True)
+    yr = _reference(xr, mod.weight.detach().double().cpu(), mod.bias.detach().double().cpu(), None, 1e-6, "gelu")
+    yr.backward(g0.double())
+    assert _rel(y.detach().cpu(), yr.detach()) < 2e-3
+    assert _rel(x.grad.cpu(), xr.grad) < 2e-3
+
+
 def test_large_mean_does_not_cancel(mk):
     """fields with |mean| >> std (e.g. geopotential, temperature in K): the shifted sums keep the variance."""
     torch.manual_seed(1)

@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define SFNO_ABI_VERSION 2
+#define SFNO_ABI_VERSION 3
 
 /* element types of spatial tensors crossing the boundary */
 enum { SFNO_F32 = 0, SFNO_BF16 = 1, SFNO_F16 = 2 };
@@ -113,7 +113,9 @@ int sfno_diag_contract(int mode, const float* sp_a, const void* w_or_spb, void* 
  * SP <-> complex64 [B][C][lmax][mmax] (what RealSHT returns / InverseRealSHT accepts).           */
 int sfno_sp_to_c64(const float* sp, int B, int C, int lmax, int mmax, int l_offset, int m_offset, void* out_c64,
                    void* stream);
-int sfno_c64_to_sp(const void* in_c64, int B, int C, int lmax, int mmax, float* sp, void* stream);
+/* entries with (m + m_offset) > (l + l_offset) are not read: they become the exact zeros the SP layout requires */
+int sfno_c64_to_sp(const void* in_c64, int B, int C, int lmax, int mmax, int l_offset, int m_offset, float* sp,
+                   void* stream);
 /* XM <-> complex64 [B][C][nlat][mmax]  (needed by the distributed SHT between its all-to-alls)   */
 int sfno_xm_to_c64(const float* xm, int B, int C, int nlat, int mmax, void* out_c64, void* stream);
 int sfno_c64_to_xm(const void* in_c64, int B, int C, int nlat, int mmax, float* xm, void* stream);
@@ -172,11 +174,15 @@ int sfno_ipc_open(const unsigned char handle[64], void** ptr);
 int sfno_ipc_close(void* ptr);
 int sfno_ipc_free(void* ptr);
 int sfno_rows_scatter(const float* src, const sfno_copy_desc* descs_host, int ndesc, void* stream);
-/* Stream-ordered barrier between the `size` (<= 8) ranks of one node through peer memory: rank r stores `epoch`
- * into slot r of every rank's flag array (flags_host[p] = pointer to rank p's array of >= 8 ints, zero at
- * allocation, mapped with sfno_ipc_open) and waits until all slots of its own array have reached `epoch`.
+/* Stream-ordered barrier between the `size` (<= 8) ranks of one node through peer memory: rank r stores the barrier
+ * number into slot r of every rank's flag array (flags_host[p] = pointer to rank p's array of >= 64 ints, zero at
+ * allocation, mapped with sfno_ipc_open) and waits until all slots of its own array have reached it.
  * Everything the ranks enqueued before the barrier (e.g. sfno_rows_scatter into peer buffers) is visible to what
- * they enqueue after it.  `epoch` must increase by one per barrier on the same flag arrays.                  */
+ * they enqueue after it.
+ * epoch <= 0 (recommended): the barrier number is kept in device memory (slot 32 of the rank's own array, incremented by
+ * the kernel), so the call can be captured in a CUDA graph and replayed (makani/utils/trainer.py:84-152); every rank
+ * must then issue the same sequence of barriers on these arrays.  epoch > 0: the caller numbers the barriers itself
+ * (+1 per barrier on the same arrays) - NOT replayable from a captured graph.                                    */
 int sfno_peer_barrier(int* const* flags_host, int rank, int size, int epoch, void* stream);
 
 /* ---- longitude DFT fused with the latitude <-> channel exchange of the h-sharded transforms --------

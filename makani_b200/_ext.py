@@ -36,7 +36,7 @@ _PROTOTYPES = {
     "sfno_dhconv_bwd_w": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "sfno_diag_contract": (_i, [_i, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "sfno_sp_to_c64": (_i, [_vp, _i, _i, _i, _i, _i, _i, _vp, _vp]),
-    "sfno_c64_to_sp": (_i, [_vp, _i, _i, _i, _i, _vp, _vp]),
+    "sfno_c64_to_sp": (_i, [_vp, _i, _i, _i, _i, _i, _i, _vp, _vp]),
     "sfno_xm_to_c64": (_i, [_vp, _i, _i, _i, _i, _vp, _vp]),
     "sfno_c64_to_xm": (_i, [_vp, _i, _i, _i, _i, _vp, _vp]),
     "sfno_add_bias": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _i, _vp]),
@@ -72,7 +72,7 @@ class CopyDesc(C.Structure):
 OP_SHT_FWD, OP_SHT_INV, OP_BLOCK_FWD = 0, 1, 2
 INSTNORM_SEGMENTS = 8
 ACT_NONE, ACT_GELU = 0, 1
-ABI_VERSION = 2
+ABI_VERSION = 3
 
 EXPORTED_SYMBOLS = tuple(_PROTOTYPES)
 

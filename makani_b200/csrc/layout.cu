@@ -53,7 +53,8 @@ __global__ void sp_to_c64_kernel(const float* __restrict__ sp, float2* __restric
   }
 }
 
-__global__ void c64_to_sp_kernel(const float2* __restrict__ in, float* __restrict__ sp, int B, int C, int L, int M) {
+__global__ void c64_to_sp_kernel(const float2* __restrict__ in, float* __restrict__ sp, int B, int C, int L, int M,
+                                 int l_off, int m_off) {
   __shared__ float tr[32][33], ti[32][33];
   const int Cp = (C + 3) & ~3;
   const long long RS = 2LL * B * Cp;
@@ -62,7 +63,8 @@ __global__ void c64_to_sp_kernel(const float2* __restrict__ in, float* __restric
   for (int j = threadIdx.y; j < 32; j += 8) {
     const int c = c0 + j, m = m0 + threadIdx.x;
     float2 v = make_float2(0.f, 0.f);
-    if (c < C && m < M) v = in[((long long)(b * C + c) * L + l) * M + m];
+    // spectral data vanish for m > l: whatever the caller holds there is not read (the SP contract wants exact zeros)
+    if (c < C && m < M && (m + m_off) <= (l + l_off)) v = in[((long long)(b * C + c) * L + l) * M + m];
     tr[j][threadIdx.x] = v.x;
     ti[j][threadIdx.x] = v.y;
   }
@@ -258,85 +260,123 @@ __global__ void add_bias_kernel(T* __restrict__ y, const float* __restrict__ bia
 //   MODE 0: y[b,o,l,m]  = sum_i x[b,i,l,m] w[i,o,l,m]          (a = SP x,  out = SP y)
 //   MODE 1: dx[b,i,l,m] = sum_o g[b,o,l,m] conj(w[i,o,l,m])    (a = SP g,  out = SP dx)
 //   MODE 2: dw[i,o,l,m] = sum_b conj(x[b,i,l,m]) g[b,o,l,m]    (a = SP x, b2 = SP g, out = complex64 dw)
-// One CTA per (l, 32 consecutive m); the SP tiles are staged in shared memory (channel-contiguous reads),
-// the weight is streamed with m across lanes (contiguous).  block (32, 8).
+// One CTA per (l, 32 consecutive m, chunk): the SP tiles are staged in shared memory (channel-contiguous reads), the
+// weight is streamed with m across lanes (contiguous).  block (32, 8).
+// Chunking keeps the staged tiles inside shared memory for any batch / channel count (the first version staged all
+// batch entries and all channels and failed for B*(Cin+Cout) > 799):
+//   MODE 0/1: blockIdx.z = (batch chunk of Bc <= kDiagBc entries) x (chunk of Cc result channels); the Bc results of
+//             one weight element are accumulated in registers, so the weight is read once per batch chunk
+//   MODE 2  : blockIdx.z = chunk of Cc output channels o; the batch is walked in chunks of Bc inside the kernel and
+//             the partial sums go through the (L2-resident) result
+constexpr int kDiagBc = 4;
 template <int MODE>
 __global__ void diag_kernel(const float* __restrict__ spa, const void* __restrict__ wb, void* __restrict__ outp,
-                            int B, int Cin, int Cout, int L, int M, int l_off, int m_off) {
+                            int B, int Cin, int Cout, int L, int M, int l_off, int m_off, int Bc, int Cc) {
   extern __shared__ float smd[];
   const int Cinp = (Cin + 3) & ~3, Coutp = (Cout + 3) & ~3;
   const int RSi = 2 * B * Cinp, RSo = 2 * B * Coutp;
   const int l = blockIdx.y, m0 = blockIdx.x * 32;
   const int mloc = threadIdx.x, m = m0 + mloc;
   const int tid = threadIdx.y * 32 + threadIdx.x;
-  const int RSa = (MODE == 1) ? RSo : RSi;            // channel extent of the staged SP input `spa`
-  const int RSb = (MODE == 1) ? RSi : RSo;            // extent of the second tile (output staging or g)
-  float* ta = smd;                                    // [32][RSa+1]
-  float* tb = smd + 32 * (RSa + 1);                   // [32][RSb+1]
   const int mhi_l = max(0, min(M, ((l + l_off + 16) & ~15) - m_off));   // defined extent of SP row l
-  // stage input tile(s); entries outside the defined / triangular region are zero
-  for (int idx = tid; idx < 32 * RSa; idx += 256) {
-    const int mm = idx / RSa, r = idx % RSa;
-    float v = 0.f;
-    if (m0 + mm < mhi_l && (m0 + mm + m_off) <= (l + l_off)) v = spa[((long long)l * M + m0 + mm) * RSa + r];
-    ta[mm * (RSa + 1) + r] = v;
-  }
-  if (MODE == 2) {
-    const float* spg = static_cast<const float*>(wb);
-    for (int idx = tid; idx < 32 * RSb; idx += 256) {
-      const int mm = idx / RSb, r = idx % RSb;
-      float v = 0.f;
-      if (m0 + mm < mhi_l && (m0 + mm + m_off) <= (l + l_off)) v = spg[((long long)l * M + m0 + mm) * RSb + r];
-      tb[mm * (RSb + 1) + r] = v;
-    }
-  }
-  __syncthreads();
   const long long LM = (long long)L * M;
+  // stage rows [r0, r0 + n) of the SP tile of (l, m0..m0+31) into t[32][n + 1]; zero outside the defined / triangular region
+  auto stage = [&](float* t, const float* sp, int RS, int r0, int n) {
+    for (int idx = tid; idx < 32 * n; idx += 256) {
+      const int mm = idx / n, r = idx - mm * n;
+      float v = 0.f;
+      if (m0 + mm < mhi_l && (m0 + mm + m_off) <= (l + l_off)) v = sp[((long long)l * M + m0 + mm) * RS + r0 + r];
+      t[mm * (n + 1) + r] = v;
+    }
+  };
   if (MODE == 0 || MODE == 1) {
-    const float2* w = static_cast<const float2*>(wb);
     const int Cred = (MODE == 0) ? Cin : Cout, Cres = (MODE == 0) ? Cout : Cin;
     const int Credp = (MODE == 0) ? Cinp : Coutp, Cresp = (MODE == 0) ? Coutp : Cinp;
-    for (int b = 0; b < B; ++b) {
-      for (int co = threadIdx.y; co < Cres; co += 8) {
-        float re = 0.f, im = 0.f;
-        if (m < M) {
-          for (int ci = 0; ci < Cred; ++ci) {
-            const int i = (MODE == 0) ? ci : co, o = (MODE == 0) ? co : ci;
-            const float2 wv = w[((long long)i * Cout + o) * LM + (long long)l * M + m];
-            const float xr = ta[mloc * (RSa + 1) + (b * 2) * Credp + ci];
-            const float xi = ta[mloc * (RSa + 1) + (b * 2 + 1) * Credp + ci];
-            if (MODE == 0) {
-              re += xr * wv.x - xi * wv.y;
-              im += xr * wv.y + xi * wv.x;
-            } else {
-              re += xr * wv.x + xi * wv.y;
-              im += xi * wv.x - xr * wv.y;
+    const int RSa = (MODE == 0) ? RSi : RSo, RSb = (MODE == 0) ? RSo : RSi;
+    const int ncc = (Cresp + Cc - 1) / Cc;
+    const int b0 = (blockIdx.z / ncc) * Bc, nb = min(Bc, B - b0);
+    const int c0 = (blockIdx.z % ncc) * Cc;
+    const int ncw = min(Cc, Cresp - c0);                // channels written by this CTA (pad channels: zeros)
+    const int nco = max(0, min(Cc, Cres - c0));         // channels computed
+    const int na = 2 * nb * Credp, nt = 2 * nb * Cc;
+    float* ta = smd;                                    // [32][na + 1]   x (or g) of this batch chunk, all channels
+    float* tb = smd + 32 * (na + 1);                    // [32][nt + 1]   results of this batch chunk, this channel chunk
+    stage(ta, spa, RSa, b0 * 2 * Credp, na);
+    __syncthreads();
+    const float2* w = static_cast<const float2*>(wb);
+    const float* xrow = ta + mloc * (na + 1);
+    for (int co = threadIdx.y; co < ncw; co += 8) {
+      float re[kDiagBc], im[kDiagBc];
+#pragma unroll
+      for (int bb = 0; bb < kDiagBc; ++bb) re[bb] = im[bb] = 0.f;
+      if (m < M && co < nco) {
+        for (int ci = 0; ci < Cred; ++ci) {
+          const int i = (MODE == 0) ? ci : c0 + co, o = (MODE == 0) ? c0 + co : ci;
+          const float2 wv = w[((long long)i * Cout + o) * LM + (long long)l * M + m];
+#pragma unroll
+          for (int bb = 0; bb < kDiagBc; ++bb) {
+            if (bb < nb) {
+              const float xr = xrow[(bb * 2) * Credp + ci], xi = xrow[(bb * 2 + 1) * Credp + ci];
+              if (MODE == 0) {
+                re[bb] += xr * wv.x - xi * wv.y;
+                im[bb] += xr * wv.y + xi * wv.x;
+              } else {
+                re[bb] += xr * wv.x + xi * wv.y;
+                im[bb] += xi * wv.x - xr * wv.y;
+              }
             }
           }
         }
-        tb[mloc * (RSb + 1) + (b * 2) * Cresp + co] = re;
-        tb[mloc * (RSb + 1) + (b * 2 + 1) * Cresp + co] = im;
+      }
+#pragma unroll
+      for (int bb = 0; bb < kDiagBc; ++bb) {
+        if (bb < nb) {
+          tb[mloc * (nt + 1) + (bb * 2) * Cc + co] = re[bb];
+          tb[mloc * (nt + 1) + (bb * 2 + 1) * Cc + co] = im[bb];
+        }
       }
     }
     __syncthreads();
     float* out = static_cast<float*>(outp);
-    for (int idx = tid; idx < 32 * RSb; idx += 256) {
-      const int mm = idx / RSb, r = idx % RSb;
-      const int c = r % Cresp;
-      if (m0 + mm < mhi_l) out[((long long)l * M + m0 + mm) * RSb + r] = (c < Cres) ? tb[mm * (RSb + 1) + r] : 0.f;
+    const int nw = 2 * nb * ncw;
+    for (int idx = tid; idx < 32 * nw; idx += 256) {
+      const int mm = idx / nw, r = idx - mm * nw;
+      const int j = r / ncw, c = r - j * ncw;           // j = bb*2 + reim
+      if (m0 + mm < mhi_l)
+        out[((long long)l * M + m0 + mm) * RSb + (long long)(b0 * 2 + j) * Cresp + c0 + c] = tb[mm * (nt + 1) + j * Cc + c];
     }
   } else {
+    const int o0 = blockIdx.z * Cc, nco = min(Cc, Cout - o0);
     float2* gw = static_cast<float2*>(outp);
-    for (int idx = threadIdx.y; idx < Cin * Cout; idx += 8) {
-      const int i = idx / Cout, o = idx % Cout;
-      float re = 0.f, im = 0.f;
-      for (int b = 0; b < B; ++b) {
-        const float xr = ta[mloc * (RSa + 1) + (b * 2) * Cinp + i], xi = ta[mloc * (RSa + 1) + (b * 2 + 1) * Cinp + i];
-        const float gr = tb[mloc * (RSb + 1) + (b * 2) * Coutp + o], gi = tb[mloc * (RSb + 1) + (b * 2 + 1) * Coutp + o];
-        re += xr * gr + xi * gi;
-        im += xr * gi - xi * gr;
+    const float* spg = static_cast<const float*>(wb);
+    for (int b0 = 0; b0 < B; b0 += Bc) {
+      const int nb = min(Bc, B - b0);
+      const int na = 2 * nb * Cinp, nt = 2 * nb * Coutp;
+      float* ta = smd;                                  // [32][na + 1]  x of this batch chunk
+      float* tb = smd + 32 * (2 * Bc * Cinp + 1);       // [32][nt + 1]  g of this batch chunk (all o: rows are contiguous)
+      __syncthreads();
+      stage(ta, spa, RSi, b0 * 2 * Cinp, na);
+      stage(tb, spg, RSo, b0 * 2 * Coutp, nt);
+      __syncthreads();
+      for (int idx = threadIdx.y; idx < Cin * nco; idx += 8) {
+        const int i = idx / nco, o = o0 + idx - i * nco;
+        float re = 0.f, im = 0.f;
+        for (int bb = 0; bb < nb; ++bb) {
+          const float xr = ta[mloc * (na + 1) + (bb * 2) * Cinp + i], xi = ta[mloc * (na + 1) + (bb * 2 + 1) * Cinp + i];
+          const float gr = tb[mloc * (nt + 1) + (bb * 2) * Coutp + o], gi = tb[mloc * (nt + 1) + (bb * 2 + 1) * Coutp + o];
+          re += xr * gr + xi * gi;
+          im += xr * gi - xi * gr;
+        }
+        if (m < M) {
+          float2* dst = gw + ((long long)i * Cout + o) * LM + (long long)l * M + m;
+          if (b0 > 0) {                                 // same thread wrote it in the previous pass
+            const float2 prev = *dst;
+            re += prev.x;
+            im += prev.y;
+          }
+          *dst = make_float2(re, im);
+        }
       }
-      if (m < M) gw[((long long)i * Cout + o) * LM + (long long)l * M + m] = make_float2(re, im);
     }
   }
 }
@@ -391,7 +431,24 @@ __global__ void __launch_bounds__(256) rows_scatter_kernel(const float* __restri
 struct BarrierArgs {
   int* flags[kMaxScatterDesc];
 };
+// epoch > 0: the caller numbers the barriers (legacy).  epoch <= 0: the barrier number lives in device memory - slot
+// kEpochSlot of this rank's own flag array is incremented by the kernel itself - so that a CUDA graph that captured the
+// launch replays with fresh numbers (a host-side epoch would be baked into the graph: from the second replay on every
+// flag already holds it and the barrier would fall through).  All ranks run the same sequence of barriers, so their
+// counters stay equal.
+constexpr int kEpochSlot = 32;
 __global__ void peer_barrier_kernel(const BarrierArgs args, int rank, int size, int epoch) {
+  __shared__ int s_epoch;
+  if (threadIdx.x == 0) {
+    if (epoch <= 0) {
+      int* ctr = args.flags[rank] + kEpochSlot;
+      epoch = *ctr + 1;
+      *ctr = epoch;
+    }
+    s_epoch = epoch;
+  }
+  __syncthreads();
+  epoch = s_epoch;
   const int p = threadIdx.x;
   if (p >= size) return;
   // everything this GPU did before this kernel (stream order) is published with the flag: system-scope release
@@ -419,10 +476,11 @@ int sfno_sp_to_c64(const float* sp, int B, int C, int lmax, int mmax, int l_offs
   SFNO_LAUNCHED();
   return 0;
 }
-int sfno_c64_to_sp(const void* in_c64, int B, int C, int lmax, int mmax, float* sp, void* stream) {
+int sfno_c64_to_sp(const void* in_c64, int B, int C, int lmax, int mmax, int l_offset, int m_offset, float* sp,
+                   void* stream) {
   const int Cp = (C + 3) & ~3;
   dim3 grid((mmax + 31) / 32, (Cp + 31) / 32, lmax * B), block(32, 8);
-  c64_to_sp_kernel<<<grid, block, 0, (cudaStream_t)stream>>>((const float2*)in_c64, sp, B, C, lmax, mmax);
+  c64_to_sp_kernel<<<grid, block, 0, (cudaStream_t)stream>>>((const float2*)in_c64, sp, B, C, lmax, mmax, l_offset, m_offset);
   SFNO_LAUNCHED();
   return 0;
 }
@@ -481,18 +539,41 @@ int sfno_add_bias(void* y, int y_dtype, const float* bias, int bias_kind, int B,
 
 int sfno_diag_contract(int mode, const float* sp_a, const void* w_or_spb, void* out, int B, int Cin, int Cout,
                        int lmax, int mmax, int l_offset, int m_offset, void* stream) {
+  SFNO_CHECK(mode >= 0 && mode <= 2, "bad mode");
   const int Cinp = (Cin + 3) & ~3, Coutp = (Cout + 3) & ~3;
-  const size_t smem = (size_t)32 * (2 * B * Cinp + 2 * B * Coutp + 2) * 4;
-  SFNO_CHECK(smem <= 200 * 1024, "diagonal contraction: B*(Cin+Cout) too large for the shared-memory tile");
-  dim3 grid((mmax + 31) / 32, lmax), block(32, 8);
+  const size_t cap = 200 * 1024;
+  // chunk sizes (see diag_kernel): as many batch entries per pass as fit (<= kDiagBc), then as many channels
+  int Bc = std::min(B, kDiagBc), Cc = 0, nz = 0;
+  size_t smem = 0;
+  if (mode == 2) {
+    for (; Bc >= 1; --Bc) {
+      smem = (size_t)32 * (2 * Bc * Cinp + 2 * Bc * Coutp + 2) * 4;
+      if (smem <= cap) break;
+    }
+    SFNO_CHECK(Bc >= 1, "diagonal contraction: Cin + Cout too large for the shared-memory tile (> 799)");
+    Cc = std::min(Cout, 64);                       // output-channel chunk per CTA (only splits the work)
+    nz = (Cout + Cc - 1) / Cc;
+  } else {
+    const int Credp = mode == 0 ? Cinp : Coutp, Cresp = mode == 0 ? Coutp : Cinp;
+    for (; Bc >= 1 && !Cc; --Bc) {
+      for (int c = Cresp; c >= 4; c = (c > 8 ? ((c / 2 + 3) & ~3) : c - 4)) {
+        smem = (size_t)32 * (2 * Bc * Credp + 2 * Bc * c + 2) * 4;
+        if (smem <= cap) { Cc = c; break; }
+      }
+      if (Cc) break;
+    }
+    SFNO_CHECK(Cc > 0, "diagonal contraction: channel count too large for the shared-memory tile (> 1590)");
+    nz = ((B + Bc - 1) / Bc) * ((Cresp + Cc - 1) / Cc);
+  }
+  SFNO_CHECK(nz <= 65535, "diagonal contraction: too many chunks");
+  dim3 grid((mmax + 31) / 32, lmax, nz), block(32, 8);
   cudaStream_t s = (cudaStream_t)stream;
 #define SFNO_DIAG(MODE)                                                                                     \
-  SFNO_CUDA(cudaFuncSetAttribute(diag_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024)); \
-  diag_kernel<MODE><<<grid, block, smem, s>>>(sp_a, w_or_spb, out, B, Cin, Cout, lmax, mmax, l_offset, m_offset)
+  SFNO_CUDA(cudaFuncSetAttribute(diag_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cap)); \
+  diag_kernel<MODE><<<grid, block, smem, s>>>(sp_a, w_or_spb, out, B, Cin, Cout, lmax, mmax, l_offset, m_offset, Bc, Cc)
   if (mode == 0) { SFNO_DIAG(0); }
   else if (mode == 1) { SFNO_DIAG(1); }
-  else if (mode == 2) { SFNO_DIAG(2); }
-  else SFNO_CHECK(false, "bad mode");
+  else { SFNO_DIAG(2); }
 #undef SFNO_DIAG
   SFNO_LAUNCHED();
   return 0;

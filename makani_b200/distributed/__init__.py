@@ -250,7 +250,7 @@ class _LegendreStage(torch.autograd.Function):
         B, Cn = c.shape[0], c.shape[1]
         ctx.mod, ctx.synthesis = mod, synthesis
         if synthesis:
-            xm = ops.legendre_synthesis(plan, ops.c64_to_sp(c), B, Cn)
+            xm = ops.legendre_synthesis(plan, ops.c64_to_sp(c, 0, plan.m_offset), B, Cn)
             return ops.xm_to_c64(xm, B, Cn, mod.nlat, plan.mmax)
         sp = ops.legendre_analysis(plan, ops.c64_to_xm(c), B, Cn)
         return ops.sp_to_c64(sp, B, Cn, mod.lmax, plan.mmax, 0, plan.m_offset)
@@ -264,7 +264,7 @@ class _LegendreStage(torch.autograd.Function):
         if ctx.synthesis:
             gsp = ops.legendre_analysis(plan, ops.c64_to_xm(g), B, Cn)
             return ops.sp_to_c64(gsp, B, Cn, mod.lmax, plan.mmax, 0, plan.m_offset), None, None
-        gxm = ops.legendre_synthesis(plan, ops.c64_to_sp(g), B, Cn)
+        gxm = ops.legendre_synthesis(plan, ops.c64_to_sp(g, 0, plan.m_offset), B, Cn)
         return ops.xm_to_c64(gxm, B, Cn, mod.nlat, plan.mmax), None, None
 
 
@@ -330,6 +330,7 @@ class _PolarExchange:
             self._plans[key] = plan
         pb, arrs, fence = plan
         b = pb.next()
+        fence.pre_write()
         if arrs[b] is not None:
             p2p.scatter(src, arrs[b])
         fence()
@@ -389,6 +390,7 @@ class _PolarExchange:
         pb, ptrs, shapes, fence = self._xm_ch_buffers()
         b = pb.next()
         me = self.me
+        fence.pre_write()
         _ext.check(_ext.load().sfno_dft_fwd_peer(
             ct.c_void_p(x.data_ptr()), ops.dtype_code(x.dtype), self.B, self.C, self.lat[me], x.shape[-1], self.M,
             ct.c_void_p(mscale.data_ptr()), ct.cast(ptrs[b], ct.c_void_p), ct.cast(shapes, ct.c_void_p), self.h, self.Kpg,
@@ -404,6 +406,7 @@ class _PolarExchange:
         pb, ptrs, shapes, fence = self._xm_ch_buffers()
         b = pb.next()
         me = self.me
+        fence.pre_write()
         ops.legendre_synthesis(plan, sp_ch, self.B, self.cs[me],
                                out=pb.local[b][: self.M * self.J * _rup4(self.cs[me]) * self.Kpg])
         fence()
@@ -460,7 +463,7 @@ def _polar_synthesis(c, mod, scale_kind, dtype):
     B, Cn = c.shape[0], c.shape[1]
     ex = _PolarExchange.of(mod, B, Cn, c.device)
     plan = mod._peer_plan(c.device)
-    sp_l = ops.c64_to_sp(c.to(torch.complex64))
+    sp_l = ops.c64_to_sp(c.to(torch.complex64), ex.l0[ex.me], 0)
     sp_ch = ex.l_to_chan(sp_l)
     if ex.dft_fused(mod):
         return ex.chan_to_field(plan, sp_ch, mod.nlon, mod._scale(c.device, scale_kind), dtype)

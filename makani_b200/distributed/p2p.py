@@ -16,6 +16,13 @@ starts.  ``MAKANI_B200_P2P_FENCE=nccl`` uses a one-element NCCL all-reduce inste
 alternately (two per layout); a buffer is written again only two exchanges later, after an intervening barrier that
 every rank enters behind its own consumer of the earlier contents - so no second barrier is needed for the
 write-after-read hazard.
+
+CUDA graphs (the reference captures forward + backward, makani/utils/trainer.py:84-152): the barrier number lives in
+device memory (the kernel increments it), so a captured barrier replays correctly; the buffer alternation, however,
+is decided on the host and is baked into a captured graph - a graph with an odd number of exchanges per layout would
+write the same buffer at its end and again at the start of the next replay with no barrier in between.  While a stream
+is capturing, every exchange is therefore preceded by one more barrier (``pre_write``): a rank enters it behind its own
+last consumer of the buffer, so nobody overwrites contents that are still being read.
 """
 from __future__ import annotations
 
@@ -87,7 +94,7 @@ class PeerFence:
         self.rank = dist.get_rank(group=group)
         self.size = dist.get_world_size(group=group)
         self.use_nccl = os.environ.get("MAKANI_B200_P2P_FENCE", "peer") == "nccl"
-        self.epoch = 0
+        self.barriers = 0                      # issued from this process (statistics only; the number itself is on the device)
         self._flag = torch.zeros(1, dtype=torch.float32, device=device)
         with torch.cuda.device(device):
             p = C.c_void_p()
@@ -110,10 +117,16 @@ class PeerFence:
         if self.use_nccl:
             dist.all_reduce(self._flag, group=self.group)
             return
-        self.epoch += 1
+        self.barriers += 1
         stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
-        _ext.check(_ext.load().sfno_peer_barrier(C.cast(self._ptrs, C.c_void_p), self.rank, self.size, self.epoch,
-                                                 stream), "sfno_peer_barrier")
+        _ext.check(_ext.load().sfno_peer_barrier(C.cast(self._ptrs, C.c_void_p), self.rank, self.size, 0, stream),
+                   "sfno_peer_barrier")
+
+    def pre_write(self):
+        """Called before a kernel writes into receive buffers: under CUDA-graph capture the host-side buffer alternation
+        cannot be relied on (module docstring), so order the write behind every rank's last consumer."""
+        if torch.cuda.is_current_stream_capturing():
+            self()
 
 
 _FENCES: Dict[Tuple, PeerFence] = {}

@@ -157,14 +157,16 @@ def sp_to_c64(sp, B, Cn, lmax, mmax, l_offset=0, m_offset=0) -> torch.Tensor:
     return out
 
 
-def c64_to_sp(c: torch.Tensor) -> torch.Tensor:
+def c64_to_sp(c: torch.Tensor, l_offset: int = 0, m_offset: int = 0) -> torch.Tensor:
+    """complex64 [B, C, L, M] -> SP.  Entries with m + m_offset > l + l_offset are taken as zero (not read)."""
     _need_cuda(c, "coefficients")
     B, Cn, L, M = c.shape
     c = c.contiguous()
     if c.dtype != torch.complex64:
         raise TypeError(f"makani_b200: spectral coefficients must be complex64, got {c.dtype}")
     sp = torch.empty(sp_elems(L, M, B, Cn), dtype=torch.float32, device=c.device)
-    _ext.check(_ext.load().sfno_c64_to_sp(_ptr(c), B, Cn, L, M, _ptr(sp), _stream()), "sfno_c64_to_sp")
+    _ext.check(_ext.load().sfno_c64_to_sp(_ptr(c), B, Cn, L, M, l_offset, m_offset, _ptr(sp), _stream()),
+               "sfno_c64_to_sp")
     return sp
 
 

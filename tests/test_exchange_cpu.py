@@ -58,7 +58,14 @@ def fake_peer_memory(monkeypatch):
     state = {"rank": 0, "h": 1}
     monkeypatch.setattr(p2p, "buffers", lambda key, n, group, device: FakeBuffers(key, n, state["h"], state["rank"]))
     monkeypatch.setattr(p2p, "scatter", fake_scatter)
-    monkeypatch.setattr(p2p, "fence", lambda group, device: (lambda: None))
+    class NoFence:                       # one process plays the ranks in turn: nothing to order
+        def __call__(self):
+            pass
+
+        def pre_write(self):
+            pass
+
+    monkeypatch.setattr(p2p, "fence", lambda group, device: NoFence())
     monkeypatch.setattr(thd, "polar_group", lambda: None)
     return state
 

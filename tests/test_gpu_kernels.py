@@ -95,6 +95,8 @@ def _table(M, L, K, seed):
     (2, 3, 33, 20, 17),          # odd everything, pad channels, latitude pad
     (1, 70, 40, 40, 21),         # more than one 128-row tile (RS = 144)
     (1, 24, 300, 280, 100),      # > 256 degrees: two N tiles
+    (1, 5, 721, 240, 241),       # the SFNO `trans_down` geometry: odd K = 721 (Kp = 724, TMA zero fill), L = 240, M = 241
+    (1, 6, 240, 240, 241),       # the SFNO internal geometry
 ])
 def test_legendre_analysis(ops, B, C, K, L, M):
     torch.manual_seed(2)
@@ -118,6 +120,8 @@ def test_legendre_analysis(ops, B, C, K, L, M):
     (2, 3, 33, 20, 17),
     (1, 70, 140, 40, 21),        # two row tiles (K > 128), RS = 144
     (1, 136, 40, 24, 30),        # RS = 272 > 256: two column tiles; m >= L columns are all-zero
+    (1, 5, 721, 240, 241),       # the SFNO `itrans_up` geometry: K = 721 -> six row tiles, the last one partial
+    (1, 6, 240, 240, 241),       # the SFNO internal geometry
 ])
 def test_legendre_synthesis(ops, B, C, K, L, M):
     torch.manual_seed(4)
@@ -167,7 +171,13 @@ def test_dhconv(ops, B, Cin, Cout, L, M):
     assert rel_err(gw, ref) < TOL_TF32, ("bwd_w", rel_err(gw, ref))
 
 
-@pytest.mark.parametrize("B,Cin,Cout,L,M", [(2, 6, 10, 20, 21), (1, 16, 16, 40, 33)])
+@pytest.mark.parametrize("B,Cin,Cout,L,M", [
+    (2, 6, 10, 20, 21),
+    (1, 16, 16, 40, 33),
+    (2, 256, 256, 8, 9),         # embed_dim 256 at local batch 2 (staged tiles must be chunked over channels)
+    (5, 40, 36, 12, 13),         # batch walked in chunks of 4 + 1
+    (1, 420, 404, 6, 7),         # C >= 400 at batch 1
+])
 def test_diagonal(ops, B, Cin, Cout, L, M):
     torch.manual_seed(7)
     dev = _dev()
@@ -250,12 +260,17 @@ def test_rows_scatter_and_peer_barrier_single_gpu(built_lib, monkeypatch, h, nla
     _ext.check(lib.sfno_ipc_alloc(256, C_.byref(flags), hnd), "sfno_ipc_alloc")
     epoch = [0]
 
-    def barrier():
-        epoch[0] += 1
-        arr = (C_.c_void_p * 1)(flags.value)
-        stream = C_.c_void_p(torch.cuda.current_stream().cuda_stream)
-        _ext.check(lib.sfno_peer_barrier(C_.cast(arr, C_.c_void_p), 0, 1, epoch[0], stream), "sfno_peer_barrier")
+    class Barrier:                       # size-1 barrier with the barrier number kept on the device (epoch argument 0)
+        def __call__(self):
+            epoch[0] += 1
+            arr = (C_.c_void_p * 1)(flags.value)
+            stream = C_.c_void_p(torch.cuda.current_stream().cuda_stream)
+            _ext.check(lib.sfno_peer_barrier(C_.cast(arr, C_.c_void_p), 0, 1, 0, stream), "sfno_peer_barrier")
 
+        def pre_write(self):
+            pass
+
+    barrier = Barrier()
     monkeypatch.setattr(p2p, "buffers", lambda key, n, group, device: DevBuffers(key, n))
     monkeypatch.setattr(p2p, "fence", lambda group, device: barrier)
     monkeypatch.setattr(thd, "polar_group", lambda: None)
@@ -263,6 +278,9 @@ def test_rows_scatter_and_peer_barrier_single_gpu(built_lib, monkeypatch, h, nla
         check_exchange(state, h, nlat, L, M, B, C, dev)
         torch.cuda.synchronize()
         assert epoch[0] > 0
+        # the kernel numbered the barriers itself: slot 0 (arrival of rank 0) and slot 32 (the counter) hold their count
+        fl = torch.as_tensor(p2p._DevPtr(flags.value, 64), device=dev).view(torch.int32).cpu()
+        assert int(fl[0]) == epoch[0] and int(fl[32]) == epoch[0]
     finally:
         torch.cuda.synchronize()
         for bufs in pool.values():

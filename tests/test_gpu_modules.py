@@ -134,6 +134,21 @@ def test_spectral_conv_sfno_internal_shapes_small_channels(mk):
     _block(mk, 240, 480, "legendre-gauss", 240, 480, "legendre-gauss", 240, 241, 8, 8, "dhconv", 1, torch.float32)
 
 
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_spectral_conv_sfno_block0_real_grids_small_channels(mk, dtype):
+    """SFNO block 0 at its real geometry (sfnonet.py:392-393,536-539): 721x1440 equiangular in (K = 721 Legendre,
+    `trans_down` table, nlon = 1440 DFT) -> L = 240, M = 241 -> 240x480 Gauss out, residual re-projected; few
+    channels so the fp64 oracle stays cheap.  Output, residual, dX and dW against the oracle values."""
+    _block(mk, 721, 1440, "equiangular", 240, 480, "legendre-gauss", 240, 241, 6, 8, "dhconv", 1, dtype)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_spectral_conv_sfno_block7_real_grids_small_channels(mk, dtype):
+    """SFNO block 7: 240x480 Gauss in -> 721x1440 equiangular out (`itrans_up` table, K = 721 synthesis, inverse
+    DFT at nlon = 1440), output and re-projected residual both at full resolution."""
+    _block(mk, 240, 480, "legendre-gauss", 721, 1440, "equiangular", 240, 241, 8, 6, "dhconv", 1, dtype)
+
+
 def test_state_dict_and_annotations(mk):
     fwd = mk.RealSHT(16, 32, grid="legendre-gauss")
     inv = mk.InverseRealSHT(16, 32, grid="legendre-gauss")

@@ -50,7 +50,7 @@ def test_library_exports_every_declared_symbol(built_lib):
         assert hasattr(lib, name), f"{name} declared in include/makani_b200.h but not exported"
     from makani_b200 import _ext
     assert set(_ext.EXPORTED_SYMBOLS) == declared
-    assert _ext.load().sfno_abi_version() == _ext.ABI_VERSION == 2
+    assert _ext.load().sfno_abi_version() == _ext.ABI_VERSION == 3
     assert _ext.launch_count() == 0
     # size helpers are pure host arithmetic
     assert _ext.load().sfno_xm_elems(721, 241, 1, 384) == 241 * 768 * 724

@@ -88,7 +88,6 @@ def gpu_step(blocks, xs_dev, grads):
     for blk, x, (gy, gr) in zip(blocks, xs_dev, grads):
         x.grad = None
         blk.weight.grad = None
-        blk._wp_cache = None          # a training step follows an optimizer update: the packed weight copy is rebuilt
         y, res = blk(x)
         if gr is not None:
             torch.autograd.backward([y, res], [gy, gr])
@@ -112,8 +111,6 @@ def gpu_step_chained(blocks, x0, grads):
             blk.prepack_async()
     for blk, (gy, gr) in zip(blocks, grads):
         blk.weight.grad = None
-        if not prepack:
-            blk._wp_cache = None      # a training step follows an optimizer update: the packed weight copy is rebuilt
         y, res = blk(x)
         if gr is not None:
             outs.append(res)

@@ -82,6 +82,27 @@ int sfno_legendre_analysis(const sfno_plan* plan, const float* xm, int B, int C,
                            void* stream);
 int sfno_legendre_synthesis(const sfno_plan* plan, const float* sp, int B, int C, float* xm, void* stream);
 
+/* ---- channel-window variants of K1 / K2 / K4 / K5 -----------------------------------------------
+ * The chain DFT -> Legendre (and Legendre -> inverse DFT) is independent per channel, so it can be run window by window
+ * over the channels, with the Fourier coefficients of ONE window going through a small XM buffer that is re-used for
+ * every window: the buffer (tens of MB) then lives in the 126 MB L2 instead of travelling to HBM and back (XM of the
+ * whole field is 178 MB at 240x480 and 536 MB at 721x1440, C = 384).  This is how SpectralConv fuses across the
+ * RFFT -> Legendre and Legendre -> inverse-RFFT boundaries of makani/models/common/spectral_convolution.py:131-141.
+ *   x / y   : the WHOLE field [B][Ctot][nlat][nlon];   sp : the WHOLE SP tensor (Ctot channels)
+ *   xm_win  : compact XM of the window, [mmax][2B][round_up(C,4)][Kp]  (sfno_xm_elems(nlat, mmax, B, C) floats)
+ *   window  : channels [c0, c0 + C);  a true window (C < Ctot) needs C % 32 == 0 and c0 % 4 == 0
+ * accumulate = 1 (analysis): SP += result (sum of the gradients of two consumers of one SP tensor).
+ * The kernels give the window and the Legendre table L2 priority (evict_last) and let the field rows stream
+ * (evict_first); SFNO_WINDOW_HINTS=0 in the environment disables the hints.                                  */
+int sfno_dft_fwd_win(const void* x, int x_dtype, int B, int Ctot, int c0, int C, int nlat, int nlon, int mmax,
+                     const float* mscale_dev, float* xm_win, int round_tf32, void* stream);
+int sfno_dft_inv_win(const float* xm_win, int B, int Ctot, int c0, int C, int nlat, int nlon, int mmax, int m_valid,
+                     const float* mscale_dev, void* y, int y_dtype, void* stream);
+int sfno_legendre_analysis_win(const sfno_plan* plan, const float* xm_win, int B, int Ctot, int c0, int C, float* sp,
+                               int round_tf32, int accumulate, void* stream);
+int sfno_legendre_synthesis_win(const sfno_plan* plan, const float* sp, int B, int Ctot, int c0, int C, float* xm_win,
+                                void* stream);
+
 /* ---- K3 dhconv channel contraction (makani/models/common/contractions.py:131-136,
  * einsum "bixy,iox->boxy" on complex64) as planar-complex TF32 tcgen05 GEMMs, batched over l.   */
 int sfno_dhconv_pack_weight(const void* w_c64 /*[Cin][Cout][L] complex64*/, int Cin, int Cout, int L,
@@ -123,6 +144,11 @@ int sfno_c64_to_xm(const void* in_c64, int B, int C, int nlat, int mmax, float* 
 /* y[b][c][h][w] (+)= bias   (spectral_convolution.py:143-144); bias_kind 0: [C], 1: [C][H][W]    */
 int sfno_add_bias(void* y, int y_dtype, const float* bias, int bias_kind, int B, int C, int H, int W,
                   void* stream);
+
+/* Constant bias [C] folded into the m = 0 Fourier coefficient of an XM tensor (or XM window: pass bias + c0) before
+ * the inverse DFT:  XM[0][b][re][c][k] += bias[c].  Equals `x = x + bias` in fp32 before the cast to the output dtype
+ * (spectral_convolution.py:143-146) at the cost of B*C*nlat elements.                                        */
+int sfno_xm_add_dc(float* xm, int B, int C, int nlat, const float* bias, void* stream);
 
 /* ---- composite calls: one call per reference operator ------------------------------------------
  * For callers that do not want to sequence the kernels themselves (the C ABI list of SURVEY.md 8(b)).

@@ -29,6 +29,10 @@ _PROTOTYPES = {
     "sfno_dft_inv": (_i, [_vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _i, _vp]),
     "sfno_legendre_analysis": (_i, [_vp, _vp, _i, _i, _vp, _i, _vp]),
     "sfno_legendre_synthesis": (_i, [_vp, _vp, _i, _i, _vp, _vp]),
+    "sfno_dft_fwd_win": (_i, [_vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _vp, _i, _vp]),
+    "sfno_dft_inv_win": (_i, [_vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _vp, _i, _vp]),
+    "sfno_legendre_analysis_win": (_i, [_vp, _vp, _i, _i, _i, _i, _vp, _i, _i, _vp]),
+    "sfno_legendre_synthesis_win": (_i, [_vp, _vp, _i, _i, _i, _i, _vp, _vp]),
     "sfno_dhconv_pack_weight": (_i, [_vp, _i, _i, _i, _vp, _vp]),
     "sfno_dhconv_unpack_wgrad": (_i, [_vp, _i, _i, _i, _vp, _vp]),
     "sfno_dhconv_fwd": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
@@ -40,6 +44,7 @@ _PROTOTYPES = {
     "sfno_xm_to_c64": (_i, [_vp, _i, _i, _i, _i, _vp, _vp]),
     "sfno_c64_to_xm": (_i, [_vp, _i, _i, _i, _i, _vp, _vp]),
     "sfno_add_bias": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _i, _vp]),
+    "sfno_xm_add_dc": (_i, [_vp, _i, _i, _i, _vp, _vp]),
     "sfno_workspace_bytes": (C.c_size_t, [_vp, _vp, _i, _i, _i]),
     "sfno_sht_fwd": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp, C.c_size_t, _vp]),
     "sfno_sht_inv": (_i, [_vp, _vp, _i, _i, _vp, _i, _vp, C.c_size_t, _vp]),

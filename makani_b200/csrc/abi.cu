@@ -105,21 +105,48 @@ int sfno_plan_destroy(sfno_plan* plan) {
 int sfno_dft_fwd(const void* x, int x_dtype, int B, int C, int nlat, int nlon, int mmax, const float* mscale_dev,
                  float* xm, int round_tf32, void* stream) {
   SFNO_CHECK(x && xm && mscale_dev, "null argument");
-  return dft_fwd(x, x_dtype, B, C, nlat, nlon, mmax, mscale_dev, xm, round_tf32, (cudaStream_t)stream);
+  return dft_fwd(x, x_dtype, B, C, C, nlat, nlon, mmax, mscale_dev, xm, round_tf32, (cudaStream_t)stream);
 }
 int sfno_dft_inv(const float* xm, int B, int C, int nlat, int nlon, int mmax, int m_valid, const float* mscale_dev,
                  void* y, int y_dtype, void* stream) {
   SFNO_CHECK(xm && y && mscale_dev, "null argument");
-  return dft_inv(xm, B, C, nlat, nlon, mmax, m_valid, mscale_dev, y, y_dtype, (cudaStream_t)stream);
+  return dft_inv(xm, B, C, C, nlat, nlon, mmax, m_valid, mscale_dev, y, y_dtype, (cudaStream_t)stream);
 }
 int sfno_legendre_analysis(const sfno_plan* plan, const float* xm, int B, int C, float* sp, int round_tf32,
                            void* stream) {
   SFNO_CHECK(plan && xm && sp, "null argument");
-  return legendre_analysis(plan, xm, B, C, sp, round_tf32, (cudaStream_t)stream);
+  return legendre_analysis(plan, xm, B, C, C, 0, sp, round_tf32, 0, (cudaStream_t)stream);
 }
 int sfno_legendre_synthesis(const sfno_plan* plan, const float* sp, int B, int C, float* xm, void* stream) {
   SFNO_CHECK(plan && xm && sp, "null argument");
-  return legendre_synthesis(plan, sp, B, C, xm, (cudaStream_t)stream);
+  return legendre_synthesis(plan, sp, B, C, C, 0, xm, (cudaStream_t)stream);
+}
+
+// ---- channel-window variants (see the header): XM is a compact tensor over the window, the field / SP are whole
+static size_t dtype_size(int dt) { return dt == SFNO_F32 ? 4 : 2; }
+int sfno_dft_fwd_win(const void* x, int x_dtype, int B, int Ctot, int c0, int C, int nlat, int nlon, int mmax,
+                     const float* mscale_dev, float* xm_win, int round_tf32, void* stream) {
+  SFNO_CHECK(x && xm_win && mscale_dev, "null argument");
+  SFNO_CHECK(c0 >= 0 && C > 0 && c0 + C <= Ctot, "sfno_dft_fwd_win: bad channel window");
+  const char* xw = static_cast<const char*>(x) + (size_t)c0 * nlat * nlon * dtype_size(x_dtype);
+  return dft_fwd(xw, x_dtype, B, C, Ctot, nlat, nlon, mmax, mscale_dev, xm_win, round_tf32, (cudaStream_t)stream);
+}
+int sfno_dft_inv_win(const float* xm_win, int B, int Ctot, int c0, int C, int nlat, int nlon, int mmax, int m_valid,
+                     const float* mscale_dev, void* y, int y_dtype, void* stream) {
+  SFNO_CHECK(xm_win && y && mscale_dev, "null argument");
+  SFNO_CHECK(c0 >= 0 && C > 0 && c0 + C <= Ctot, "sfno_dft_inv_win: bad channel window");
+  char* yw = static_cast<char*>(y) + (size_t)c0 * nlat * nlon * dtype_size(y_dtype);
+  return dft_inv(xm_win, B, C, Ctot, nlat, nlon, mmax, m_valid, mscale_dev, yw, y_dtype, (cudaStream_t)stream);
+}
+int sfno_legendre_analysis_win(const sfno_plan* plan, const float* xm_win, int B, int Ctot, int c0, int C, float* sp,
+                               int round_tf32, int accumulate, void* stream) {
+  SFNO_CHECK(plan && xm_win && sp, "null argument");
+  return legendre_analysis(plan, xm_win, B, C, Ctot, c0, sp, round_tf32, accumulate, (cudaStream_t)stream);
+}
+int sfno_legendre_synthesis_win(const sfno_plan* plan, const float* sp, int B, int Ctot, int c0, int C, float* xm_win,
+                                void* stream) {
+  SFNO_CHECK(plan && xm_win && sp, "null argument");
+  return legendre_synthesis(plan, sp, B, C, Ctot, c0, xm_win, (cudaStream_t)stream);
 }
 int sfno_dhconv_fwd(const float* sp_in, const float* wp, float* sp_out, int B, int Cin, int Cout, int lmax, int mmax,
                     int l_offset, int m_offset, int round_tf32, void* stream) {
@@ -171,8 +198,8 @@ int sfno_sht_fwd(const sfno_plan* plan, const void* x, int x_dtype, int B, int C
   cudaStream_t s = (cudaStream_t)stream;
   float* xm = static_cast<float*>(ws);
   float* sp = reinterpret_cast<float*>(static_cast<char*>(ws) + xm_bytes(plan, B, C));
-  if (dft_fwd(x, x_dtype, B, C, plan->nlat, plan->nlon, plan->mmax, plan->mscale, xm, 1, s)) return 1;
-  if (legendre_analysis(plan, xm, B, C, sp, 0, s)) return 1;
+  if (dft_fwd(x, x_dtype, B, C, C, plan->nlat, plan->nlon, plan->mmax, plan->mscale, xm, 1, s)) return 1;
+  if (legendre_analysis(plan, xm, B, C, C, 0, sp, 0, 0, s)) return 1;
   return sfno_sp_to_c64(sp, B, C, plan->lmax, plan->mmax, 0, 0, coeffs_c64, stream);
 }
 
@@ -186,8 +213,8 @@ int sfno_sht_inv(const sfno_plan* plan, const void* coeffs_c64, int B, int C, vo
   float* xm = static_cast<float*>(ws);
   float* sp = reinterpret_cast<float*>(static_cast<char*>(ws) + xm_bytes(plan, B, C));
   if (sfno_c64_to_sp(coeffs_c64, B, C, plan->lmax, plan->mmax, 0, plan->m_offset, sp, stream)) return 1;
-  if (legendre_synthesis(plan, sp, B, C, xm, s)) return 1;
-  return dft_inv(xm, B, C, plan->nlat, plan->nlon, plan->mmax, plan->mmax, plan->mscale + (plan->nlon / 2 + 1), y,
+  if (legendre_synthesis(plan, sp, B, C, C, 0, xm, s)) return 1;
+  return dft_inv(xm, B, C, C, plan->nlat, plan->nlon, plan->mmax, plan->mmax, plan->mscale + (plan->nlon / 2 + 1), y,
                  y_dtype, s);
 }
 
@@ -205,11 +232,11 @@ int sfno_block_fwd(const sfno_plan* pf, const sfno_plan* pi, const void* x, int 
   float* sp_a = reinterpret_cast<float*>(base + std::max(xm_bytes(pf, B, C), xm_bytes(pi, B, C)));
   float* sp_b = reinterpret_cast<float*>(reinterpret_cast<char*>(sp_a) + sp_bytes(pf, B, C));
   // every intermediate feeds a TF32 contraction: store round-to-nearest TF32 values (see sfno_legendre_analysis)
-  if (dft_fwd(x, dtype, B, Cin, pf->nlat, pf->nlon, pf->mmax, pf->mscale, xm, 1, s)) return 1;
-  if (legendre_analysis(pf, xm, B, Cin, sp_a, 1, s)) return 1;
+  if (dft_fwd(x, dtype, B, Cin, Cin, pf->nlat, pf->nlon, pf->mmax, pf->mscale, xm, 1, s)) return 1;
+  if (legendre_analysis(pf, xm, B, Cin, Cin, 0, sp_a, 1, 0, s)) return 1;
   if (dhconv_fwd(sp_a, wp, sp_b, B, Cin, Cout, pf->lmax, pf->mmax, 0, 0, 1, s)) return 1;
-  if (legendre_synthesis(pi, sp_b, B, Cout, xm, s)) return 1;
-  return dft_inv(xm, B, Cout, pi->nlat, pi->nlon, pi->mmax, pi->mmax, pi->mscale + (pi->nlon / 2 + 1), y, dtype, s);
+  if (legendre_synthesis(pi, sp_b, B, Cout, Cout, 0, xm, s)) return 1;
+  return dft_inv(xm, B, Cout, Cout, pi->nlat, pi->nlon, pi->mmax, pi->mmax, pi->mscale + (pi->nlon / 2 + 1), y, dtype, s);
 }
 
 int sfno_dft_peer_supported(int nlon, int mmax) { return dft_peer_supported(nlon, mmax) ? 1 : 0; }

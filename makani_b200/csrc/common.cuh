@@ -59,6 +59,20 @@ inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, s
   return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
 
+// Per-device "done once" flag: function attributes (cudaFuncSetAttribute) and the SM count belong to a device, so a
+// process that drives several GPUs must set / query them once per device, not once per process.
+struct PerDeviceOnce {
+  std::atomic<unsigned long long> done{0};
+  static int device() {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    return dev & 63;
+  }
+  bool needed() const { return !((done.load(std::memory_order_acquire) >> device()) & 1ull); }
+  void mark() { done.fetch_or(1ull << device(), std::memory_order_release); }
+};
+int sm_count_current_device();
+
 inline int round_up(int x, int m) { return (x + m - 1) / m * m; }
 inline long long round_up_ll(long long x, long long m) { return (x + m - 1) / m * m; }
 

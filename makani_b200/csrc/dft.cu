@@ -71,7 +71,7 @@ constexpr int kRows = 16;   // flat positions per CTA tile
 template <typename T>
 __global__ void __launch_bounds__(256)
 dft_fwd_generic_kernel(const T* __restrict__ x, float* __restrict__ xm, const float2* __restrict__ tw,
-                       const float* __restrict__ mscale, int B, int C, int K, int Kp, int W, int M, int round_out) {
+                       const float* __restrict__ mscale, int B, int C, int K, int Kp, int W, int M, int round_out, long long xbs) {
   extern __shared__ float sm[];
   const int Cp = (C + 3) & ~3;
   const long long RS = 2LL * B * Cp;
@@ -88,7 +88,7 @@ dft_fwd_generic_kernel(const T* __restrict__ x, float* __restrict__ xm, const fl
     const int f = f0 + r;
     const int c = f / Kp, lat = f % Kp;
     const bool valid = (f < flat) && (lat < K);
-    const T* row = x + ((long long)(b * C + c) * K + lat) * W;
+    const T* row = x + b * xbs + ((long long)c * K + lat) * W;
     for (int w = threadIdx.x; w < W; w += blockDim.x) xs[r * (W + 1) + w] = valid ? to_f32<T>(row[w]) : 0.f;
   }
   __syncthreads();
@@ -124,7 +124,7 @@ dft_fwd_generic_kernel(const T* __restrict__ x, float* __restrict__ xm, const fl
 template <typename T>
 __global__ void __launch_bounds__(256)
 dft_inv_generic_kernel(const float* __restrict__ xm, T* __restrict__ y, const float2* __restrict__ tw,
-                       const float* __restrict__ mscale, int B, int C, int K, int Kp, int W, int M, int m_valid) {
+                       const float* __restrict__ mscale, int B, int C, int K, int Kp, int W, int M, int m_valid, long long xbs) {
   extern __shared__ float sm[];
   const int Cp = (C + 3) & ~3;
   const long long RS = 2LL * B * Cp;
@@ -150,7 +150,7 @@ dft_inv_generic_kernel(const float* __restrict__ xm, T* __restrict__ y, const fl
     const int f = f0 + r;
     const int c = f / Kp, lat = f % Kp;
     if (f >= flat || lat >= K) continue;
-    T* row = y + ((long long)(b * C + c) * K + lat) * W;
+    T* row = y + b * xbs + ((long long)c * K + lat) * W;
     for (int w = threadIdx.x; w < W; w += blockDim.x) {
       float acc = 0.f;
       int t = 0;
@@ -279,7 +279,7 @@ __device__ __forceinline__ void store_pair(T* row, int n, int r, fl::cf z) {
 template <int R, typename T>
 __global__ void __launch_bounds__(256, 2)
 dft_fwd_fft480_kernel(const T* __restrict__ x, float* __restrict__ xm, const fl::cf* __restrict__ tables,
-                      const float* __restrict__ mscale, int B, int C, int K, int Kp, int M, int round_out) {
+                      const float* __restrict__ mscale, int B, int C, int K, int Kp, int M, int round_out, long long xbs) {
   using S = FftSmem<R, T>;
   constexpr int W = S::W;
   extern __shared__ __align__(16) uint8_t smraw[];
@@ -312,7 +312,7 @@ dft_fwd_fft480_kernel(const T* __restrict__ x, float* __restrict__ xm, const fl:
     if (threadIdx.x < kRows) {
       const int f = f0 + threadIdx.x;
       const int c = f / Kp, lat = f - c * Kp;
-      rowoff[threadIdx.x] = (f < flat && lat < K) ? ((long long)(b * C + c) * K + lat) * W : -1;
+      rowoff[threadIdx.x] = (f < flat && lat < K) ? b * xbs + ((long long)c * K + lat) * W : -1;
     }
     __syncthreads();
     // ---- 1. rows -> smem (coalesced 16 B async copies); padded / out-of-range rows are zero filled
@@ -364,7 +364,7 @@ dft_fwd_fft480_kernel(const T* __restrict__ x, float* __restrict__ xm, const fl:
 template <int R, typename T>
 __global__ void __launch_bounds__(256, 2)
 dft_inv_fft480_kernel(const float* __restrict__ xm, T* __restrict__ y, const fl::cf* __restrict__ tables,
-                      const float* __restrict__ mscale, int B, int C, int K, int Kp, int M, int m_valid) {
+                      const float* __restrict__ mscale, int B, int C, int K, int Kp, int M, int m_valid, long long xbs) {
   using S = FftSmem<R, T>;
   constexpr int W = S::W;
   extern __shared__ __align__(16) uint8_t smraw[];
@@ -397,7 +397,7 @@ dft_inv_fft480_kernel(const float* __restrict__ xm, T* __restrict__ y, const fl:
     if (threadIdx.x < kRows) {
       const int f = f0 + threadIdx.x;
       const int c = f / Kp, lat = f - c * Kp;
-      rowoff[threadIdx.x] = (f < flat && lat < K) ? ((long long)(b * C + c) * K + lat) * W : -1;
+      rowoff[threadIdx.x] = (f < flat && lat < K) ? b * xbs + ((long long)c * K + lat) * W : -1;
     }
     // ---- 1. XM -> stage[reim][m][16 latitudes]: 16 B async copies, all in flight at once
     const long long ibase = ((long long)(b * 2) * Cp) * Kp + f0;
@@ -441,58 +441,49 @@ dft_inv_fft480_kernel(const float* __restrict__ xm, T* __restrict__ y, const fl:
 }
 
 // ------------------------------------------------------------------ host dispatch
-static int sm_count() {
-  static int n = 0;
-  if (!n) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
-    if (n <= 0) n = 148;
-  }
-  return n;
-}
+static int sm_count() { return sm_count_current_device(); }
 
 }  // namespace sfno
 #include "dft_p2.cuh"
 namespace sfno {
 
 template <int R, typename T>
-static int launch_fwd_fft(const void* x, int B, int C, int K, int Kp, int M, const float* mscale, float* xm,
+static int launch_fwd_fft(const void* x, int B, int C, int Ctot, int K, int Kp, int M, const float* mscale, float* xm,
                           int round_out, cudaStream_t stream) {
   using S = FftSmem<R, T>;
   const fl::cf* tables;
   if (get_fft_tables(&tables)) return 1;
-  static bool attr = false;
-  if (!attr) {
+  static PerDeviceOnce attr;
+  if (attr.needed()) {
     SFNO_CUDA(cudaFuncSetAttribute(dft_fwd_fft480_kernel<R, T>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kBytes));
-    attr = true;
+    attr.mark();
   }
   const int ntiles = ((C * Kp + kRows - 1) / kRows) * B;
   const int grid = std::min(ntiles, 2 * sm_count());
-  dft_fwd_fft480_kernel<R, T><<<grid, 256, S::kBytes, stream>>>(static_cast<const T*>(x), xm, tables, mscale, B, C, K, Kp, M, round_out);
+  dft_fwd_fft480_kernel<R, T><<<grid, 256, S::kBytes, stream>>>(static_cast<const T*>(x), xm, tables, mscale, B, C, K, Kp, M, round_out, (long long)Ctot * K * S::W);
   SFNO_LAUNCHED();
   return 0;
 }
 template <int R, typename T>
-static int launch_inv_fft(const float* xm, int B, int C, int K, int Kp, int M, int m_valid, const float* mscale,
+static int launch_inv_fft(const float* xm, int B, int C, int Ctot, int K, int Kp, int M, int m_valid, const float* mscale,
                           void* y, cudaStream_t stream) {
   using S = FftSmem<R, T>;
   const fl::cf* tables;
   if (get_fft_tables(&tables)) return 1;
-  static bool attr = false;
-  if (!attr) {
+  static PerDeviceOnce attr;
+  if (attr.needed()) {
     SFNO_CUDA(cudaFuncSetAttribute(dft_inv_fft480_kernel<R, T>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kBytes));
-    attr = true;
+    attr.mark();
   }
   const int ntiles = ((C * Kp + kRows - 1) / kRows) * B;
   const int grid = std::min(ntiles, 2 * sm_count());
-  dft_inv_fft480_kernel<R, T><<<grid, 256, S::kBytes, stream>>>(xm, static_cast<T*>(y), tables, mscale, B, C, K, Kp, M, m_valid);
+  dft_inv_fft480_kernel<R, T><<<grid, 256, S::kBytes, stream>>>(xm, static_cast<T*>(y), tables, mscale, B, C, K, Kp, M, m_valid, (long long)Ctot * K * S::W);
   SFNO_LAUNCHED();
   return 0;
 }
 
 template <typename T>
-static int launch_fwd_generic(const void* x, int B, int C, int K, int Kp, int W, int M, const float* mscale, float* xm,
+static int launch_fwd_generic(const void* x, int B, int C, int Ctot, int K, int Kp, int W, int M, const float* mscale, float* xm,
                               int round_out, cudaStream_t stream) {
   const float2* tw;
   if (get_twiddles(W, &tw)) return 1;
@@ -500,12 +491,12 @@ static int launch_fwd_generic(const void* x, int B, int C, int K, int Kp, int W,
   SFNO_CHECK(smem <= 200 * 1024, "generic DFT: nlon too large for the shared-memory kernel");
   SFNO_CUDA(cudaFuncSetAttribute(dft_fwd_generic_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
   const int ntiles = ((C * Kp + kRows - 1) / kRows) * B;
-  dft_fwd_generic_kernel<T><<<ntiles, 256, smem, stream>>>(static_cast<const T*>(x), xm, tw, mscale, B, C, K, Kp, W, M, round_out);
+  dft_fwd_generic_kernel<T><<<ntiles, 256, smem, stream>>>(static_cast<const T*>(x), xm, tw, mscale, B, C, K, Kp, W, M, round_out, (long long)Ctot * K * W);
   SFNO_LAUNCHED();
   return 0;
 }
 template <typename T>
-static int launch_inv_generic(const float* xm, int B, int C, int K, int Kp, int W, int M, int m_valid,
+static int launch_inv_generic(const float* xm, int B, int C, int Ctot, int K, int Kp, int W, int M, int m_valid,
                               const float* mscale, void* y, cudaStream_t stream) {
   const float2* tw;
   if (get_twiddles(W, &tw)) return 1;
@@ -513,7 +504,7 @@ static int launch_inv_generic(const float* xm, int B, int C, int K, int Kp, int 
   SFNO_CHECK(smem <= 200 * 1024, "generic inverse DFT: sizes too large for the shared-memory kernel");
   SFNO_CUDA(cudaFuncSetAttribute(dft_inv_generic_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
   const int ntiles = ((C * Kp + kRows - 1) / kRows) * B;
-  dft_inv_generic_kernel<T><<<ntiles, 256, smem, stream>>>(xm, static_cast<T*>(y), tw, mscale, B, C, K, Kp, W, M, m_valid);
+  dft_inv_generic_kernel<T><<<ntiles, 256, smem, stream>>>(xm, static_cast<T*>(y), tw, mscale, B, C, K, Kp, W, M, m_valid, (long long)Ctot * K * W);
   SFNO_LAUNCHED();
   return 0;
 }
@@ -534,19 +525,20 @@ static bool use_fft480(int W, int M, const void* p) {
   return (W == 480 || W == 1440) && M <= 241 && (reinterpret_cast<uintptr_t>(p) & 15) == 0;
 }
 
-int dft_fwd(const void* x, int x_dtype, int B, int C, int nlat, int nlon, int mmax, const float* mscale,
+int dft_fwd(const void* x, int x_dtype, int B, int C, int Ctot, int nlat, int nlon, int mmax, const float* mscale,
             float* xm, int round_out, cudaStream_t stream) {
   SFNO_CHECK(mmax <= nlon / 2 + 1, "mmax exceeds nlon/2+1");
+  SFNO_CHECK(Ctot >= C, "channel window larger than the field");
   const int Kp = round_up(nlat, 4);
   const bool fast = use_fft480(nlon, mmax, x);
   const bool lane_fft = use_lane_fft();
 #define SFNO_DISPATCH_FWD(T)                                                                           \
   do {                                                                                                 \
-    if (fast && lane_fft && nlon == 480) return launch_fwd_fft<1, T>(x, B, C, nlat, Kp, mmax, mscale, xm, round_out, stream); \
-    if (fast && lane_fft && nlon == 1440) return launch_fwd_fft<3, T>(x, B, C, nlat, Kp, mmax, mscale, xm, round_out, stream);\
-    if (fast && nlon == 480) return launch_fwd_p2<1, T>(x, B, C, nlat, Kp, mmax, mscale, xm, round_out, stream); \
-    if (fast && nlon == 1440) return launch_fwd_p2<3, T>(x, B, C, nlat, Kp, mmax, mscale, xm, round_out, stream);\
-    return launch_fwd_generic<T>(x, B, C, nlat, Kp, nlon, mmax, mscale, xm, round_out, stream);                   \
+    if (fast && lane_fft && nlon == 480) return launch_fwd_fft<1, T>(x, B, C, Ctot, nlat, Kp, mmax, mscale, xm, round_out, stream); \
+    if (fast && lane_fft && nlon == 1440) return launch_fwd_fft<3, T>(x, B, C, Ctot, nlat, Kp, mmax, mscale, xm, round_out, stream);\
+    if (fast && nlon == 480) return launch_fwd_p2<1, T>(x, B, C, Ctot, nlat, Kp, mmax, mscale, xm, round_out, stream); \
+    if (fast && nlon == 1440) return launch_fwd_p2<3, T>(x, B, C, Ctot, nlat, Kp, mmax, mscale, xm, round_out, stream);\
+    return launch_fwd_generic<T>(x, B, C, Ctot, nlat, Kp, nlon, mmax, mscale, xm, round_out, stream);                   \
   } while (0)
   switch (x_dtype) {
     case SFNO_F32: SFNO_DISPATCH_FWD(float);
@@ -557,20 +549,21 @@ int dft_fwd(const void* x, int x_dtype, int B, int C, int nlat, int nlon, int mm
 #undef SFNO_DISPATCH_FWD
 }
 
-int dft_inv(const float* xm, int B, int C, int nlat, int nlon, int mmax, int m_valid, const float* mscale,
+int dft_inv(const float* xm, int B, int C, int Ctot, int nlat, int nlon, int mmax, int m_valid, const float* mscale,
             void* y, int y_dtype, cudaStream_t stream) {
   SFNO_CHECK(mmax <= nlon / 2 + 1, "mmax exceeds nlon/2+1");
+  SFNO_CHECK(Ctot >= C, "channel window larger than the field");
   const int Kp = round_up(nlat, 4);
   m_valid = std::min(m_valid, mmax);
   const bool fast = use_fft480(nlon, mmax, y);
   const bool lane_fft = use_lane_fft();
 #define SFNO_DISPATCH_INV(T)                                                                                    \
   do {                                                                                                          \
-    if (fast && lane_fft && nlon == 480) return launch_inv_fft<1, T>(xm, B, C, nlat, Kp, mmax, m_valid, mscale, y, stream); \
-    if (fast && lane_fft && nlon == 1440) return launch_inv_fft<3, T>(xm, B, C, nlat, Kp, mmax, m_valid, mscale, y, stream);\
-    if (fast && nlon == 480) return launch_inv_p2<1, T>(xm, B, C, nlat, Kp, mmax, m_valid, mscale, y, stream); \
-    if (fast && nlon == 1440) return launch_inv_p2<3, T>(xm, B, C, nlat, Kp, mmax, m_valid, mscale, y, stream);\
-    return launch_inv_generic<T>(xm, B, C, nlat, Kp, nlon, mmax, m_valid, mscale, y, stream);                   \
+    if (fast && lane_fft && nlon == 480) return launch_inv_fft<1, T>(xm, B, C, Ctot, nlat, Kp, mmax, m_valid, mscale, y, stream); \
+    if (fast && lane_fft && nlon == 1440) return launch_inv_fft<3, T>(xm, B, C, Ctot, nlat, Kp, mmax, m_valid, mscale, y, stream);\
+    if (fast && nlon == 480) return launch_inv_p2<1, T>(xm, B, C, Ctot, nlat, Kp, mmax, m_valid, mscale, y, stream); \
+    if (fast && nlon == 1440) return launch_inv_p2<3, T>(xm, B, C, Ctot, nlat, Kp, mmax, m_valid, mscale, y, stream);\
+    return launch_inv_generic<T>(xm, B, C, Ctot, nlat, Kp, nlon, mmax, m_valid, mscale, y, stream);                   \
   } while (0)
   switch (y_dtype) {
     case SFNO_F32: SFNO_DISPATCH_INV(float);
@@ -599,8 +592,8 @@ int dft_fwd_peer(const void* x, int x_dtype, int B, int C, int nlat_loc, int nlo
   const int pitch = round_up(nlat_loc, 16);
 #define SFNO_DISPATCH_FWD_PEER(T)                                                                                   \
   do {                                                                                                              \
-    if (nlon == 480) return launch_fwd_p2_maps<1, T, PeerMaps>(x, B, C, nlat_loc, pitch, mmax, mscale, pm, round_out, stream); \
-    return launch_fwd_p2_maps<3, T, PeerMaps>(x, B, C, nlat_loc, pitch, mmax, mscale, pm, round_out, stream);       \
+    if (nlon == 480) return launch_fwd_p2_maps<1, T, PeerMaps>(x, B, C, C, nlat_loc, pitch, mmax, mscale, pm, round_out, stream); \
+    return launch_fwd_p2_maps<3, T, PeerMaps>(x, B, C, C, nlat_loc, pitch, mmax, mscale, pm, round_out, stream);       \
   } while (0)
   switch (x_dtype) {
     case SFNO_F32: SFNO_DISPATCH_FWD_PEER(float);
@@ -623,8 +616,8 @@ int dft_inv_peer(void* const* xm_ch, const int* chan_shapes, int nranks, int Kg,
   const int pitch = round_up(nlat_loc, 16);
 #define SFNO_DISPATCH_INV_PEER(T)                                                                                   \
   do {                                                                                                              \
-    if (nlon == 480) return launch_inv_p2_maps<1, T, PeerMaps>(pm, B, C, nlat_loc, pitch, m_valid, mscale, y, stream); \
-    return launch_inv_p2_maps<3, T, PeerMaps>(pm, B, C, nlat_loc, pitch, m_valid, mscale, y, stream);               \
+    if (nlon == 480) return launch_inv_p2_maps<1, T, PeerMaps>(pm, B, C, C, nlat_loc, pitch, m_valid, mscale, y, stream); \
+    return launch_inv_p2_maps<3, T, PeerMaps>(pm, B, C, C, nlat_loc, pitch, m_valid, mscale, y, stream);               \
   } while (0)
   switch (y_dtype) {
     case SFNO_F32: SFNO_DISPATCH_INV_PEER(float);

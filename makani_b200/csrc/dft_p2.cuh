@@ -18,13 +18,13 @@ struct DeviceWarp16p {
   __device__ __forceinline__ void sync() const { __syncwarp(); }
 };
 
-__device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
-  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-               ::"r"(smem_u32(smem_dst)), "l"(gsrc), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+__device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar, uint64_t policy) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
+               ::"r"(smem_u32(smem_dst)), "l"(gsrc), "r"(bytes), "r"(smem_u32(bar)), "l"(policy) : "memory");
 }
-__device__ __forceinline__ void bulk_s2g(void* gdst, const void* smem_src, uint32_t bytes) {
-  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
-               ::"l"(gdst), "r"(smem_u32(smem_src)), "r"(bytes) : "memory");
+__device__ __forceinline__ void bulk_s2g(void* gdst, const void* smem_src, uint32_t bytes, uint64_t policy) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group.L2::cache_hint [%0], [%1], %2, %3;"
+               ::"l"(gdst), "r"(smem_u32(smem_src)), "r"(bytes), "l"(policy) : "memory");
 }
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
@@ -40,9 +40,11 @@ constexpr int kPlaneFloats = 248 * 16;                     // 15872 B: planes st
 constexpr int kStageTileBytes = 2 * kPlaneFloats * 4;      // 31744 >= 16 rows x 240 complex (30720)
 __device__ __forceinline__ int stage_idx(int m, int r) { return m * 16 + ((((r >> 2) ^ (m >> 1)) & 3) << 2) + (r & 3); }
 
-__device__ __forceinline__ void tma_store_3d(const CUtensorMap* m, const void* smem_src, int c0, int c1, int c2) {
-  asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
-               ::"l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2) : "memory");
+__device__ __forceinline__ void tma_store_3d(const CUtensorMap* m, const void* smem_src, int c0, int c1, int c2,
+                                             uint64_t policy) {
+  asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group.L2::cache_hint [%0, {%2, %3, %4}], [%1], %5;"
+               ::"l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2), "l"(policy)
+               : "memory");
 }
 
 __device__ __forceinline__ void tma_store_4d(const CUtensorMap* m, const void* smem_src, int c0, int c1, int c2, int c3) {
@@ -73,9 +75,11 @@ template <>
 struct XmTile<LocalMap> {
   static constexpr bool kDist = false;
   __device__ static void prefetch(const LocalMap& m) { tma_prefetch_desc(&m.map); }
-  __device__ static void store(const LocalMap& m, const void* src, int f0, int, int j) { tma_store_3d(&m.map, src, f0, j, 0); }
-  __device__ static void load(const LocalMap& m, void* dst, uint64_t* bar, int f0, int, int j) {
-    tma_load_3d(dst, &m.map, bar, f0, j, 0);
+  __device__ static void store(const LocalMap& m, const void* src, int f0, int, int j, uint64_t pol) {
+    tma_store_3d(&m.map, src, f0, j, 0, pol);
+  }
+  __device__ static void load(const LocalMap& m, void* dst, uint64_t* bar, int f0, int, int j, uint64_t pol) {
+    tma_load_3d_hint(dst, &m.map, bar, f0, j, 0, pol);
   }
 };
 template <>
@@ -89,11 +93,11 @@ struct XmTile<PeerMaps> {
     while (p + 1 < m.n && c >= m.c0[p + 1]) ++p;
     return p;
   }
-  __device__ static void store(const PeerMaps& m, const void* src, int f0, int pitch, int j) {
+  __device__ static void store(const PeerMaps& m, const void* src, int f0, int pitch, int j, uint64_t) {
     const int c = f0 / pitch, p = owner(m, c);
     tma_store_4d(&m.map[p], src, f0 - c * pitch, c - m.c0[p], j, 0);
   }
-  __device__ static void load(const PeerMaps& m, void* dst, uint64_t* bar, int f0, int pitch, int j) {
+  __device__ static void load(const PeerMaps& m, void* dst, uint64_t* bar, int f0, int pitch, int j, uint64_t) {
     const int c = f0 / pitch, p = owner(m, c);
     tma_load_4d(dst, &m.map[p], bar, f0 - c * pitch, c - m.c0[p], j, 0);
   }
@@ -162,7 +166,7 @@ template <int R, typename T, int NBUF, bool ROUND, int OCC, class MAPS>
 __global__ void __launch_bounds__(256, OCC)
 dft_fwd_p2_kernel(const T* __restrict__ x, const __grid_constant__ MAPS xm_map,
                   const fl::cf* __restrict__ tables, const float* __restrict__ mscale, int B, int C, int K, int Kp,
-                  int M, int* __restrict__ sched) {
+                  int M, int* __restrict__ sched, long long xbs, unsigned long long pol_x, unsigned long long pol_xm) {
   using S = P2FwdSmem<R, T, NBUF>;
   constexpr int W = S::W;
   // 1024-byte aligned base, computed as an OFFSET from the shared array so that every access below stays in the
@@ -215,7 +219,7 @@ dft_fwd_p2_kernel(const T* __restrict__ x, const __grid_constant__ MAPS xm_map,
     const unsigned mask = __ballot_sync(0xffffffffu, valid);
     if (wl == 0) mbar_arrive_expect_tx(&full[buf], (uint32_t)__popc(mask) * S::kRowBytes);
     __syncwarp();
-    if (valid) bulk_g2s(dst, x + ((long long)(b * C + c) * K + lat) * W, S::kRowBytes, &full[buf]);
+    if (valid) bulk_g2s(dst, x + b * xbs + ((long long)c * K + lat) * W, S::kRowBytes, &full[buf], pol_x);
   };
 
   // tiles are claimed from a global counter (a CTA that starts late - SMs shared with NCCL kernels - just takes fewer);
@@ -283,8 +287,8 @@ dft_fwd_p2_kernel(const T* __restrict__ x, const __grid_constant__ MAPS xm_map,
     // ---- staging tile -> XM: one tensor store per plane (16 latitudes x 241 bins; bins >= M and positions beyond
     //      C*Kp are clipped by the tensor map)
     if (tid == 0) {
-      XmTile<MAPS>::store(xm_map, stage, f0, Kp, 2 * b);
-      XmTile<MAPS>::store(xm_map, stage + kPlaneFloats, f0, Kp, 2 * b + 1);
+      XmTile<MAPS>::store(xm_map, stage, f0, Kp, 2 * b, pol_xm);
+      XmTile<MAPS>::store(xm_map, stage + kPlaneFloats, f0, Kp, 2 * b + 1, pol_xm);
       bulk_commit();
     }
   }
@@ -332,7 +336,8 @@ struct P2InvDepth {
 template <int R, typename T, int NST, class MAPS>
 __global__ void __launch_bounds__(256, P2InvSmem<R, T, NST>::kCtasPerSm)
 dft_inv_p2_kernel(const __grid_constant__ MAPS xm_map, T* __restrict__ y, const fl::cf* __restrict__ tables,
-                  const float* __restrict__ mscale, int B, int C, int K, int Kp, int m_valid, int* __restrict__ sched) {
+                  const float* __restrict__ mscale, int B, int C, int K, int Kp, int m_valid, int* __restrict__ sched,
+                  long long xbs, unsigned long long pol_y, unsigned long long pol_xm) {
   using S = P2InvSmem<R, T, NST>;
   constexpr int W = S::W;
   extern __shared__ __align__(1024) uint8_t smp2[];
@@ -384,8 +389,8 @@ dft_inv_p2_kernel(const __grid_constant__ MAPS xm_map, T* __restrict__ y, const 
     const int b = t / tiles_per_b;
     const int f0 = (t - b * tiles_per_b) * kRows;
     mbar_arrive_expect_tx(full + buf, 2u * 241u * 64u);
-    XmTile<MAPS>::load(xm_map, dst, full + buf, f0, Kp, 2 * b);
-    XmTile<MAPS>::load(xm_map, dst + kPlaneFloats, full + buf, f0, Kp, 2 * b + 1);
+    XmTile<MAPS>::load(xm_map, dst, full + buf, f0, Kp, 2 * b, pol_xm);
+    XmTile<MAPS>::load(xm_map, dst + kPlaneFloats, full + buf, f0, Kp, 2 * b + 1, pol_xm);
   };
   if (tid == 0) {
     for (int j = 0; j < NST; ++j) claim(j, j);
@@ -431,7 +436,7 @@ dft_inv_p2_kernel(const __grid_constant__ MAPS xm_map, T* __restrict__ y, const 
     if (lane == 0) {
       const int f = f0 + r;
       const int c = f / Kp, lat = f - c * Kp;
-      if (f < flat && lat < K) bulk_s2g(y + ((long long)(b * C + c) * K + lat) * W, myrow, S::kRowBytes);
+      if (f < flat && lat < K) bulk_s2g(y + b * xbs + ((long long)c * K + lat) * W, myrow, S::kRowBytes, pol_y);
       bulk_commit();
     }
   }
@@ -457,8 +462,8 @@ static int p2_prepare(Kern kern, int smem_bytes) {
 // maps: LocalMap (XM tensor of this GPU, pitch = Kp) or PeerMaps (channel-sharded XM_ch buffers of all ranks,
 // pitch = round_up(K, 16): tiles never straddle two channels there)
 template <int R, typename T, class MAPS>
-static int launch_fwd_p2_maps(const void* x, int B, int C, int K, int pitch, int M, const float* mscale, const MAPS& maps,
-                              int round_out, cudaStream_t stream) {
+static int launch_fwd_p2_maps(const void* x, int B, int C, int Ctot, int K, int pitch, int M, const float* mscale,
+                              const MAPS& maps, int round_out, cudaStream_t stream) {
   // 16-bit rows at R = 3: a single row buffer lets two CTAs share an SM (16 warps instead of 8)
   constexpr int NBUF = (R == 3 && sizeof(T) == 2) ? 1 : 2;
   using S = P2FwdSmem<R, T, NBUF>;
@@ -466,63 +471,70 @@ static int launch_fwd_p2_maps(const void* x, int B, int C, int K, int pitch, int
   constexpr int OCC = S::kCtasPerSm;
   const fl::cf* tables;
   if (get_p2_tables(&tables)) return 1;
-  static bool attr = false;
-  if (!attr) {
+  static PerDeviceOnce attr;
+  if (attr.needed()) {
     SFNO_CUDA(cudaFuncSetAttribute(dft_fwd_p2_kernel<R, T, NBUF, true, OCC, MAPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kBytes));
     SFNO_CUDA(cudaFuncSetAttribute(dft_fwd_p2_kernel<R, T, NBUF, false, OCC, MAPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kBytes));
-    attr = true;
+    attr.mark();
   }
   const int ntiles = ((C * pitch + kRows - 1) / kRows) * B;
   const int grid = std::min(ntiles, OCC * sm_count());
   int* sched = sched_counters();
   SFNO_CHECK(sched != nullptr, "could not allocate the tile scheduler counters");
+  // channel window (Ctot > C): the field rows stream through L2, the XM window is meant to stay there
+  const bool win = Ctot != C && window_hints();
+  const unsigned long long pol_x = win ? kL2EvictFirst : kL2EvictNormal, pol_xm = win ? kL2EvictLast : kL2EvictNormal;
+  const long long xbs = (long long)Ctot * K * S::W;
   if (round_out)
     SFNO_CUDA(launch_pdl(dft_fwd_p2_kernel<R, T, NBUF, true, OCC, MAPS>, dim3(grid), dim3(256), S::kBytes, stream,
-                         static_cast<const T*>(x), maps, tables, mscale, B, C, K, pitch, M, sched));
+                         static_cast<const T*>(x), maps, tables, mscale, B, C, K, pitch, M, sched, xbs, pol_x, pol_xm));
   else
     SFNO_CUDA(launch_pdl(dft_fwd_p2_kernel<R, T, NBUF, false, OCC, MAPS>, dim3(grid), dim3(256), S::kBytes, stream,
-                         static_cast<const T*>(x), maps, tables, mscale, B, C, K, pitch, M, sched));
+                         static_cast<const T*>(x), maps, tables, mscale, B, C, K, pitch, M, sched, xbs, pol_x, pol_xm));
   SFNO_LAUNCHED();
   return 0;
 }
 
 template <int R, typename T>
-static int launch_fwd_p2(const void* x, int B, int C, int K, int Kp, int M, const float* mscale, float* xm,
+static int launch_fwd_p2(const void* x, int B, int C, int Ctot, int K, int Kp, int M, const float* mscale, float* xm,
                          int round_out, cudaStream_t stream) {
   LocalMap lm;
   if (xm_stage_map(&lm.map, xm, B, C, Kp, M)) return 1;
-  return launch_fwd_p2_maps<R, T, LocalMap>(x, B, C, K, Kp, M, mscale, lm, round_out, stream);
+  return launch_fwd_p2_maps<R, T, LocalMap>(x, B, C, Ctot, K, Kp, M, mscale, lm, round_out, stream);
 }
 
 template <int R, typename T, class MAPS>
-static int launch_inv_p2_maps(const MAPS& maps, int B, int C, int K, int pitch, int m_valid, const float* mscale,
+static int launch_inv_p2_maps(const MAPS& maps, int B, int C, int Ctot, int K, int pitch, int m_valid, const float* mscale,
                               void* y, cudaStream_t stream) {
   constexpr int NST = P2InvDepth<R, T>::value;
   using S = P2InvSmem<R, T, NST>;
   static_assert(S::kBytes <= 227 * 1024, "inverse DFT tile does not fit shared memory");
   const fl::cf* tables;
   if (get_p2_tables(&tables)) return 1;
-  static bool attr = false;
-  if (!attr) {
+  static PerDeviceOnce attr;
+  if (attr.needed()) {
     if (p2_prepare(dft_inv_p2_kernel<R, T, NST, MAPS>, S::kBytes)) return 1;
-    attr = true;
+    attr.mark();
   }
   const int ntiles = ((C * pitch + kRows - 1) / kRows) * B;
   const int grid = std::min(ntiles, S::kCtasPerSm * sm_count());
   int* sched = sched_counters();
   SFNO_CHECK(sched != nullptr, "could not allocate the tile scheduler counters");
+  const bool win = Ctot != C && window_hints();
+  const unsigned long long pol_y = win ? kL2EvictFirst : kL2EvictNormal, pol_xm = win ? kL2EvictLast : kL2EvictNormal;
   SFNO_CUDA(launch_pdl(dft_inv_p2_kernel<R, T, NST, MAPS>, dim3(grid), dim3(256), S::kBytes, stream, maps,
-                       static_cast<T*>(y), tables, mscale, B, C, K, pitch, m_valid, sched));
+                       static_cast<T*>(y), tables, mscale, B, C, K, pitch, m_valid, sched,
+                       (long long)Ctot * K * S::W, pol_y, pol_xm));
   SFNO_LAUNCHED();
   return 0;
 }
 
 template <int R, typename T>
-static int launch_inv_p2(const float* xm, int B, int C, int K, int Kp, int M, int m_valid, const float* mscale,
+static int launch_inv_p2(const float* xm, int B, int C, int Ctot, int K, int Kp, int M, int m_valid, const float* mscale,
                          void* y, cudaStream_t stream) {
   LocalMap lm;
   if (xm_stage_map(&lm.map, xm, B, C, Kp, std::max(1, std::min(M, m_valid)))) return 1;
-  return launch_inv_p2_maps<R, T, LocalMap>(lm, B, C, K, Kp, std::min(M, m_valid), mscale, y, stream);
+  return launch_inv_p2_maps<R, T, LocalMap>(lm, B, C, Ctot, K, Kp, std::min(M, m_valid), mscale, y, stream);
 }
 
 // channel-sharded XM_ch buffers of all ranks as seen from this rank's latitude slab (see PeerMaps)

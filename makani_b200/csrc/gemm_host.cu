@@ -122,16 +122,18 @@ static int get_tiles(const TileKey& key, const std::function<void(std::vector<Ge
   return 0;
 }
 
-static int num_sms() {
-  static int n = 0;
+int sm_count_current_device() {
+  static std::atomic<int> cache[64];
+  const int dev = PerDeviceOnce::device();
+  int n = cache[dev].load(std::memory_order_relaxed);
   if (!n) {
-    int dev = 0;
-    cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
     if (n <= 0) n = 148;
+    cache[dev].store(n, std::memory_order_relaxed);
   }
   return n;
 }
+static int num_sms() { return sm_count_current_device(); }
 
 // SFNO_L2_HINTS=1 enables L2 eviction-priority hints (keep SP resident between producer and consumer kernels).
 // Measured on B200: no gain (14.25 vs 14.20 ms/step), so they are off by default.
@@ -140,6 +142,17 @@ static bool l2_hints() {
   if (v < 0) {
     const char* env = getenv("SFNO_L2_HINTS");
     v = (env && env[0] == '1') ? 1 : 0;
+  }
+  return v == 1;
+}
+// Channel-window mode (XM produced and consumed window by window through a small re-used buffer): keep the window and
+// the Legendre table in L2 (evict_last), let the field rows stream (evict_first).  SFNO_WINDOW_HINTS=0 turns the
+// hints off for A/B measurements.
+bool window_hints() {
+  static int v = -1;
+  if (v < 0) {
+    const char* env = getenv("SFNO_WINDOW_HINTS");
+    v = (env && env[0] == '0') ? 0 : 1;
   }
   return v == 1;
 }
@@ -186,11 +199,11 @@ static int launch(const CUtensorMap& ma, const CUtensorMap& mb, GemmArgs args, c
   SFNO_CHECK(args.sched != nullptr, "could not allocate the tile scheduler counters");
   SFNO_CHECK(args.out_col_stride > 0 && args.out_col_stride < (1LL << 31) / 32,
              "output column stride too large for the 32-bit epilogue addressing (reduce batch*channels)");
-  static bool attr_set = false;
-  if (!attr_set) {
+  static PerDeviceOnce attr_set;
+  if (attr_set.needed()) {
     SFNO_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                    Cfg::kSmemBytes));
-    attr_set = true;
+    attr_set.mark();
   }
   int grid = std::min(args.num_tiles, num_sms());
   SFNO_CUDA(launch_pdl(gemm_tc_kernel<MODE>, dim3(grid), dim3(kGemmThreads), Cfg::kSmemBytes, stream, ma, mb, args));
@@ -205,10 +218,22 @@ static int current_device() {
 }
 
 // ------------------------------------------------------------------ Legendre analysis  (K2)
-int legendre_analysis(const sfno_plan* plan, const float* xm, int B, int C, float* sp, int round_out,
-                      cudaStream_t stream) {
+// Channel window: XM holds channels [c0, c0 + C) of a field with Ctot channels (compact: [M][2B][round_up(C,4)][Kp]);
+// SP is the full tensor over Ctot channels.  Ctot == C, c0 == 0: no window.
+static int window_ok(int C, int Ctot, int c0) {
+  if (Ctot == C && c0 == 0) return 0;
+  SFNO_CHECK(c0 >= 0 && c0 + C <= Ctot && C % 32 == 0 && c0 % 4 == 0,
+             "channel window: needs 0 <= c0, c0 + C <= Ctot, C % 32 == 0, c0 % 4 == 0");
+  return 0;
+}
+
+int legendre_analysis(const sfno_plan* plan, const float* xm, int B, int C, int Ctot, int c0, float* sp, int round_out,
+                      int accumulate, cudaStream_t stream) {
   const int K = plan->nlat, Kp = plan->Kp, L = plan->lmax, M = plan->mmax, moff = plan->m_offset;
-  const int RS = 2 * B * round_up(C, 4);
+  const int RS = 2 * B * round_up(C, 4);                 // rows of the XM operand (the window)
+  const int RSt = 2 * B * round_up(Ctot, 4);             // rows of SP
+  if (window_ok(C, Ctot, c0)) return 1;
+  const bool win = !(Ctot == C && c0 == 0);
   CUtensorMap ma, mb;
   {
     uint64_t dims[3] = {(uint64_t)K, (uint64_t)RS, (uint64_t)M};
@@ -242,18 +267,30 @@ int legendre_analysis(const sfno_plan* plan, const float* xm, int B, int C, floa
   args.tiles = tl.dev;
   args.num_tiles = tl.count;
   args.row_limit = RS;
-  args.out_g_stride = RS;                       // SP[l][m][r]: g = m
-  args.out_col_stride = (long long)M * RS;      // column = l
+  args.out_g_stride = RSt;                      // SP[l][m][r]: g = m
+  args.out_col_stride = (long long)M * RSt;     // column = l
   args.out_im_offset = 0;
   args.round_out = round_out;
+  args.accumulate = accumulate;
+  args.grp_rows = win ? round_up(C, 4) : 0;
+  args.grp_stride = round_up(Ctot, 4);
+  args.grp_off = c0;
   set_policies(args, false, false, true, true, false, false);     // XM streams through, SP stays for the channel contraction
+  if (win && window_hints()) {                  // the XM window and the table are re-used from L2 (see window_hints)
+    args.pol_a = kL2EvictLast;
+    args.pol_b = kL2EvictLast;
+  }
   return launch<LEG_ANA>(ma, mb, args, stream);
 }
 
 // ------------------------------------------------------------------ Legendre synthesis  (K4)
-int legendre_synthesis(const sfno_plan* plan, const float* sp, int B, int C, float* xm, cudaStream_t stream) {
+int legendre_synthesis(const sfno_plan* plan, const float* sp, int B, int C, int Ctot, int c0, float* xm,
+                       cudaStream_t stream) {
   const int K = plan->nlat, Kp = plan->Kp, L = plan->lmax, M = plan->mmax, moff = plan->m_offset;
-  const int RS = 2 * B * round_up(C, 4);
+  const int RS = 2 * B * round_up(C, 4);                 // rows of the XM result (the window)
+  const int RSt = 2 * B * round_up(Ctot, 4);             // rows of SP
+  if (window_ok(C, Ctot, c0)) return 1;
+  const bool win = !(Ctot == C && c0 == 0);
   CUtensorMap ma, mb;
   {
     uint64_t dims[3] = {(uint64_t)K, (uint64_t)L, (uint64_t)M};
@@ -262,8 +299,8 @@ int legendre_synthesis(const sfno_plan* plan, const float* sp, int B, int C, flo
     if (encode_tensor_map(&ma, plan->table, 3, dims, str, box, 2)) return 1;
   }
   {
-    uint64_t dims[3] = {(uint64_t)RS, (uint64_t)M, (uint64_t)L};
-    uint64_t str[2] = {(uint64_t)RS * 4, (uint64_t)M * RS * 4};
+    uint64_t dims[3] = {(uint64_t)RSt, (uint64_t)M, (uint64_t)L};
+    uint64_t str[2] = {(uint64_t)RSt * 4, (uint64_t)M * RSt * 4};
     uint32_t box[3] = {32, 1, 32};
     if (encode_tensor_map(&mb, sp, 3, dims, str, box, 2)) return 1;
   }
@@ -292,7 +329,15 @@ int legendre_synthesis(const sfno_plan* plan, const float* sp, int B, int C, flo
   args.out_col_stride = Kp;                     // column = r
   args.out_im_offset = 0;
   args.round_out = 0;                           // consumed by the fp32 inverse DFT
+  args.accumulate = 0;
+  args.grp_rows = win ? round_up(C, 4) : 0;
+  args.grp_stride = round_up(Ctot, 4);
+  args.grp_off = c0;
   set_policies(args, false, false, false, false, true, true);     // SP is consumed here; XM (178 MB) cannot stay in L2
+  if (win && window_hints()) {                  // the table is re-read by every window, the XM window is consumed from L2
+    args.pol_a = kL2EvictLast;
+    args.pol_out = kL2EvictLast;
+  }
   return launch<LEG_SYN>(ma, mb, args, stream);
 }
 
@@ -351,6 +396,7 @@ int dhconv_fwd(const float* sp_in, const float* wp, float* sp_out, int B, int Ci
   args.out_col_stride = 2 * Coutp;              // column = n = m*B + b
   args.out_im_offset = Coutp;
   args.round_out = round_out;
+  args.accumulate = args.grp_rows = args.grp_stride = args.grp_off = 0;
   set_policies(args, false, false, true, true, false, false);     // weights stream, the result feeds the synthesis
   return launch<DH_FWD>(ma, mb, args, stream);
 }
@@ -385,6 +431,7 @@ int dhconv_bwd_x(const float* gsp_out, const float* wp, float* gsp_in, int B, in
   args.out_col_stride = 2 * Cinp;
   args.out_im_offset = Cinp;
   args.round_out = round_out;
+  args.accumulate = args.grp_rows = args.grp_stride = args.grp_off = 0;
   set_policies(args, false, false, true, true, false, false);
   return launch<DH_BWDX>(ma, mb, args, stream);
 }
@@ -419,6 +466,7 @@ int dhconv_bwd_w(const float* sp_in, const float* gsp_out, float* gwp, int B, in
   args.out_col_stride = Cinp;
   args.out_im_offset = (long long)Coutp * Cinp;
   args.round_out = 0;
+  args.accumulate = args.grp_rows = args.grp_stride = args.grp_off = 0;
   set_policies(args, false, true, false, true, false, true);      // dY is read again by the dX contraction
   return launch<DH_BWDW>(ma, mb, args, stream);
 }

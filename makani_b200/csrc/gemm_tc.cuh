@@ -45,6 +45,12 @@ struct GemmArgs {
   int round_out;            // 1: store round-to-nearest TF32 values (the consumer is another TF32 GEMM)
   unsigned long long pol_a, pol_b, pol_out;   // L2 cache policies of the two operand streams and of the output
   int* sched;               // [0] next tile (dynamic scheduler), [1] finished CTAs; both zero at launch, reset by the last CTA
+  // Channel-window view (Legendre modes): the XM operand / result is a compact tensor over a WINDOW of `grp_rows`
+  // (padded) channels per (batch, re/im) group, while SP is the full tensor with `grp_stride` channels per group:
+  //   SP row (LEG_ANA output row / LEG_SYN B column)  =  (r / grp_rows) * grp_stride + grp_off + r % grp_rows
+  // grp_rows == 0: no window (r maps to itself).  LEG_SYN needs grp_rows % 32 == 0 (one TMA box never straddles groups).
+  int grp_rows, grp_stride, grp_off;
+  int accumulate;           // 1: add to what the output already holds (LEG_ANA: gradients of two consumers of one SP)
 };
 
 template <int MODE>
@@ -175,7 +181,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
               if constexpr (MODE == LEG_ANA) {               // table (k, l, m) K-major, 64-row boxes
                 tma_load_3d_hint(sb + j * 8192, &map_b, &full_bar[stage], kc, tile.col0 + 64 * j, tile.g, args.pol_b);
               } else if constexpr (MODE == LEG_SYN) {        // SP (r, m, l) MN-major, 32-col chunks
-                tma_load_3d_hint(sb + j * 4096, &map_b, &full_bar[stage], tile.col0 + 32 * j, tile.g, kc, args.pol_b);
+                int rcol = tile.col0 + 32 * j;
+                if (args.grp_rows) rcol = (rcol / args.grp_rows) * args.grp_stride + args.grp_off + rcol % args.grp_rows;
+                tma_load_3d_hint(sb + j * 4096, &map_b, &full_bar[stage], rcol, tile.g, kc, args.pol_b);
               } else if constexpr (MODE == DH_FWD || MODE == DH_BWDX) {   // SP (c, reim, n, l) K-major
                 tma_load_4d_hint(sb + j * 8192, &map_b, &full_bar[stage], kc, p, tile.col0 + 64 * j, tile.g, args.pol_b);
               } else {                                       // DH_BWDW: gSP_out (o, reim, n, l) MN-major in o
@@ -269,8 +277,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
       if (t < 0) break;
       const GemmTile tile = args.tiles[t];
       const int row = tile.row0 + q * 32 + lane;
-      const bool row_ok = row < args.row_limit;
-      float* obase = args.out + (long long)tile.g * args.out_g_stride + row;
+      bool row_ok = row < args.row_limit;
+      int orow = row;
+      if constexpr (MODE == LEG_ANA) {
+        if (args.grp_rows) orow = (row / args.grp_rows) * args.grp_stride + args.grp_off + row % args.grp_rows;
+      }
+      float* obase = args.out + (long long)tile.g * args.out_g_stride + orow;
       if (tile.nkk == 0) {
         for (int c = tile.col0; c < tile.col_limit; ++c) {
           if (row_ok) {
@@ -306,6 +318,18 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
             for (int j = 0; j < 32; ++j) w[j] = __uint_as_float(v[j]);
           }
           if (c + 32 < tile.n_mma) tmem_ld_32x32(tbase + p * 128 + c + 32, v);   // prefetch the next chunk
+          if constexpr (MODE == LEG_ANA) {
+            if (args.accumulate && row_ok) {
+              const int nv = nvalid - c;
+#pragma unroll
+              for (int j = 0; j < 32; ++j)
+                if (j < nv) w[j] += op[j * cstride];
+              if (args.round_out) {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) w[j] = tf32_rn(w[j]);
+              }
+            }
+          }
           if (row_ok) {
             const int nv = nvalid - c;
             if (nv >= 32) {

@@ -256,6 +256,19 @@ __global__ void add_bias_kernel(T* __restrict__ y, const float* __restrict__ bia
   }
 }
 
+// constant bias as the m = 0 Fourier coefficient: irfft(norm="forward") adds Re XM[0][b][c][k] to every longitude of
+// latitude k, so  y + bias[c]  ==  irfft(XM with XM[0].re += bias[c])  - the add happens in fp32 before the cast to the
+// output dtype, as the reference does (spectral_convolution.py:143-146), and costs B*C*nlat elements instead of a pass
+// over the field.
+__global__ void xm_add_dc_kernel(float* __restrict__ xm, const float* __restrict__ bias, int B, int C, int K, int Kp) {
+  const int Cp = (C + 3) & ~3;
+  const int n = B * C * K;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const int k = i % K, c = (i / K) % C, b = i / (K * C);
+    xm[((long long)(b * 2) * Cp + c) * Kp + k] += bias[c];
+  }
+}
+
 // ------------------------------------------------------------------ diagonal contraction (contractions.py:122-127)
 //   MODE 0: y[b,o,l,m]  = sum_i x[b,i,l,m] w[i,o,l,m]          (a = SP x,  out = SP y)
 //   MODE 1: dx[b,i,l,m] = sum_o g[b,o,l,m] conj(w[i,o,l,m])    (a = SP g,  out = SP dx)
@@ -533,6 +546,14 @@ int sfno_add_bias(void* y, int y_dtype, const float* bias, int bias_kind, int B,
     case SFNO_F16: add_bias_kernel<__half><<<grid, 256, 0, s>>>((__half*)y, bias, bias_kind, n, C, HW); break;
     default: SFNO_CHECK(false, "unsupported dtype");
   }
+  SFNO_LAUNCHED();
+  return 0;
+}
+
+int sfno_xm_add_dc(float* xm, int B, int C, int nlat, const float* bias, void* stream) {
+  SFNO_CHECK(xm && bias, "null argument");
+  const int n = B * C * nlat;
+  xm_add_dc_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(xm, bias, B, C, nlat, round_up(nlat, 4));
   SFNO_LAUNCHED();
   return 0;
 }

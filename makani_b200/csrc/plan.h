@@ -17,9 +17,13 @@ namespace sfno {
 int sp_mhi(int l_local, int l_offset, int m_offset, int M_local);
 int* sched_counters();   // {next tile, finished CTAs} pair for one launch of a dynamically scheduled kernel
 
-int legendre_analysis(const sfno_plan* plan, const float* xm, int B, int C, float* sp, int round_out,
-                      cudaStream_t stream);
-int legendre_synthesis(const sfno_plan* plan, const float* sp, int B, int C, float* xm, cudaStream_t stream);
+bool window_hints();     // L2 eviction hints of the channel-window mode (SFNO_WINDOW_HINTS=0 disables)
+
+// XM holds the channel window [c0, c0 + C) of Ctot channels; SP is the full tensor (Ctot == C, c0 == 0: no window)
+int legendre_analysis(const sfno_plan* plan, const float* xm, int B, int C, int Ctot, int c0, float* sp, int round_out,
+                      int accumulate, cudaStream_t stream);
+int legendre_synthesis(const sfno_plan* plan, const float* sp, int B, int C, int Ctot, int c0, float* xm,
+                       cudaStream_t stream);
 int dhconv_fwd(const float* sp_in, const float* wp, float* sp_out, int B, int Cin, int Cout, int L, int M,
                int l_offset, int m_offset, int round_out, cudaStream_t stream);
 int dhconv_bwd_x(const float* gsp_out, const float* wp, float* gsp_in, int B, int Cin, int Cout, int L, int M,
@@ -27,9 +31,10 @@ int dhconv_bwd_x(const float* gsp_out, const float* wp, float* gsp_in, int B, in
 int dhconv_bwd_w(const float* sp_in, const float* gsp_out, float* gwp, int B, int Cin, int Cout, int L, int M,
                  int l_offset, int m_offset, cudaStream_t stream);
 
-int dft_fwd(const void* x, int x_dtype, int B, int C, int nlat, int nlon, int mmax, const float* mscale,
+// x / y point at channel c0 of a field with Ctot channels per batch entry; C channels are transformed
+int dft_fwd(const void* x, int x_dtype, int B, int C, int Ctot, int nlat, int nlon, int mmax, const float* mscale,
             float* xm, int round_out, cudaStream_t stream);
-int dft_inv(const float* xm, int B, int C, int nlat, int nlon, int mmax, int m_valid, const float* mscale,
+int dft_inv(const float* xm, int B, int C, int Ctot, int nlat, int nlon, int mmax, int m_valid, const float* mscale,
             void* y, int y_dtype, cudaStream_t stream);
 
 bool dft_peer_supported(int nlon, int mmax);

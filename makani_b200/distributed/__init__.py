@@ -517,7 +517,7 @@ class _DistributedMixin:
         plans = self.__dict__.setdefault("_peer_plans", {})
         p = plans.get(idx)
         if p is None:
-            tab = self._table64()
+            tab = self._table_slice()[1]              # w == 1 on this path: the m-slab is the whole table
             kp = sum(_rup8(k) for k in self.lat_shapes)
             padded = np.zeros(tab.shape[:2] + (kp,), dtype=np.float64)
             src = dst = 0
@@ -531,7 +531,9 @@ class _DistributedMixin:
     def _table_slice(self):
         m0 = sum(self.m_shapes[: self.comm_rank_azimuth])
         m1 = m0 + self.m_shapes[self.comm_rank_azimuth]
-        return m0, np.ascontiguousarray(self._table64()[m0:m1])
+        if self.__dict__.get("_slab_registered", False):       # the registered buffer already is this rank's m-slab
+            return m0, self._host_table64()
+        return m0, np.ascontiguousarray(self._host_table64()[m0:m1])
 
     # local stages; tests replace these with the CPU oracle to exercise the choreography without a GPU
     def _dft_stage(self, x):
@@ -552,6 +554,7 @@ class DistributedRealSHT(_DistributedMixin, RealSHT):
         self._setup_shards()
         m0, tab = self._table_slice()
         self.register_buffer("weights", torch.from_numpy(tab), persistent=False)
+        self._slab_registered = True
 
     @annotate("DistributedRealSHT.forward")
     def forward(self, x: torch.Tensor) -> torch.Tensor:
@@ -584,6 +587,7 @@ class DistributedInverseRealSHT(_DistributedMixin, InverseRealSHT):
         self._setup_shards()
         m0, tab = self._table_slice()
         self.register_buffer("pct", torch.from_numpy(tab), persistent=False)
+        self._slab_registered = True
 
     @annotate("DistributedInverseRealSHT.forward")
     def forward(self, x: torch.Tensor) -> torch.Tensor:

@@ -149,6 +149,95 @@ def legendre_synthesis(plan: Plan, sp: torch.Tensor, B: int, Cn: int, out: torch
     return xm
 
 
+# ------------------------------------------------------------------------------------------ channel windows
+# The chain DFT -> Legendre (and Legendre -> inverse DFT) is independent per channel.  Run over WINDOWS of channels, with
+# the Fourier coefficients of one window going through a small buffer that every window re-uses, the intermediate XM
+# (178 MB at 240x480, 536 MB at 721x1440 for C = 384) stays in the 126 MB L2 instead of being written to HBM by one
+# kernel and read back by the next: this is the fusion across the RFFT -> Legendre and Legendre -> inverse-RFFT
+# boundaries of makani/models/common/spectral_convolution.py:131-141 (see include/makani_b200.h, "channel-window
+# variants").  MAKANI_B200_WINDOW_MB sets the size of the window buffer (default 60; 0 disables windows).
+import os as _os
+
+_WINDOW_MB = float(_os.environ.get("MAKANI_B200_WINDOW_MB", "60"))
+_WINDOW_BUFFERS = {}
+
+
+def window_channels(C: int, B: int, nlat: int, mmax: int) -> int:
+    """Channels per window (a multiple of 32), or C when the chain runs in one pass."""
+    if _WINDOW_MB <= 0 or C % 32 != 0:
+        return C
+    per_channel = mmax * 2 * B * _rup(nlat, 4) * 4
+    cc = int(_WINDOW_MB * 1e6 // per_channel) // 32 * 32
+    cc = max(32, cc)
+    return C if cc >= C else cc
+
+
+def _window_buffer(nfloats: int, device) -> torch.Tensor:
+    """One persistent XM window buffer per device (grown on demand): same addresses every time, so the lines it
+    occupies in L2 are simply overwritten by the next window."""
+    dev = torch.device(device)
+    buf = _WINDOW_BUFFERS.get(dev)
+    if buf is None or buf.numel() < nfloats:
+        if torch.cuda.is_current_stream_capturing():
+            raise RuntimeError("makani_b200: run one eager warm-up step before CUDA-graph capture (window buffer)")
+        buf = torch.empty(nfloats, dtype=torch.float32, device=dev)
+        _WINDOW_BUFFERS[dev] = buf
+    return buf[:nfloats]
+
+
+def sht_to_sp(plan: Plan, x: torch.Tensor, mscale: torch.Tensor, round_tf32: bool = False, out: torch.Tensor = None,
+              accumulate: bool = False) -> torch.Tensor:
+    """x [B, C, nlat, nlon] -> SP: longitude DFT (K1) + Legendre analysis (K2), window by window.
+    accumulate: add to `out` (the sum of the gradients of two consumers of one SP tensor)."""
+    _need_cuda(x, "x")
+    B, Cn, K, W = x.shape
+    x = x.contiguous()
+    M = plan.mmax
+    sp = out if out is not None else torch.empty(sp_elems(plan.lmax, M, B, Cn), dtype=torch.float32, device=x.device)
+    cc = window_channels(Cn, B, K, M)
+    if cc >= Cn:
+        xm = dft_fwd(x, M, mscale)
+        _ext.check(_ext.load().sfno_legendre_analysis_win(plan.handle, _ptr(xm), B, Cn, 0, Cn, _ptr(sp), int(round_tf32),
+                                                          int(accumulate), _stream()), "sfno_legendre_analysis_win")
+        return sp
+    lib, st, dt = _ext.load(), _stream(), dtype_code(x.dtype)
+    xm = _window_buffer(xm_elems(K, M, B, cc), x.device)
+    for c0 in range(0, Cn, cc):
+        c = min(cc, Cn - c0)
+        _ext.check(lib.sfno_dft_fwd_win(_ptr(x), dt, B, Cn, c0, c, K, W, M, _ptr(mscale), _ptr(xm), 1, st),
+                   "sfno_dft_fwd_win")
+        _ext.check(lib.sfno_legendre_analysis_win(plan.handle, _ptr(xm), B, Cn, c0, c, _ptr(sp), int(round_tf32),
+                                                  int(accumulate), st), "sfno_legendre_analysis_win")
+    return sp
+
+
+def sp_to_field(plan: Plan, sp: torch.Tensor, B: int, Cn: int, nlon: int, mscale: torch.Tensor, dtype: torch.dtype,
+                m_valid=None, dc_bias: torch.Tensor = None) -> torch.Tensor:
+    """SP -> y [B, C, nlat, nlon]: Legendre synthesis (K4) + inverse longitude DFT (K5), window by window.
+    dc_bias: fp32 [C], added to every point of channel c in fp32 (as the m = 0 coefficient; needs mscale[0] == 1)."""
+    K, M = plan.nlat, plan.mmax
+    mv = M if m_valid is None else m_valid
+    cc = window_channels(Cn, B, K, M)
+    if cc >= Cn:
+        xm = legendre_synthesis(plan, sp, B, Cn)
+        if dc_bias is not None:
+            _ext.check(_ext.load().sfno_xm_add_dc(_ptr(xm), B, Cn, K, _ptr(dc_bias), _stream()), "sfno_xm_add_dc")
+        return dft_inv(xm, B, Cn, K, nlon, M, mscale, dtype, m_valid)
+    lib, st, dt = _ext.load(), _stream(), dtype_code(dtype)
+    y = torch.empty((B, Cn, K, nlon), dtype=dtype, device=sp.device)
+    xm = _window_buffer(xm_elems(K, M, B, cc), sp.device)
+    for c0 in range(0, Cn, cc):
+        c = min(cc, Cn - c0)
+        _ext.check(lib.sfno_legendre_synthesis_win(plan.handle, _ptr(sp), B, Cn, c0, c, _ptr(xm), st),
+                   "sfno_legendre_synthesis_win")
+        if dc_bias is not None:
+            _ext.check(lib.sfno_xm_add_dc(_ptr(xm), B, c, K, C.c_void_p(dc_bias.data_ptr() + 4 * c0), st),
+                       "sfno_xm_add_dc")
+        _ext.check(lib.sfno_dft_inv_win(_ptr(xm), B, Cn, c0, c, K, nlon, M, mv, _ptr(mscale), _ptr(y), dt, st),
+                   "sfno_dft_inv_win")
+    return y
+
+
 # ------------------------------------------------------------------------------------------ layout
 def sp_to_c64(sp, B, Cn, lmax, mmax, l_offset=0, m_offset=0) -> torch.Tensor:
     out = torch.empty((B, Cn, lmax, mmax), dtype=torch.complex64, device=sp.device)

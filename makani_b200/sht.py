@@ -62,7 +62,30 @@ class _TransformBase(nn.Module):
 
     def _table_slice(self):
         """(m_offset, table64) actually held by this module (overridden by the azimuth-sharded variants)."""
-        return 0, self._table64()
+        return 0, self._host_table64()
+
+    def _host_table64(self) -> np.ndarray:
+        """The registered table buffer as fp64 numpy (exact: it is fp64, or the fp32 rounding `.float()` made of it -
+        which is what the device plan rounds to anyway)."""
+        buf = self._buffers.get(self._table_name)
+        if buf is None:
+            return self._table64()
+        return buf.detach().cpu().double().numpy()
+
+    def _apply(self, fn, *args, **kwargs):
+        # The table buffer (`weights` / `pct`: what torch-harmonics registers, non-persistent) follows dtype changes
+        # (`.float()`, as makani/models/networks/sfnonet.py:536-539 calls it) but stays in HOST memory when the module
+        # moves to a GPU: the kernels read the plan's own device copy (TF32-rounded, padded), and a second copy of the
+        # table (333 MB in fp64 at 721x1440) would be dead device memory.  Nothing in the reference reads the buffer.
+        name = self._table_name
+        tab = self._buffers.pop(name, None)
+        try:
+            super()._apply(fn, *args, **kwargs)
+        finally:
+            if tab is not None:
+                probe = fn(torch.empty(0, dtype=tab.dtype))
+                self._buffers[name] = tab.to(probe.dtype) if probe.dtype.is_floating_point else tab
+        return self
 
     def _plan(self, device: torch.device) -> ops.Plan:
         idx = device.index if device.index is not None else torch.cuda.current_device()
@@ -102,8 +125,7 @@ class _SHTFunction(torch.autograd.Function):
     def forward(ctx, x, mod):
         plan = mod._plan(x.device)
         B, Cn = x.shape[0], x.shape[1]
-        xm = ops.dft_fwd(x, mod.mmax, mod._scale(x.device, "fwd"))
-        sp = ops.legendre_analysis(plan, xm, B, Cn)
+        sp = ops.sht_to_sp(plan, x, mod._scale(x.device, "fwd"))
         ctx.mod, ctx.in_dtype = mod, x.dtype
         return ops.sp_to_c64(sp, B, Cn, mod.lmax, mod.mmax)
 
@@ -113,8 +135,7 @@ class _SHTFunction(torch.autograd.Function):
         plan = mod._plan(g.device)
         B, Cn = g.shape[0], g.shape[1]
         gsp = ops.c64_to_sp(g.to(torch.complex64))
-        gxm = ops.legendre_synthesis(plan, gsp, B, Cn)
-        gx = ops.dft_inv(gxm, B, Cn, mod.nlat, mod.nlon, mod.mmax, mod._scale(g.device, "rfft_adj"), ctx.in_dtype)
+        gx = ops.sp_to_field(plan, gsp, B, Cn, mod.nlon, mod._scale(g.device, "rfft_adj"), ctx.in_dtype)
         return gx, None
 
 
@@ -126,17 +147,15 @@ class _ISHTFunction(torch.autograd.Function):
         plan = mod._plan(c.device)
         B, Cn = c.shape[0], c.shape[1]
         sp = ops.c64_to_sp(c)
-        xm = ops.legendre_synthesis(plan, sp, B, Cn)
         ctx.mod = mod
-        return ops.dft_inv(xm, B, Cn, mod.nlat, mod.nlon, mod.mmax, mod._scale(c.device, "one"), torch.float32)
+        return ops.sp_to_field(plan, sp, B, Cn, mod.nlon, mod._scale(c.device, "one"), torch.float32)
 
     @staticmethod
     def backward(ctx, g):
         mod = ctx.mod
         plan = mod._plan(g.device)
         B, Cn = g.shape[0], g.shape[1]
-        gxm = ops.dft_fwd(g.contiguous(), mod.mmax, mod._scale(g.device, "irfft_adj"))
-        gsp = ops.legendre_analysis(plan, gxm, B, Cn)
+        gsp = ops.sht_to_sp(plan, g, mod._scale(g.device, "irfft_adj"))
         return ops.sp_to_c64(gsp, B, Cn, mod.lmax, mod.mmax), None
 
 
@@ -165,6 +184,8 @@ class RealSHT(_TransformBase):
 
 class InverseRealSHT(_TransformBase):
     """Inverse real spherical harmonic transform (synthesis)."""
+
+    _table_name = "pct"
 
     def __init__(self, nlat, nlon, lmax=None, mmax=None, grid="lobatto", norm="ortho", csphase=True):
         super().__init__(nlat, nlon, lmax, mmax, grid, norm, csphase)

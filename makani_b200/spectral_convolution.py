@@ -46,38 +46,46 @@ def _distributed_classes():
 
 
 class _SpectralConvFunction(torch.autograd.Function):
-    """(x, weight) -> (y, residual_or_None); single-device transforms only."""
+    """(x, weight, bias_or_None) -> (y, residual_or_None); single-device transforms only.
+
+    forward :  x -[DFT + Legendre analysis]-> SP -[channel contraction]-> SP' -[Legendre synthesis + inverse DFT]-> y
+    The two bracketed pairs run window by window over the channels (ops.sht_to_sp / ops.sp_to_field), so the Fourier
+    coefficients between the DFT and the Legendre contraction never leave L2.  A constant bias is added in fp32 as the
+    m = 0 Fourier coefficient, a position bias by one pass over y (spectral_convolution.py:143-146)."""
 
     @staticmethod
-    def forward(ctx, x, weight, mod):
+    def forward(ctx, x, weight, bias, mod):
         fwd, inv = mod.forward_transform, mod.inverse_transform
         dev = x.device
         B, Cin = x.shape[0], x.shape[1]
         Cout, L, M = mod.out_channels, mod.modes_lat, mod.modes_lon
         pf, pi = fwd._plan(dev), inv._plan(dev)
+        one = inv._scale(dev, "one")
 
-        xm = ops.dft_fwd(x, M, fwd._scale(dev, "fwd"))
-        sp = ops.legendre_analysis(pf, xm, B, Cin, round_tf32=True)
-        del xm
+        sp = ops.sht_to_sp(pf, x, fwd._scale(dev, "fwd"), round_tf32=True)
         residual = None
         if mod.scale_residual:
-            rxm = ops.legendre_synthesis(pi, sp, B, Cin)
-            residual = ops.dft_inv(rxm, B, Cin, inv.nlat, inv.nlon, M, inv._scale(dev, "one"), x.dtype)
-            del rxm
+            residual = ops.sp_to_field(pi, sp, B, Cin, inv.nlon, one, x.dtype)
         if mod.operator_type == "dhconv":
             wp = mod._packed_weight(weight)
             sp2 = ops.dhconv_fwd(sp, wp, B, Cin, Cout, L, M, round_tf32=True)
         else:
             wp = None
             sp2 = ops.diag_fwd(sp, weight, B, Cin, Cout, L, M)
-        xm2 = ops.legendre_synthesis(pi, sp2, B, Cout)
+        dc = None
+        if bias is not None and bias.numel() == Cout:
+            dc = bias.detach().reshape(Cout).to(torch.float32).contiguous()
+        y = ops.sp_to_field(pi, sp2, B, Cout, inv.nlon, one, x.dtype, dc_bias=dc)
         del sp2
-        y = ops.dft_inv(xm2, B, Cout, inv.nlat, inv.nlon, M, inv._scale(dev, "one"), x.dtype)
+        if bias is not None and dc is None:
+            ops.add_bias_(y, bias)
 
         ctx.mod = mod
         ctx.in_dtype = x.dtype
         ctx.shape = (B, Cin, Cout, L, M)
         ctx.has_residual = residual is not None
+        ctx.bias_shape = None if bias is None else tuple(bias.shape)
+        ctx.bias_dtype = None if bias is None else bias.dtype
         if wp is not None:
             ctx.save_for_backward(sp, wp)
         else:
@@ -97,9 +105,11 @@ class _SpectralConvFunction(torch.autograd.Function):
         adj = inv._scale(dev, "irfft_adj")
         unpack_done = None
 
-        gxm2 = ops.dft_fwd(gy.contiguous(), M, adj)
-        gsp2 = ops.legendre_analysis(pi, gxm2, B, Cout, round_tf32=True)
-        del gxm2
+        gbias = None
+        if ctx.bias_shape is not None and ctx.needs_input_grad[2]:
+            dims = (0, 2, 3) if ctx.bias_shape[-1] == 1 else (0,)
+            gbias = gy.sum(dim=dims, keepdim=True, dtype=torch.float32).to(ctx.bias_dtype).reshape(ctx.bias_shape)
+        gsp2 = ops.sht_to_sp(pi, gy, adj, round_tf32=True)
         gw = None
         if mod.operator_type == "dhconv":
             if ctx.needs_input_grad[1]:
@@ -126,14 +136,13 @@ class _SpectralConvFunction(torch.autograd.Function):
         gx = None
         if ctx.needs_input_grad[0]:
             if ctx.has_residual and gres is not None:
-                grxm = ops.dft_fwd(gres.contiguous(), M, adj)
-                gsp = gsp + ops.legendre_analysis(pi, grxm, B, Cin, round_tf32=True)     # both zero outside the defined region
-                del grxm
-            gxm = ops.legendre_synthesis(pf, gsp, B, Cin)
-            gx = ops.dft_inv(gxm, B, Cin, fwd.nlat, fwd.nlon, M, fwd._scale(dev, "rfft_adj"), ctx.in_dtype)
+                # gradient of the re-projected residual: accumulated into gsp by the analysis epilogue (both tensors
+                # are defined on the same band of SP; no separate add pass)
+                ops.sht_to_sp(pi, gres, adj, round_tf32=True, out=gsp, accumulate=True)
+            gx = ops.sp_to_field(pf, gsp, B, Cin, fwd.nlon, fwd._scale(dev, "rfft_adj"), ctx.in_dtype)
         if unpack_done is not None:
             torch.cuda.current_stream().wait_event(unpack_done)   # join: whatever consumes gw runs after the unpack
-        return gx, gw, None
+        return gx, gw, gbias, None
 
 
 class SpectralConv(nn.Module):
@@ -230,20 +239,32 @@ class SpectralConv(nn.Module):
 
         self._wp_cache = None     # (weight version, data_ptr, packed tensor)
 
-    # packed planar copy of the dhconv weight, refreshed when the parameter changes (optimizer step / load)
+    # Packed planar copy of the dhconv weight (the tensor-core GEMMs cannot read the checkpoint layout).
+    # While the weight is being trained (grad mode on and weight.requires_grad) it is re-packed on EVERY forward: an
+    # optimizer may update the parameter without touching its version counter (apex FusedLAMB / raw-pointer updates,
+    # `p.data.add_()`, EMA restores - all selectable in the reference, makani/utils/trainer.py:458-470), and a stale
+    # packed copy would silently freeze the filter.  In inference (no_grad / frozen weight) the copy is cached and
+    # keyed on (version, storage, device); call `invalidate()` after changing the weight behind autograd's back there.
     def _packed_weight(self, weight: torch.Tensor) -> torch.Tensor:
         key = (weight._version, weight.data_ptr(), weight.device)
         cache = self._wp_cache
-        if cache is not None and cache[0] == key and not torch.cuda.is_current_stream_capturing():
-            if len(cache) > 2 and cache[2] is not None:          # packed by prepack_async on the side stream
-                cur = torch.cuda.current_stream()
-                cur.wait_event(cache[2])
-                cache[1].record_stream(cur)
-                self._wp_cache = (key, cache[1])
+        training = torch.is_grad_enabled() and weight.requires_grad
+        if cache is not None and cache[0] == key and len(cache) > 2 and cache[2] is not None:
+            cur = torch.cuda.current_stream()                    # packed by prepack_async for exactly this forward
+            cur.wait_event(cache[2])
+            cache[1].record_stream(cur)
+            self._wp_cache = None if training else (key, cache[1])
+            return cache[1]
+        if (cache is not None and cache[0] == key and not training
+                and not torch.cuda.is_current_stream_capturing()):
             return cache[1]
         wp = ops.pack_weight(weight)
-        self._wp_cache = (key, wp)
+        self._wp_cache = None if training else (key, wp)
         return wp
+
+    def invalidate(self):
+        """Drop the cached packed weight (inference only; training re-packs every forward)."""
+        self._wp_cache = None
 
     def prepack_async(self):
         """Start re-packing the dhconv weight on the side stream; the next forward waits for it instead of packing on
@@ -273,13 +294,13 @@ class SpectralConv(nn.Module):
         ops._need_cuda(x, "SpectralConv input")
         ops.dtype_code(dtype)
         if self._fused_ok():
-            y, residual = _SpectralConvFunction.apply(x.contiguous(), self.weight, self)
+            y, residual = _SpectralConvFunction.apply(x.contiguous(), self.weight, getattr(self, "bias", None), self)
             if residual is None:
                 residual = x
         else:
             y, residual = self._forward_composed(x)
-        if hasattr(self, "bias"):
-            y = y + self.bias.to(y.dtype)
+            if hasattr(self, "bias"):
+                y = y + self.bias.to(y.dtype)
         return y, residual
 
     # distributed (or foreign) transforms: same arithmetic, stage by stage through the module API

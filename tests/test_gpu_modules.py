@@ -164,6 +164,65 @@ def test_state_dict_and_annotations(mk):
         mk.SpectralConv(fwd, inv, 4, 6, operator_type="nope")
 
 
+@pytest.mark.parametrize("case", ["internal", "down", "up"])
+def test_channel_windows_are_bit_identical_to_the_single_pass(mk, case, monkeypatch):
+    """The DFT <-> Legendre stages run window by window over the channels (ops.sht_to_sp / ops.sp_to_field) so that the
+    Fourier coefficients stay in L2.  Same kernels, same arithmetic per output element: output, re-projected residual,
+    dX, dW and the bias gradient must equal the single-pass path bit for bit (B = 2, three windows of 32 channels)."""
+    from makani_b200 import ops
+    gin, gout = {"internal": ((60, 480, "legendre-gauss"), (60, 480, "legendre-gauss")),
+                 "down": ((45, 1440, "equiangular"), (60, 480, "legendre-gauss")),
+                 "up": ((60, 480, "legendre-gauss"), (45, 1440, "equiangular"))}[case]
+    L, M, C, B = 40, 41, 96, 2
+    torch.manual_seed(11)
+    fwd = mk.RealSHT(gin[0], gin[1], lmax=L, mmax=M, grid=gin[2]).to(DEV)
+    inv = mk.InverseRealSHT(gout[0], gout[1], lmax=L, mmax=M, grid=gout[2]).to(DEV)
+    conv = mk.SpectralConv(fwd, inv, C, C, operator_type="dhconv", bias="constant").to(DEV)
+    with torch.no_grad():
+        conv.bias.normal_()
+    x = torch.randn(B, C, gin[0], gin[1], device=DEV).to(torch.bfloat16).requires_grad_(True)
+    gy = torch.randn(B, C, gout[0], gout[1], device=DEV).to(torch.bfloat16)
+
+    def run(window_mb):
+        monkeypatch.setattr(ops, "_WINDOW_MB", window_mb)
+        x.grad = conv.weight.grad = conv.bias.grad = None
+        y, res = conv(x)
+        outs, gs = ([y, res], [gy, gy]) if conv.scale_residual else ([y], [gy])
+        torch.autograd.backward(outs, gs)
+        return [t.detach().clone() for t in (y, res, x.grad, torch.view_as_real(conv.weight.grad), conv.bias.grad)]
+
+    ref = run(0.0)
+    assert ops.window_channels(C, B, gin[0], M) == C
+    per_channel_mb = M * 2 * B * ((max(gin[0], gout[0]) + 3) // 4 * 4) * 4 / 1e6
+    win = run(33 * per_channel_mb)                                   # room for 33 channels -> windows of 32
+    assert ops.window_channels(C, B, max(gin[0], gout[0]), M) == 32
+    for name, a, b in zip(["y", "residual", "dx", "dw", "dbias"], ref, win):
+        assert torch.equal(a, b), name
+
+
+def test_weight_update_behind_the_version_counter_is_seen(mk):
+    """Optimizers that write through raw pointers or `.data` (apex FusedLAMB, selectable at makani/utils/trainer.py:458-470)
+    do not bump `weight._version`; the packed copy of the dhconv weight must not go stale.  Training: re-packed every
+    forward.  Inference: cached, `invalidate()` is the documented contract."""
+    torch.manual_seed(5)
+    fwd = mk.RealSHT(16, 32, grid="legendre-gauss").to(DEV)
+    inv = mk.InverseRealSHT(16, 32, grid="legendre-gauss").to(DEV)
+    conv = mk.SpectralConv(fwd, inv, 4, 4, operator_type="dhconv").to(DEV)
+    x = torch.randn(1, 4, 16, 32, device=DEV)
+    y0, _ = conv(x)
+    v0 = conv.weight._version
+    conv.weight.data.mul_(2.0)                               # in place behind autograd: version unchanged
+    assert conv.weight._version == v0
+    y1, _ = conv(x)
+    assert O.rel_l2(y1.detach().cpu(), 2.0 * y0.detach().cpu()) < 1e-5
+    with torch.no_grad():
+        y2, _ = conv(x)                                      # fills the inference cache
+        conv.weight.data.mul_(0.5)
+        conv.invalidate()
+        y3, _ = conv(x)
+    assert O.rel_l2(y2.cpu(), y1.detach().cpu()) < 1e-6 and O.rel_l2(y3.cpu(), y0.detach().cpu()) < 1e-5
+
+
 # ---------------------------------------------------------------- full BASELINE sizes: properties only
 def test_full_size_roundtrip_and_linearity_internal_grid(mk):
     torch.manual_seed(3)

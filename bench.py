@@ -1,19 +1,24 @@
 #!/usr/bin/env python
-"""bench.py - SFNO spectral hot path on B200 (contract: see the task statement / DESIGN.md section "Measurement").
+"""bench.py - SFNO spectral hot path on B200 (contract: the task statement / DESIGN.md section 7 "Measurement").
 
-Workload (BASELINE.json configs[1], `sfno_linear_73chq_sc3_layers8_edim384_asgl2`, batch 1 per GPU, bf16 AMP):
-the eight SpectralConv blocks of the model, forward + backward (dX and dW), chained as they are inside the model
-(the batch enters block 0 at 721x1440, each block's output is the next block's input, the gradient enters at block 7;
-`--inputs independent` gives every block its own synthetic input instead), with the shapes/dtypes of the model:
-    block 0      RealSHT(721x1440 equiangular) -> dhconv(384->384, L=240, M=241) -> InverseRealSHT(240x480 Gauss)
-                 + residual re-projection to 240x480
-    blocks 1..6  240x480 Gauss in and out
-    block 7      240x480 in -> 721x1440 equiangular out (+ residual re-projection to 721x1440)
-Spatial tensors are bf16 (what autocast hands the module), spectral arithmetic is TF32 tensor-core
-contractions with fp32 accumulation and fp32 FFTs (the reference runs this path in fp32 with TF32 allowed).
+Workload (BASELINE.json configs[1], `sfno_linear_73chq_sc3_layers8_edim384_asgl2`, batch 1 per GPU, bf16 AMP): the eight
+SpectralConv blocks of the model, forward + backward (dX and dW), chained as they are inside the model - see
+tools/benchlib/workload.py.  Spatial tensors are bf16 (what autocast hands the module), spectral arithmetic is TF32
+tensor-core contractions with fp32 accumulation and fp32 FFTs (the reference runs this path in fp32 with TF32 allowed).
 
-One JSON line on stdout (rank 0).  `--impl reference` times the reference-equivalent torch CPU path
-(oracle/sht_oracle.py - the reference itself cannot be imported: torch-harmonics / modulus are absent).
+One JSON line on stdout (rank 0):
+  value / ms_per_step   device-resident step, CUDA events, max over ranks
+  e2e                   the same step fed from pinned host memory every step (+ checksum read back)
+  roofline              dominant kernel family (live CUDA events) + `block` (one internal block forward against SURVEY
+                        8(d)'s algorithmic bytes) + `step` + `traffic_ratio` (ncu DRAM bytes / algorithmic bytes)
+  gpu_baseline          the reference-equivalent torch path (cuFFT + cuBLAS einsums, TF32 allowed) on the same GPU
+  cpu_baseline          the oracle port on the host cores, bounded sample (N = 1 only)
+  rollout               BASELINE config 5: 40 chained forward passes, eager and CUDA-graph replay (N = 1 only)
+  config3               BASELINE config 3: global batch 8 split over the N GPUs
+  parity / spatial      N >= 2: h-sharded transforms + SpectralConv against the fp64 oracle (exit code != 0 on mismatch)
+                        and BASELINE config 4 timings (tools/benchlib/spatial.py)
+`--impl reference` runs the SAME step through the oracle port on the host cores (the reference itself cannot be
+imported: torch-harmonics / modulus are absent) - whole steps, nothing extrapolated.
 """
 import argparse
 import json
@@ -21,105 +26,17 @@ import os
 import subprocess
 import sys
 import tempfile
-import threading
 import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tools"))
 
 import torch  # noqa: E402
 
-C_EMBED, L_MODES, M_MODES = 384, 240, 241
-GRID_IN = (721, 1440, "equiangular")
-GRID_INT = (240, 480, "legendre-gauss")
-METRIC = "SFNO spectral path (8x SHT+SpectralConv+ISHT, fwd+bwd) samples/s"
-WORKLOAD = "sfno_linear_73chq_sc3_layers8_edim384_asgl2: 8 SpectralConv blocks fwd+bwd, batch 1/GPU, bf16 I/O"
-
-
-def block_specs():
-    """(in_grid, out_grid) of the eight blocks (sfnonet.py:392-393, 536-539)."""
-    return [(GRID_IN, GRID_INT)] + [(GRID_INT, GRID_INT)] * 6 + [(GRID_INT, GRID_IN)]
-
-
-# ------------------------------------------------------------------------------------------------ GPU arm
-def build_gpu(dev, dtype, seed=0):
-    import makani_b200 as mk
-    torch.manual_seed(seed)
-    sht_in = mk.RealSHT(*GRID_IN[:2], lmax=L_MODES, mmax=M_MODES, grid=GRID_IN[2]).to(dev)
-    sht_int = mk.RealSHT(*GRID_INT[:2], lmax=L_MODES, mmax=M_MODES, grid=GRID_INT[2]).to(dev)
-    isht_int = mk.InverseRealSHT(*GRID_INT[:2], lmax=L_MODES, mmax=M_MODES, grid=GRID_INT[2]).to(dev)
-    isht_out = mk.InverseRealSHT(*GRID_IN[:2], lmax=L_MODES, mmax=M_MODES, grid=GRID_IN[2]).to(dev)
-    blocks = []
-    for gin, gout in block_specs():
-        f = sht_in if gin is GRID_IN else sht_int
-        i = isht_out if gout is GRID_IN else isht_int
-        blocks.append(mk.SpectralConv(f, i, C_EMBED, C_EMBED, operator_type="dhconv").to(dev))
-    return blocks
-
-
-def make_inputs(batch, dtype, pinned, chained=False):
-    g = torch.Generator().manual_seed(1)
-    xs = []
-    for gin, _ in block_specs()[:1 if chained else None]:
-        x = torch.rand(batch, C_EMBED, gin[0], gin[1], generator=g, dtype=torch.float32).to(dtype)
-        xs.append(x.pin_memory() if pinned else x)
-    return xs
-
-
-def make_grads(batch, dtype, dev, chained=False):
-    """Per block: (gradient of y, gradient of the re-projected residual or None).  Chained blocks get their output
-    gradient from the next block, so only the last block's `gy` is materialised there."""
-    g = torch.Generator().manual_seed(2)
-    gs = []
-    specs = block_specs()
-    for i, (gin, gout) in enumerate(specs):
-        rescale = (gin is not gout)
-        if chained and i < len(specs) - 1 and not rescale:
-            gs.append((None, None))
-            continue
-        gy = (torch.rand(batch, C_EMBED, gout[0], gout[1], generator=g) - 0.5).to(dtype).to(dev)
-        gs.append((gy, gy.clone() if rescale else None))
-    return gs
-
-
-def gpu_step(blocks, xs_dev, grads):
-    """One pass of the hot path: every block forward + backward.  Returns a tiny checksum tensor."""
-    sums = []
-    for blk, x, (gy, gr) in zip(blocks, xs_dev, grads):
-        x.grad = None
-        blk.weight.grad = None
-        y, res = blk(x)
-        if gr is not None:
-            torch.autograd.backward([y, res], [gy, gr])
-        else:
-            torch.autograd.backward([y], [gy])
-        sums.append(y[0, 0, 0, :8].float().sum())
-    return torch.stack(sums)
-
-
-def gpu_step_chained(blocks, x0, grads):
-    """One pass of the hot path as it runs inside the model (sfnonet.py:239-267 without the pointwise layers between
-    the filters): the batch enters block 0, every block's output is the next block's input, and ONE backward pass
-    carries the output gradient of block 7 (and the gradients of the two re-projected residuals) back to `x0`
-    and to every weight.  Same kernels and launch count as `gpu_step`.  Returns a tiny checksum tensor."""
-    x0.grad = None
-    outs, gouts = [], []
-    x = x0
-    prepack = os.environ.get("MAKANI_B200_OVERLAP_WEIGHTS", "0") == "1"
-    if prepack:                        # opt-in A/B: all eight re-packs start on the side stream right away
-        for blk in blocks:
-            blk.prepack_async()
-    for blk, (gy, gr) in zip(blocks, grads):
-        blk.weight.grad = None
-        y, res = blk(x)
-        if gr is not None:
-            outs.append(res)
-            gouts.append(gr)
-        x = y
-    outs.append(x)
-    gouts.append(grads[-1][0])
-    torch.autograd.backward(outs, gouts)
-    return torch.stack([x[0, 0, 0, :8].float().sum(), x0.grad[0, 0, 0, :8].float().sum()])
+from benchlib import workload as W  # noqa: E402
+from benchlib.workload import (C_EMBED, GRID_IN, GRID_INT, L_MODES, M_MODES, METRIC, WORKLOAD,  # noqa: E402,F401
+                               block_specs, build_gpu, gpu_step, gpu_step_chained, make_grads, make_inputs)
 
 
 class ClockSampler:
@@ -169,101 +86,23 @@ class ClockSampler:
         return out
 
 
-# ------------------------------------------------------------------------------------------------ roofline
-def alg_bytes(name, a):
-    """Algorithmic HBM bytes of one launch (what the op must move; fp32 internal tensors, dense table, the
-    l >= m half of spectral tensors) - formulas documented in DESIGN.md section "Kernels"."""
-    tri = lambda L, M: sum(min(l + 1, M) for l in range(L))           # noqa: E731  number of (l, m <= l) pairs
-    if name == "dft_fwd":
-        return a["B"] * a["C"] * a["K"] * (a["W"] * a["esize"] + a["M"] * 8)
-    if name == "dft_inv":
-        return a["B"] * a["C"] * a["K"] * (a["W"] * a["esize"] + a["M"] * 8)
-    if name in ("legendre_analysis", "legendre_synthesis"):
-        return a["B"] * a["C"] * 8 * (a["K"] * a["M"] + tri(a["L"], a["M"])) + 4 * a["M"] * a["L"] * a["K"]
-    if name in ("dhconv_fwd", "dhconv_bwd_x"):
-        return 8 * a["B"] * (a["Cin"] + a["Cout"]) * tri(a["L"], a["M"]) + 8 * a["Cin"] * a["Cout"] * a["L"]
-    if name == "dhconv_bwd_w":
-        return 8 * a["B"] * (a["Cin"] + a["Cout"]) * tri(a["L"], a["M"]) + 8 * a["Cin"] * a["Cout"] * a["L"]
-    if name in ("pack_weight", "unpack_wgrad"):
-        return 16 * a["Cin"] * a["Cout"] * a["L"]
-    return 0
-
-
-class KernelProfiler:
-    """Wraps makani_b200.ops entry points with CUDA events (on the launching stream) for one profiling pass."""
-
-    def __init__(self):
-        from makani_b200 import ops
-        self.ops = ops
-        self.records = []
-        self.saved = {}
-
-    def _wrap(self, name, fn, describe):
-        def inner(*args, **kw):
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record()
-            out = fn(*args, **kw)
-            e1.record()
-            self.records.append((name, describe(*args, **kw), e0, e1))
-            return out
-        return inner
-
-    def __enter__(self):
-        o = self.ops
-        es = lambda t: t.element_size()                                # noqa: E731
-        desc = {
-            "dft_fwd": lambda x, M, s, **kw: dict(B=x.shape[0], C=x.shape[1], K=x.shape[2], W=x.shape[3], M=M, esize=es(x)),
-            "dft_inv": lambda xm, B, C, K, W, M, s, dt, m_valid=None: dict(B=B, C=C, K=K, W=W, M=M,
-                                                                          esize=torch.empty(0, dtype=dt).element_size()),
-            "legendre_analysis": lambda p, xm, B, C, **kw: dict(B=B, C=C, K=p.nlat, L=p.lmax, M=p.mmax),
-            "legendre_synthesis": lambda p, sp, B, C, **kw: dict(B=B, C=C, K=p.nlat, L=p.lmax, M=p.mmax),
-            "dhconv_fwd": lambda s, w, B, Ci, Co, L, M, *r, **kw: dict(B=B, Cin=Ci, Cout=Co, L=L, M=M),
-            "dhconv_bwd_x": lambda s, w, B, Ci, Co, L, M, *r, **kw: dict(B=B, Cin=Ci, Cout=Co, L=L, M=M),
-            "dhconv_bwd_w": lambda s, g, B, Ci, Co, L, M, *r, **kw: dict(B=B, Cin=Ci, Cout=Co, L=L, M=M),
-            "pack_weight": lambda w: dict(Cin=w.shape[0], Cout=w.shape[1], L=w.shape[2]),
-            "unpack_wgrad": lambda g, Ci, Co, L: dict(Cin=Ci, Cout=Co, L=L),
-        }
-        for name, d in desc.items():
-            self.saved[name] = getattr(o, name)
-            setattr(o, name, self._wrap(name, self.saved[name], d))
-        return self
-
-    def __exit__(self, *exc):
-        for name, fn in self.saved.items():
-            setattr(self.ops, name, fn)
-
-    def summary(self):
-        torch.cuda.synchronize()
-        agg = {}
-        for name, a, e0, e1 in self.records:
-            key = (name, tuple(sorted(a.items())))
-            t = agg.setdefault(key, dict(name=name, args=a, ms=0.0, n=0))
-            t["ms"] += e0.elapsed_time(e1)
-            t["n"] += 1
-        rows = []
-        for t in agg.values():
-            avg_ms = t["ms"] / t["n"]
-            b = alg_bytes(t["name"], t["args"])
-            rows.append(dict(kernel=t["name"], shape=t["args"], launches=t["n"], avg_us=avg_ms * 1e3,
-                             total_ms=t["ms"], alg_bytes=b, gbs=b / (avg_ms * 1e-3) / 1e9 if avg_ms > 0 else 0.0))
-        rows.sort(key=lambda r: -r["total_ms"])
-        return rows
-
-
-def ncu_traffic(kernel, shape):
-    """DRAM bytes per launch of `kernel` from the committed ncu --set full capture (profiles/ncu_traffic.json,
-    built by tools/ncu_traffic.py); None when that kernel / shape was not captured."""
+def ncu_traffic():
+    """profiles/ncu_traffic.json: DRAM bytes per kernel family and for one internal block forward, from the committed
+    ncu capture (tools/ncu_traffic.py); {} when absent."""
     try:
         with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
-            t = json.load(f)
+            return json.load(f)
     except Exception:
-        return None
+        return {}
+
+
+def kernel_traffic(table, kernel, shape):
     key = kernel
     if kernel.startswith("dft_"):
         key = f"{kernel}_{shape.get('W')}"
     elif kernel.startswith("legendre_"):
         key = f"{kernel}_{shape.get('K')}"
-    e = t.get(key)
+    e = table.get(key)
     return float(e["bytes"]) if e else None
 
 
@@ -276,59 +115,96 @@ def measured_peaks():
         return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def base_config(world, batch):
+    return {"workload": WORKLOAD, "per_gpu_batch": batch, "embed_dim": C_EMBED, "modes": [L_MODES, M_MODES],
+            "io_dtype": "bf16", "accumulate": "fp32", "parallelism": f"dp{world}",
+            "inputs": "chained: block i+1 reads block i's output, one backward pass from block 7 to the input",
+            "includes": "fwd + dX + dW of all 8 blocks, weight repack every step; no optimizer update"}
+
+
 # ------------------------------------------------------------------------------------------------ CPU arm
-def cpu_reference_sample(threads):
-    """Reference-equivalent torch CPU path (fp32, the oracle port) on a bounded sample of the workload:
-    ONE internal block (240x480, C=384, B=1) forward + backward.  Returns seconds."""
-    from oracle import sht_oracle as O
-    torch.set_num_threads(threads)
-    if not hasattr(cpu_reference_sample, "state"):
-        torch.manual_seed(0)
-        fwd = O.RealSHT(*GRID_INT[:2], lmax=L_MODES, mmax=M_MODES, grid=GRID_INT[2], dtype=torch.float32)
-        inv = O.InverseRealSHT(*GRID_INT[:2], lmax=L_MODES, mmax=M_MODES, grid=GRID_INT[2], dtype=torch.float32)
-        w = O.init_spectral_weight(C_EMBED, C_EMBED, L_MODES, operator_type="dhconv").requires_grad_(True)
-        x = torch.rand(1, C_EMBED, GRID_INT[0], GRID_INT[1]).requires_grad_(True)
-        g = torch.rand(1, C_EMBED, GRID_INT[0], GRID_INT[1]) - 0.5
-        cpu_reference_sample.state = (fwd, inv, w, x, g)
-    fwd, inv, w, x, g = cpu_reference_sample.state
-    x.grad = None
-    w.grad = None
-    t0 = time.perf_counter()
-    y, _ = O.spectral_conv_forward(x, fwd, inv, w, "dhconv", compute_dtype=torch.float32)
-    torch.autograd.backward([y], [g])
-    return time.perf_counter() - t0
-
-
-# An internal block moves/computes 1 unit; the two resolution-changing blocks are heavier.  Work ratio used to
-# scale the one-block CPU sample to a whole step (8 blocks): Legendre + FFT cost scale with nlat*nlon of the big
-# side; measured with this same oracle on the build container (8 threads): internal 2.55 s, block 0 6.76 s (2.65x),
-# block 7 8.61 s (3.38x)  -> a whole step is 6 + 2.65 + 3.38 = 12.0 internal-block samples (DESIGN.md).
-CPU_STEP_OVER_SAMPLE = 6 + 2.65 + 3.38
-
-
 def run_reference(args):
+    """The reference arm: the same chained step (same config keys) through the oracle port on all host cores.  Every
+    step is a whole step; as many of the requested `--steps` as fit into about 150 s of wall clock are run and `steps`
+    reports how many that was (a step takes tens of seconds on the host)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    threads = os.cpu_count() or 1
-    for _ in range(max(args.warmup, 1)):
-        cpu_reference_sample(threads)
-    times = [cpu_reference_sample(threads) for _ in range(args.steps)]
+    from benchlib import cpu_reference
+    times, ran, warm, threads = cpu_reference.run(args.steps, args.warmup, budget_s=args.cpu_budget)
     t = sum(times) / len(times)
-    step_s = t * CPU_STEP_OVER_SAMPLE
-    value = 1.0 / step_s
-    sample = ("one internal SpectralConv block (240x480, C=384, B=1) fwd+bwd per step, torch CPU fp32; "
-              f"scaled x{CPU_STEP_OVER_SAMPLE:.1f} to the 8-block step")
+    value = 1.0 / t
+    sample = (f"{ran} whole step(s) of the 8-block chained workload (block 0 at 721x1440, block 7 up-scaling), fwd+bwd, "
+              f"torch CPU fp32 spectral arithmetic on bf16 fields, {threads} threads, after {warm} untimed step(s); "
+              f"requested --steps {args.steps} --warmup {args.warmup}, bounded to ~{args.cpu_budget:.0f} s")
+    cfg = base_config(args.gpus, 1)
+    cfg.update({"host_threads": threads, "steps_requested": args.steps, "warmup_requested": args.warmup,
+                "step_seconds": [round(x, 2) for x in times]})
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": "samples/s", "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": step_s * 1e3, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "sample_ms": t * 1e3},
+        "steps": ran, "warmup": warm, "ms_per_step": t * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": cfg,
         "cpu_baseline": {"value": value, "unit": "samples/s", "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     print(json.dumps(line), flush=True)
+
+
+def cpu_baseline_sample():
+    """`cpu_baseline` of the GPU arm (rank 0, N = 1): the three block kinds of the step measured once each on the host."""
+    from benchlib import cpu_reference
+    cs = cpu_reference.CpuStep()
+    t = cs.sample()
+    step_s = t[0] + 6 * t[1] + t[7]
+    return {"value": 1.0 / step_s, "unit": "samples/s", "cores": cs.threads, "kind": "port",
+            "sample": (f"blocks 0, 1, 7 of the step (721x1440 -> 240x480, 240x480 internal, 240x480 -> 721x1440), each fwd+bwd "
+                       f"once on the host: {t[0]:.1f} s, {t[1]:.1f} s, {t[7]:.1f} s; step = t0 + 6 t1 + t7 = {step_s:.1f} s "
+                       "(six identical internal blocks); torch CPU fp32 (oracle port); the --impl reference arm runs "
+                       "whole chained steps")}
+
+
+# ------------------------------------------------------------------------------------------------ block roofline
+def block_roofline(blocks, dev, peak, traffic):
+    """SURVEY 8(d)'s unit: ONE internal SpectralConv block forward (240x480, C = 384, B = 1).  Timed through the module
+    call with CUDA events over rotating inputs (4 x 88.5 MB bf16 + 283 MB of weights per call: nothing survives in
+    the 126 MB L2 from one call to the next)."""
+    blk = blocks[1]
+    xs = [torch.rand(1, C_EMBED, GRID_INT[0], GRID_INT[1], device=dev).to(torch.bfloat16) for _ in range(4)]
+    n = 24
+
+    def timed(fn):
+        for i in range(4):
+            fn(i % 4)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(n):
+            fn(i % 4)
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / n * 1e3
+
+    with torch.no_grad():
+        blk.invalidate()
+        us = timed(lambda i: blk(xs[i]))                   # inference: packed weight cached
+    xg = [x.clone().requires_grad_(True) for x in xs]
+    us_pack = timed(lambda i: blk(xg[i]))                  # training forward: + weight re-pack (layout change)
+    b16 = W.block_forward_bytes(GRID_INT, GRID_INT, 1, esize=2)
+    b32 = W.block_forward_bytes(GRID_INT, GRID_INT, 1, esize=4)
+    out = {"unit": "one internal SpectralConv block forward (240x480, C=384, B=1, bf16 I/O)", "us": us,
+           "us_with_weight_repack": us_pack,
+           "alg_bytes_bf16_io": b16, "alg_bytes_fp32_survey_8d": b32,
+           "formula": "fields in + out (176.9 MB x b at 2 B, 353.9 MB x b at 4 B) + 394.2 MB (weight 283.1 + two tables 55.5)",
+           "achieved_gbs": b16 / (us * 1e-6) / 1e9, "frac": b16 / (us * 1e-6) / 1e9 / peak,
+           "frac_fp32_formula": b32 / (us * 1e-6) / 1e9 / peak,
+           "frac_with_weight_repack": b16 / (us_pack * 1e-6) / 1e9 / peak, "target_frac": 0.70}
+    t = traffic.get("block_internal_fwd")
+    if t:
+        out["dram_bytes_ncu"] = t["bytes"]
+        out["traffic_ratio"] = t["bytes"] / b16
+        out["traffic_source"] = t.get("source")
+    return out
 
 
 # ------------------------------------------------------------------------------------------------ main
@@ -347,7 +223,24 @@ def run_ours(args):
 
     dtype = torch.bfloat16
     batch = 1
-    blocks = build_gpu(dev, dtype)
+    t_wall0 = time.perf_counter()
+
+    def barrier():
+        if distributed:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- N >= 2: parity of the h-sharded path against the fp64 oracle BEFORE anything is timed (config 4 geometry)
+    parity, parity_ok, h, polar = None, True, 1, None
+    if distributed and not args.no_spatial:
+        from benchlib import spatial
+        import makani_b200.distributed as thd
+        h, polar, replica = spatial.make_groups(world, rank)
+        thd.init(polar, None)
+        parity, parity_ok = spatial.parity(dev, rank, h, polar, replica)
+        barrier()
+
+    blocks = build_gpu(dev)
 
     # data-parallel replicas: the only exchange is the weight-gradient all-reduce (DDP's job in the reference,
     # makani/mpu/mappings.py:104-172); issued per block as soon as its gradient exists so NCCL overlaps the
@@ -355,47 +248,15 @@ def run_ours(args):
     from makani_b200.distributed.grad_sync import GradientAverager
     sync = GradientAverager([blk.weight for blk in blocks]) if distributed else None
 
-    state = {}
+    grads = make_grads(batch, dtype, dev, chained=True)
+    xs_host = make_inputs(batch, dtype, pinned=True, chained=True)
+    x_dev = xs_host[0].to(dev).requires_grad_(True)
 
-    def setup(chained):
-        state.clear()
-        state["chained"] = chained
-        state["grads"] = make_grads(batch, dtype, dev, chained=chained)
-        state["xs_host"] = make_inputs(batch, dtype, pinned=True, chained=chained)
-        state["xs_dev"] = [x.to(dev).requires_grad_(True) for x in state["xs_host"]]
-
-    def step(xs=None):
-        xs = state["xs_dev"] if xs is None else xs
-        if state["chained"]:
-            out = gpu_step_chained(blocks, xs[0], state["grads"])
-        else:
-            out = gpu_step(blocks, xs, state["grads"])
+    def step(x=None, g=None):
+        out = gpu_step_chained(blocks, x_dev if x is None else x, grads if g is None else g)
         if sync is not None:
             sync.wait()
         return out
-
-    setup(args.inputs == "chained")
-    if state["chained"]:
-        # the chained step is one autograd graph over all eight blocks; should it fail on this box, measure the same
-        # kernels block by block (every block on its own input) rather than nothing, and say so in `config`.
-        try:
-            step()
-            torch.cuda.synchronize()
-        except Exception as e:                                      # noqa: BLE001
-            print(f"bench: chained step failed ({type(e).__name__}: {e}); using independent inputs", file=sys.stderr)
-            if sync is not None:
-                try:
-                    sync.wait()
-                except Exception:                                   # noqa: BLE001
-                    sync._pending.clear()
-            setup(False)
-    chained = state["chained"]
-    xs_host, xs_dev = state["xs_host"], state["xs_dev"]
-
-    def barrier():
-        if distributed:
-            dist.barrier()
-        torch.cuda.synchronize()
 
     # ---- device-resident timing (`value`)
     for _ in range(max(args.warmup, 3)):
@@ -414,9 +275,9 @@ def run_ours(args):
     launches = _ext.launch_count() - launches0
 
     # ---- end-to-end timing: pinned host inputs -> device, step, checksum back to host, every step.
-    # Two device input sets: while step i computes on one, the copy engine fills the other with the inputs of step
+    # Two device input sets: while step i computes on one, the copy engine fills the other with the input of step
     # i+1 (a data loader's prefetch); every step's host->device copy and device->host read are inside the timed region.
-    sets = [xs_dev, [x.detach().clone().requires_grad_(True) for x in xs_dev]]
+    sets = [x_dev, x_dev.detach().clone().requires_grad_(True)]
     copy_stream = torch.cuda.Stream()
     ready = [torch.cuda.Event(), torch.cuda.Event()]
     consumed = [torch.cuda.Event(), torch.cuda.Event()]
@@ -424,15 +285,12 @@ def run_ours(args):
     def enqueue_copy(k):
         with torch.cuda.stream(copy_stream):
             copy_stream.wait_event(consumed[k])
-            for xd, xh in zip(sets[k], xs_host):
-                xd.data.copy_(xh, non_blocking=True)
+            sets[k].data.copy_(xs_host[0], non_blocking=True)
             ready[k].record(copy_stream)
 
     def e2e_step(i, last):
         k = i & 1
-        # prefetch first: the other set was released by step i-1 (already enqueued), so its copy is handed to the
-        # copy engine BEFORE the host spends ~3 ms enqueueing this step's 560 launches, not after
-        if not last:
+        if not last:                                    # hand the next copy to the copy engine before enqueueing this step
             enqueue_copy(k ^ 1)
         torch.cuda.current_stream().wait_event(ready[k])
         out = step(sets[k])
@@ -444,8 +302,7 @@ def run_ours(args):
     enqueue_copy(0)
     e2e_step(0, True)
     barrier()
-    t0 = torch.cuda.Event(enable_timing=True)
-    t1 = torch.cuda.Event(enable_timing=True)
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t0.record()
     enqueue_copy(0)
     for i in range(args.steps):
@@ -454,7 +311,7 @@ def run_ours(args):
     barrier()
     ms_e2e = t0.elapsed_time(t1)
     del sets
-    h2d = sum(x.numel() * x.element_size() for x in xs_host)
+    h2d = xs_host[0].numel() * xs_host[0].element_size()
     d2h = chk.numel() * chk.element_size()
 
     times = torch.tensor([ms, ms_e2e], dtype=torch.float64, device=dev)
@@ -462,11 +319,15 @@ def run_ours(args):
         dist.all_reduce(times, op=dist.ReduceOp.MAX)
     ms, ms_e2e = times.tolist()
 
-    # ---- roofline of the dominant kernel, measured live with CUDA events in a separate profiled pass.
+    # ---- per-kernel numbers, measured live with CUDA events in a separate profiled pass.
     # Every rank runs the pass (the steps contain the gradient all-reduce); only rank 0 instruments and reports.
     rows = None
     if rank == 0:
-        with KernelProfiler() as prof:
+        from benchlib.profiler import KernelProfiler
+        plans = []
+        for blk in blocks:
+            plans += [blk.forward_transform._plan(dev), blk.inverse_transform._plan(dev)]
+        with KernelProfiler(plans) as prof:
             for _ in range(3):
                 step()
             rows = prof.summary()
@@ -475,50 +336,117 @@ def run_ours(args):
             step()
     barrier()
 
+    # ---- BASELINE config 3: global batch 8 over the N GPUs (local batch 8 / N), same step
+    config3 = None
+    if not args.no_config3 and 8 % world == 0:
+        lb = 8 // world
+        g3 = make_grads(lb, dtype, dev, chained=True)
+        x3 = make_inputs(lb, dtype, pinned=False, chained=True)[0].to(dev).requires_grad_(True)
+        for _ in range(2):
+            step(x3, g3)
+        barrier()
+        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        n3 = max(2, min(args.steps, 4))
+        a0.record()
+        for _ in range(n3):
+            step(x3, g3)
+        a1.record()
+        barrier()
+        t3 = torch.tensor([a0.elapsed_time(a1) / n3], dtype=torch.float64, device=dev)
+        if distributed:
+            dist.all_reduce(t3, op=dist.ReduceOp.MAX)
+        config3 = {"global_batch": 8, "per_gpu_batch": lb, "ms_per_step": float(t3), "steps": n3,
+                   "value": 8.0 / (float(t3) * 1e-3), "unit": "samples/s", "scaling": "strong (global batch fixed)"}
+        del g3, x3
+        x_dev.grad = None
+        torch.cuda.empty_cache()
+
+    # ---- BASELINE config 4: h-sharded SpectralConv blocks (N >= 2)
+    spatial_out = None
+    if distributed and not args.no_spatial:
+        spatial_out = spatial.timings(dev, rank, h, polar, blocks, steps=6, warmup=2)
+        if world > h:
+            spatial_out["layout"] = f"{world // h} data-parallel replicas x h = {h}"
+        barrier()
+
     line = None
     if rank == 0:
         peak, peak_src = measured_peaks()
-        dom = rows[0]
+        traffic = ncu_traffic()
         step_ms_prof = sum(r["total_ms"] for r in rows) / 3
-        top = [dict(kernel=r["kernel"], shape={k: v for k, v in r["shape"].items()}, launches_per_step=r["launches"] // 3,
-                    avg_us=round(r["avg_us"], 1), share=round(r["total_ms"] / 3 / step_ms_prof, 3),
-                    gbs=round(r["gbs"], 1), frac=round(r["gbs"] / peak, 3)) for r in rows[:16]]
+        kernels = []
+        for r in rows[:16]:
+            per_step = r["total_ms"] / 3
+            kernels.append(dict(kernel=r["kernel"], shape=r["shape"], launches_per_step=r["launches"] // 3,
+                                ms_per_step=round(per_step, 4), share=round(per_step / step_ms_prof, 3),
+                                alg_MB_per_step=round(r["alg_bytes_total"] / 3 / 1e6, 1), gbs=round(r["gbs"], 1),
+                                frac=round(r["gbs"] / peak, 3)))
+        dom = rows[0]
+        # one "launch" of the dominant family = one pass over a whole tensor (its channel windows together)
+        passes = max(1, round(dom["channels_total"] / C_EMBED)) if dom["channels_total"] else dom["launches"]
         roofline = {"bound": "hbm", "kernel": dom["kernel"], "shape": dom["shape"], "achieved": dom["gbs"], "peak": peak,
-                    "peak_source": peak_src, "unit": "GB/s", "frac": dom["gbs"] / peak, "traffic": ncu_traffic(dom["kernel"], dom["shape"]),
-                    "alg_bytes": dom["alg_bytes"],
-                    "avg_us": dom["avg_us"], "share_of_step": dom["total_ms"] / 3 / step_ms_prof}
-        # CPU baseline: bounded sample on the host cores (rank 0, N = 1 only)
-        cpu = None
-        if world == 1 and not args.no_cpu_baseline:
-            threads = os.cpu_count() or 1
-            cpu_reference_sample(threads)
-            ts = [cpu_reference_sample(threads) for _ in range(3)]
-            t = sorted(ts)[1]
-            cpu = {"value": 1.0 / (t * CPU_STEP_OVER_SAMPLE), "unit": "samples/s", "cores": threads, "kind": "port",
-                   "sample": "one internal SpectralConv block (240x480, C=384, B=1) fwd+bwd, torch CPU fp32 (oracle port), "
-                             f"median of 3 = {t * 1e3:.0f} ms, scaled x{CPU_STEP_OVER_SAMPLE:.1f} to the 8-block step"}
+                    "peak_source": peak_src, "unit": "GB/s", "frac": dom["gbs"] / peak,
+                    "traffic": kernel_traffic(traffic, dom["kernel"], dom["shape"]),
+                    "alg_bytes": dom["alg_bytes_total"] / passes, "avg_us": dom["total_ms"] / passes * 1e3,
+                    "kernel_launches_per_pass": dom["launches"] / passes,
+                    "share_of_step": dom["total_ms"] / 3 / step_ms_prof}
+        sb = W.step_bytes(batch)
+        roofline["step"] = {"alg_bytes": sb, "achieved_gbs": sb / (ms / args.steps * 1e-3) / 1e9,
+                            "frac": sb / (ms / args.steps * 1e-3) / 1e9 / peak,
+                            "definition": "sum over the 8 blocks of fields in/out/residual + weight (+ dW) + tables, fwd + bwd "
+                                          "(tools/benchlib/workload.py step_bytes); weight re-pack / gradient unpack count as 0"}
+        if world == 1:
+            roofline["block"] = block_roofline(blocks, dev, peak, traffic)
+            if "traffic_ratio" in roofline["block"]:
+                roofline["traffic_ratio"] = roofline["block"]["traffic_ratio"]
+    barrier()
+
+    rollout = gpu_base = cpu = None
+    if rank == 0 and world == 1:
+        if not args.no_rollout:
+            from benchlib import rollout as R
+            x_dev.grad = None
+            rollout = R.measure(blocks, x_dev.detach(), steps=40)
+        if not args.no_gpu_baseline:
+            from benchlib import torch_gpu
+            del grads
+            torch.cuda.empty_cache()
+            try:
+                gpu_base = torch_gpu.measure(dev, steps=5, warmup=2)
+                gpu_base["speedup_of_this_repo"] = gpu_base["ms_per_step"] / (ms / args.steps)
+            except Exception as e:                          # noqa: BLE001  (an OOM here must not lose the bench line)
+                gpu_base = {"error": f"{type(e).__name__}: {e}"[:300]}
+        if not args.no_cpu_baseline:
+            cpu = cpu_baseline_sample()
+
+    if rank == 0:
         samples = batch * world * args.steps
+        cfg = base_config(world, batch)
+        cfg.update({"l2": f"inputs ({h2d / 1e9:.1f} GB/step) and weights (2.27 GB) are far larger than the 126 MB L2; the "
+                          "DFT<->Legendre intermediates go through a re-used window buffer that is meant to stay in L2",
+                    "window_mb": float(os.environ.get("MAKANI_B200_WINDOW_MB", "60")),
+                    "e2e": "pinned-host input (block 0's field) copied every step on a copy stream, double buffered "
+                           "against compute; the step's results (output field, input gradient, weight gradients) stay on "
+                           "the device as in a training step - a 16-byte checksum of output and input gradient is read back",
+                    "wall_s": round(time.perf_counter() - t_wall0, 1)})
         line = {
             "metric": METRIC, "value": samples / (ms * 1e-3), "unit": "samples/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "tf32", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "per_gpu_batch": batch, "embed_dim": C_EMBED, "modes": [L_MODES, M_MODES],
-                       "io_dtype": "bf16", "accumulate": "fp32", "parallelism": f"dp{world}",
-                       "inputs": ("chained: block i+1 reads block i's output, one backward pass from block 7 to the input"
-                                  if chained else "independent: every block on its own synthetic input"),
-                       "l2": f"inputs ({h2d / 1e9:.1f} GB/step) and intermediates (XM / SP 178-536 MB per kernel) are far "
-                             "larger than the 126 MB L2",
-                       "includes": "fwd + dX + dW of all 8 blocks, weight repack every step; no optimizer update",
-                       "e2e": "pinned-host inputs copied every step on a copy stream, double buffered against compute"},
+            "vs_baseline": None, "dtype": "tf32", "data": "synthetic", "config": cfg,
             "e2e": {"value": samples / (ms_e2e * 1e-3), "unit": "samples/s", "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e / args.steps},
-            "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu, "kernels": top,
+            "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
+            "gpu_baseline": gpu_base, "rollout": rollout, "config3": config3, "parity": parity, "spatial": spatial_out,
+            "kernels": kernels,
         }
     if distributed:
         dist.barrier()
         dist.destroy_process_group()
     if line is not None:
         print(json.dumps(line), flush=True)
+    if not parity_ok:
+        print("bench: PARITY FAILURE of the h-sharded path against the fp64 oracle (see `parity`)", file=sys.stderr)
+        sys.exit(3)
 
 
 def main():
@@ -527,10 +455,12 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--cpu-budget", type=float, default=150.0, help="--impl reference: wall-clock bound in seconds")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--inputs", default="chained", choices=["chained", "independent"],
-                    help="chained: the batch flows through the eight blocks as in the model (default); "
-                         "independent: every block gets its own host input")
+    ap.add_argument("--no-gpu-baseline", action="store_true")
+    ap.add_argument("--no-rollout", action="store_true")
+    ap.add_argument("--no-config3", action="store_true")
+    ap.add_argument("--no-spatial", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -145,6 +145,10 @@ int sfno_c64_to_xm(const void* in_c64, int B, int C, int nlat, int mmax, float* 
 int sfno_add_bias(void* y, int y_dtype, const float* bias, int bias_kind, int B, int C, int H, int W,
                   void* stream);
 
+/* dst[i] += src[i], i < n (n % 4 == 0, 16-byte aligned): the sum of two gradients in an internal layout (SP_l of the
+ * h-sharded SpectralConv backward: filter branch + re-projected residual, spectral_convolution.py:132-134).   */
+int sfno_add_inplace(float* dst, const float* src, long long n, void* stream);
+
 /* Constant bias [C] folded into the m = 0 Fourier coefficient of an XM tensor (or XM window: pass bias + c0) before
  * the inverse DFT:  XM[0][b][re][c][k] += bias[c].  Equals `x = x + bias` in fp32 before the cast to the output dtype
  * (spectral_convolution.py:143-146) at the cost of B*C*nlat elements.                                        */

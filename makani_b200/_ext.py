@@ -44,6 +44,7 @@ _PROTOTYPES = {
     "sfno_xm_to_c64": (_i, [_vp, _i, _i, _i, _i, _vp, _vp]),
     "sfno_c64_to_xm": (_i, [_vp, _i, _i, _i, _i, _vp, _vp]),
     "sfno_add_bias": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _i, _vp]),
+    "sfno_add_inplace": (_i, [_vp, _vp, _ll, _vp]),
     "sfno_xm_add_dc": (_i, [_vp, _i, _i, _i, _vp, _vp]),
     "sfno_workspace_bytes": (C.c_size_t, [_vp, _vp, _i, _i, _i]),
     "sfno_sht_fwd": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp, C.c_size_t, _vp]),

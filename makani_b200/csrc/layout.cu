@@ -256,6 +256,16 @@ __global__ void add_bias_kernel(T* __restrict__ y, const float* __restrict__ bia
   }
 }
 
+// dst += src over n floats (n % 4 == 0, 16-byte aligned): sum of two SP gradients on the h-sharded path
+__global__ void __launch_bounds__(256) add_inplace_kernel(float4* __restrict__ dst, const float4* __restrict__ src, long long n4) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
+    float4 a = dst[i];
+    const float4 b = src[i];
+    a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+    dst[i] = a;
+  }
+}
+
 // constant bias as the m = 0 Fourier coefficient: irfft(norm="forward") adds Re XM[0][b][c][k] to every longitude of
 // latitude k, so  y + bias[c]  ==  irfft(XM with XM[0].re += bias[c])  - the add happens in fp32 before the cast to the
 // output dtype, as the reference does (spectral_convolution.py:143-146), and costs B*C*nlat elements instead of a pass
@@ -546,6 +556,17 @@ int sfno_add_bias(void* y, int y_dtype, const float* bias, int bias_kind, int B,
     case SFNO_F16: add_bias_kernel<__half><<<grid, 256, 0, s>>>((__half*)y, bias, bias_kind, n, C, HW); break;
     default: SFNO_CHECK(false, "unsupported dtype");
   }
+  SFNO_LAUNCHED();
+  return 0;
+}
+
+int sfno_add_inplace(float* dst, const float* src, long long n, void* stream) {
+  SFNO_CHECK(dst && src && n % 4 == 0, "sfno_add_inplace: null argument or n % 4 != 0");
+  SFNO_CHECK(((reinterpret_cast<uintptr_t>(dst) | reinterpret_cast<uintptr_t>(src)) & 15) == 0, "sfno_add_inplace: alignment");
+  if (n == 0) return 0;
+  const long long n4 = n / 4;
+  const int grid = (int)std::min<long long>((n4 + 255) / 256, 148 * 16);
+  add_inplace_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(reinterpret_cast<float4*>(dst), reinterpret_cast<const float4*>(src), n4);
   SFNO_LAUNCHED();
   return 0;
 }

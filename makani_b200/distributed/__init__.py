@@ -442,8 +442,9 @@ class _PolarExchange:
         return self._run("sp_ch", n, sp_l, mk, self.L * M * J * _rup4(self.cs[me]))
 
 
-def _polar_analysis(x, mod, scale_kind):
-    """x [B, C, K_loc, W] -> coefficients complex64 [B, C, L_loc, M]  (dft, lat->chan, Legendre analysis, chan->l)."""
+def _polar_analysis_sp(x, mod, scale_kind, round_tf32=False):
+    """x [B, C, K_loc, W] -> SP_l [L_loc][M][2B][Cp] (a VIEW of a peer receive buffer: consume or clone it before the
+    next exchange of the same layout)  (dft, lat->chan, Legendre analysis, chan->l)."""
     B, Cn = x.shape[0], x.shape[1]
     ex = _PolarExchange.of(mod, B, Cn, x.device)
     plan = mod._peer_plan(x.device)
@@ -453,23 +454,93 @@ def _polar_analysis(x, mod, scale_kind):
     else:
         xm_loc = ops.dft_fwd(x, mod.mmax, mod._scale(x.device, scale_kind))
         xm_ch = ex.lat_to_chan(xm_loc)
-    sp_ch = ops.legendre_analysis(plan, xm_ch, B, ex.cs[ex.me])
-    sp_l = ex.chan_to_l(sp_ch)
-    return ops.sp_to_c64(sp_l, B, Cn, ex.ls[ex.me], mod.mmax, ex.l0[ex.me], 0)
+    sp_ch = ops.legendre_analysis(plan, xm_ch, B, ex.cs[ex.me], round_tf32=round_tf32)
+    return ex.chan_to_l(sp_ch), ex
+
+
+def _polar_synthesis_sp(sp_l, B, Cn, mod, scale_kind, dtype):
+    """SP_l [L_loc][M][2B][Cp] -> x [B, C, K_loc, W]  (l->chan, Legendre synthesis, chan->lat, idft)."""
+    ex = _PolarExchange.of(mod, B, Cn, sp_l.device)
+    plan = mod._peer_plan(sp_l.device)
+    sp_ch = ex.l_to_chan(sp_l)
+    if ex.dft_fused(mod):
+        return ex.chan_to_field(plan, sp_ch, mod.nlon, mod._scale(sp_l.device, scale_kind), dtype)
+    xm_ch = ops.legendre_synthesis(plan, sp_ch, B, ex.cs[ex.me])
+    xm_loc = ex.chan_to_lat(xm_ch)
+    return ops.dft_inv(xm_loc, B, Cn, ex.lat[ex.me], mod.nlon, mod.mmax, mod._scale(sp_l.device, scale_kind), dtype)
+
+
+def _polar_analysis(x, mod, scale_kind):
+    """x [B, C, K_loc, W] -> coefficients complex64 [B, C, L_loc, M]."""
+    sp_l, ex = _polar_analysis_sp(x, mod, scale_kind)
+    return ops.sp_to_c64(sp_l, x.shape[0], x.shape[1], ex.ls[ex.me], mod.mmax, ex.l0[ex.me], 0)
 
 
 def _polar_synthesis(c, mod, scale_kind, dtype):
-    """coefficients complex64 [B, C, L_loc, M] -> x [B, C, K_loc, W]  (l->chan, Legendre synthesis, chan->lat, idft)."""
+    """coefficients complex64 [B, C, L_loc, M] -> x [B, C, K_loc, W]."""
     B, Cn = c.shape[0], c.shape[1]
     ex = _PolarExchange.of(mod, B, Cn, c.device)
-    plan = mod._peer_plan(c.device)
     sp_l = ops.c64_to_sp(c.to(torch.complex64), ex.l0[ex.me], 0)
-    sp_ch = ex.l_to_chan(sp_l)
-    if ex.dft_fused(mod):
-        return ex.chan_to_field(plan, sp_ch, mod.nlon, mod._scale(c.device, scale_kind), dtype)
-    xm_ch = ops.legendre_synthesis(plan, sp_ch, B, ex.cs[ex.me])
-    xm_loc = ex.chan_to_lat(xm_ch)
-    return ops.dft_inv(xm_loc, B, Cn, ex.lat[ex.me], mod.nlon, mod.mmax, mod._scale(c.device, scale_kind), dtype)
+    return _polar_synthesis_sp(sp_l, B, Cn, mod, scale_kind, dtype)
+
+
+class PolarSpectralConvFunction(torch.autograd.Function):
+    """(x_loc, weight shard, module) -> (y_loc, residual_loc or None): the h-sharded SpectralConv (dhconv) of
+    makani/models/common/spectral_convolution.py:78-82,104-107,124-148 on the peer-memory path, staying in the internal
+    layouts end to end:
+
+        dft -> [lat->chan] -> Legendre analysis -> [chan->l] -> dhconv on SP_l with l_offset (weights sharded on l, no
+        communication) -> [l->chan] -> Legendre synthesis -> [chan->lat] -> inverse dft
+
+    bf16 / fp16 / fp32 fields in and out, no complex64 tensor, no `.float()` copy, packed weight shard from the
+    module's cache.  Backward is the adjoint chain with the same four exchanges in the reverse roles."""
+
+    @staticmethod
+    def forward(ctx, x, weight, mod):
+        fwd, inv = mod.forward_transform, mod.inverse_transform
+        B, Cin, Cout = x.shape[0], mod.in_channels, mod.out_channels
+        M = mod.modes_lon
+        sp_l, ex = _polar_analysis_sp(x, fwd, "fwd", round_tf32=True)
+        Lloc, l0 = ex.ls[ex.me], ex.l0[ex.me]
+        need_grad = weight.requires_grad or x.requires_grad
+        sp_l = sp_l.clone() if (need_grad or mod.scale_residual) else sp_l      # leaves the receive buffer
+        residual = None
+        if mod.scale_residual:
+            residual = _polar_synthesis_sp(sp_l, B, Cin, inv, "one", x.dtype)
+        wp = mod._packed_weight(weight)
+        sp2_l = ops.dhconv_fwd(sp_l, wp, B, Cin, Cout, Lloc, M, l0, 0, round_tf32=True)
+        y = _polar_synthesis_sp(sp2_l, B, Cout, inv, "one", x.dtype)
+        ctx.mod, ctx.in_dtype, ctx.dims = mod, x.dtype, (B, Cin, Cout, Lloc, M, l0)
+        ctx.has_residual = residual is not None
+        ctx.save_for_backward(sp_l, wp)
+        return (y, residual) if residual is not None else (y, None)
+
+    @staticmethod
+    def backward(ctx, gy, gres):
+        mod = ctx.mod
+        fwd, inv = mod.forward_transform, mod.inverse_transform
+        B, Cin, Cout, Lloc, M, l0 = ctx.dims
+        sp_l, wp = ctx.saved_tensors
+        gsp2_l, _ = _polar_analysis_sp(gy, inv, "irfft_adj", round_tf32=True)
+        gw = None
+        if ctx.needs_input_grad[1]:
+            gw = ops.unpack_wgrad(ops.dhconv_bwd_w(sp_l, gsp2_l, B, Cin, Cout, Lloc, M, l0, 0), Cin, Cout, Lloc)
+        gx = None
+        if ctx.needs_input_grad[0]:
+            gsp_l = ops.dhconv_bwd_x(gsp2_l, wp, B, Cin, Cout, Lloc, M, l0, 0, round_tf32=True)
+            if ctx.has_residual and gres is not None:
+                gr_l, _ = _polar_analysis_sp(gres, inv, "irfft_adj", round_tf32=True)
+                ops.sp_band_add_(gsp_l, gr_l, B, Cin, Lloc, M, l0)
+            gx = _polar_synthesis_sp(gsp_l, B, Cin, fwd, "rfft_adj", ctx.in_dtype)
+        return gx, gw, None
+
+
+def polar_spectral_conv_ok(mod, x) -> bool:
+    """The fused h-sharded path applies: both transforms distributed, h-sharded over peer memory, dhconv, no bias."""
+    f, i = mod.forward_transform, mod.inverse_transform
+    return (isinstance(f, DistributedRealSHT) and isinstance(i, DistributedInverseRealSHT)
+            and mod.operator_type == "dhconv" and f.lmax == i.lmax and f.mmax == i.mmax
+            and f._peer_path(x) and i._peer_path(x))
 
 
 class _PolarSHT(torch.autograd.Function):

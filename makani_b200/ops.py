@@ -286,6 +286,13 @@ def add_bias_(y: torch.Tensor, bias: torch.Tensor) -> torch.Tensor:
     return y
 
 
+def sp_band_add_(dst: torch.Tensor, src: torch.Tensor, B: int, Cn: int, lmax: int, mmax: int, l_offset: int = 0):
+    """dst += src for two SP tensors of the same shape (values outside the defined band are never read by anyone)."""
+    n = sp_elems(lmax, mmax, B, Cn)
+    _ext.check(_ext.load().sfno_add_inplace(_ptr(dst), _ptr(src), n, _stream()), "sfno_add_inplace")
+    return dst
+
+
 # ------------------------------------------------------------------------------------------ dhconv
 def pack_weight(w: torch.Tensor) -> torch.Tensor:
     """complex64 [Cin, Cout, L] -> WP."""

@@ -288,6 +288,10 @@ class SpectralConv(nn.Module):
                 and type(self.forward_transform) is RealSHT and type(self.inverse_transform) is InverseRealSHT
                 and self.forward_transform.lmax == self.modes_lat and self.forward_transform.mmax == self.modes_lon)
 
+    def _polar_fused_ok(self, x):
+        from .distributed import polar_spectral_conv_ok
+        return polar_spectral_conv_ok(self, x)
+
     @annotate("SpectralConv.forward")
     def forward(self, x):
         dtype = x.dtype
@@ -295,6 +299,11 @@ class SpectralConv(nn.Module):
         ops.dtype_code(dtype)
         if self._fused_ok():
             y, residual = _SpectralConvFunction.apply(x.contiguous(), self.weight, getattr(self, "bias", None), self)
+            if residual is None:
+                residual = x
+        elif self._distributed and not hasattr(self, "bias") and self._polar_fused_ok(x):
+            from .distributed import PolarSpectralConvFunction
+            y, residual = PolarSpectralConvFunction.apply(x.contiguous(), self.weight, self)
             if residual is None:
                 residual = x
         else:

@@ -25,7 +25,6 @@ class _StandInBlock(nn.Module):
         super().__init__()
         self.weight = nn.Parameter(torch.randn(3, dtype=torch.complex64))
         self.n_in, self.n_out = n_in, n_out
-        self._wp_cache = "stale"
 
     def _resize(self, x):
         if self.n_in == self.n_out:
@@ -55,7 +54,6 @@ def test_chained_step_matches_manual_composition():
             grads.append((None, None))
     chk = b.gpu_step_chained(blocks, x0, grads)
     assert chk.shape == (2,) and torch.isfinite(chk).all()
-    assert all(blk._wp_cache is None for blk in blocks)
     got_x = x0.grad.clone()
     got_w = [blk.weight.grad.clone() for blk in blocks]
 
@@ -81,9 +79,12 @@ def test_chained_step_matches_manual_composition():
     torch.testing.assert_close(x0.grad, got_x)
 
 
-def test_make_grads_and_inputs_shapes():
+def test_make_grads_and_inputs_shapes(monkeypatch):
     b = _bench()
-    b.C_EMBED, b.GRID_IN, b.GRID_INT = 2, (9, 16, "equiangular"), (4, 8, "legendre-gauss")
+    b = b.W                                                 # tools/benchlib/workload.py
+    monkeypatch.setattr(b, "C_EMBED", 2)
+    monkeypatch.setattr(b, "GRID_IN", (9, 16, "equiangular"))
+    monkeypatch.setattr(b, "GRID_INT", (4, 8, "legendre-gauss"))
     cpu = torch.device("cpu")
     ind = b.make_grads(1, torch.float32, cpu)
     assert len(ind) == 8 and all(g is not None for g, _ in ind)
@@ -101,14 +102,24 @@ def test_algorithmic_bytes_formulas():
     b = _bench()
     tri = sum(min(l + 1, 241) for l in range(240))
     assert tri == 240 * 241 // 2
+    kb = b.W.kernel_bytes
     a = dict(B=1, C=384, K=240, W=480, M=241, esize=2)
-    assert b.alg_bytes("dft_fwd", a) == 384 * 240 * (480 * 2 + 241 * 8)
-    leg = b.alg_bytes("legendre_analysis", dict(B=1, C=384, K=240, L=240, M=241))
+    assert kb("dft_fwd", a) == 384 * 240 * (480 * 2 + 241 * 8)
+    leg = kb("legendre_analysis", dict(B=1, C=384, K=240, L=240, M=241))
     assert leg == 384 * 8 * (240 * 241 + tri) + 4 * 241 * 240 * 240
     assert abs(leg / 1e6 - 322) < 1.0                                   # DESIGN: 322 MB
-    dh = b.alg_bytes("dhconv_fwd", dict(B=1, Cin=384, Cout=384, L=240, M=241))
+    # channel windows: the pieces add up to the whole, the table is charged once
+    parts = sum(kb("legendre_analysis", dict(B=1, C=128, K=240, L=240, M=241, c0=c0)) for c0 in (0, 128, 256))
+    assert parts == leg
+    dh = kb("dhconv_fwd", dict(B=1, Cin=384, Cout=384, L=240, M=241))
     assert abs(dh / 1e6 - 461) < 1.0                                    # DESIGN: 461 MB
-    assert b.alg_bytes("pack_weight", dict(Cin=384, Cout=384, L=240)) == 16 * 384 * 384 * 240
+    assert kb("pack_weight", dict(Cin=384, Cout=384, L=240)) == 16 * 384 * 384 * 240
+    # one fused internal block forward, fp32 I/O: 353.9 b + 394.2 MB; the bf16-I/O variant; the whole step
+    g = b.W.GRID_INT
+    assert abs(b.W.block_forward_bytes(g, g, 1, esize=4) / 1e6 - 748.1) < 0.1
+    assert abs(b.W.block_forward_bytes(g, g, 8, esize=4) / 1e6 - 3225.3) < 0.1
+    assert abs(b.W.block_forward_bytes(g, g, 1, esize=2) / 1e6 - 571.1) < 0.1
+    assert abs(b.W.step_bytes() / 1e9 - 17.87) < 0.01
 
 
 def _chained_dp_worker(rank, world, port):

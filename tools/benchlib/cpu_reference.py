@@ -51,6 +51,29 @@ class CpuStep:
         return time.perf_counter() - t0
 
 
+    def sample(self):
+        """Bounded sample for the `cpu_baseline` leg of the GPU arm: blocks 0, 1 and 7 (the three block kinds), each
+        forward + backward once on its own synthetic input.  Returns {kind: seconds}; a whole step is
+        t[0] + 6 * t[1] + t[7] (six identical internal blocks)."""
+        O, dt = self.O, torch.bfloat16
+        xs = W.make_inputs(1, dt, pinned=False, chained=False, channels=self.C)
+        gs = W.make_grads(1, dt, torch.device("cpu"), chained=False, channels=self.C)
+        out = {}
+        for idx in (0, 1, 7):
+            f, i, w = self.blocks[idx]
+            x = xs[idx].requires_grad_(True)
+            gy, gr = gs[idx]
+            w.grad = None
+            t0 = time.perf_counter()
+            y, res = O.spectral_conv_forward(x, f, i, w, "dhconv", compute_dtype=torch.float32)
+            if gr is not None:
+                torch.autograd.backward([y, res], [gy, gr])
+            else:
+                torch.autograd.backward([y], [gy])
+            out[idx] = time.perf_counter() - t0
+        return out
+
+
 def run(steps, warmup, budget_s=150.0, channels=None):
     """Run up to `steps` timed steps (after `warmup` untimed ones) within about `budget_s` seconds of wall clock.
     Returns (seconds per step [list], steps run, warm-up steps run, threads)."""

@@ -422,9 +422,9 @@ def run_ours(args):
     if rank == 0:
         samples = batch * world * args.steps
         cfg = base_config(world, batch)
-        cfg.update({"l2": f"inputs ({h2d / 1e9:.1f} GB/step) and weights (2.27 GB) are far larger than the 126 MB L2; the "
-                          "DFT<->Legendre intermediates go through a re-used window buffer that is meant to stay in L2",
-                    "window_mb": float(os.environ.get("MAKANI_B200_WINDOW_MB", "60")),
+        cfg.update({"l2": f"inputs ({h2d / 1e9:.1f} GB/step), weights (2.27 GB) and intermediates (XM / SP 178-536 MB per kernel) "
+                          "are far larger than the 126 MB L2",
+                    "window_mb": float(os.environ.get("MAKANI_B200_WINDOW_MB", "0")),
                     "e2e": "pinned-host input (block 0's field) copied every step on a copy stream, double buffered "
                            "against compute; the step's results (output field, input gradient, weight gradients) stay on "
                            "the device as in a training step - a 16-byte checksum of output and input gradient is read back",

@@ -134,9 +134,11 @@ int sfno_diag_contract(int mode, const float* sp_a, const void* w_or_spb, void* 
  * SP <-> complex64 [B][C][lmax][mmax] (what RealSHT returns / InverseRealSHT accepts).           */
 int sfno_sp_to_c64(const float* sp, int B, int C, int lmax, int mmax, int l_offset, int m_offset, void* out_c64,
                    void* stream);
-/* entries with (m + m_offset) > (l + l_offset) are not read: they become the exact zeros the SP layout requires */
-int sfno_c64_to_sp(const void* in_c64, int B, int C, int lmax, int mmax, int l_offset, int m_offset, float* sp,
-                   void* stream);
+/* entries with (m + m_offset) > (l + l_offset) are not read: they become the exact zeros the SP layout requires.
+ * round_tf32 = 1: values are stored round-to-nearest TF32 (the consumer is a tensor-core contraction: Legendre
+ * synthesis, dhconv); 0: exact fp32 (the consumer is the fp32 diagonal contraction).                          */
+int sfno_c64_to_sp(const void* in_c64, int B, int C, int lmax, int mmax, int l_offset, int m_offset, int round_tf32,
+                   float* sp, void* stream);
 /* XM <-> complex64 [B][C][nlat][mmax]  (needed by the distributed SHT between its all-to-alls)   */
 int sfno_xm_to_c64(const float* xm, int B, int C, int nlat, int mmax, void* out_c64, void* stream);
 int sfno_c64_to_xm(const void* in_c64, int B, int C, int nlat, int mmax, float* xm, void* stream);

@@ -40,7 +40,7 @@ _PROTOTYPES = {
     "sfno_dhconv_bwd_w": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "sfno_diag_contract": (_i, [_i, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "sfno_sp_to_c64": (_i, [_vp, _i, _i, _i, _i, _i, _i, _vp, _vp]),
-    "sfno_c64_to_sp": (_i, [_vp, _i, _i, _i, _i, _i, _i, _vp, _vp]),
+    "sfno_c64_to_sp": (_i, [_vp, _i, _i, _i, _i, _i, _i, _i, _vp, _vp]),
     "sfno_xm_to_c64": (_i, [_vp, _i, _i, _i, _i, _vp, _vp]),
     "sfno_c64_to_xm": (_i, [_vp, _i, _i, _i, _i, _vp, _vp]),
     "sfno_add_bias": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _i, _vp]),

@@ -20,7 +20,7 @@ class _ContractFunction(torch.autograd.Function):
     def forward(ctx, x, weight, operator_type, l_offset, m_offset):
         B, Cin, L, M = x.shape
         Cout = weight.shape[1]
-        sp = ops.c64_to_sp(x, l_offset, m_offset)
+        sp = ops.c64_to_sp(x, l_offset, m_offset, round_tf32=(operator_type == "dhconv"))
         if operator_type == "dhconv":
             wsaved = ops.pack_weight(weight)
             sp2 = ops.dhconv_fwd(sp, wsaved, B, Cin, Cout, L, M, l_offset, m_offset)
@@ -35,7 +35,7 @@ class _ContractFunction(torch.autograd.Function):
     def backward(ctx, g):
         operator_type, B, Cin, Cout, L, M, lo, mo = ctx.meta
         sp, wsaved = ctx.saved_tensors
-        gsp2 = ops.c64_to_sp(g.to(torch.complex64), lo, mo)
+        gsp2 = ops.c64_to_sp(g.to(torch.complex64), lo, mo, round_tf32=(operator_type == "dhconv"))
         gx = gw = None
         if operator_type == "dhconv":
             if ctx.needs_input_grad[1]:

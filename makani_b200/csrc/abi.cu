@@ -212,7 +212,7 @@ int sfno_sht_inv(const sfno_plan* plan, const void* coeffs_c64, int B, int C, vo
   cudaStream_t s = (cudaStream_t)stream;
   float* xm = static_cast<float*>(ws);
   float* sp = reinterpret_cast<float*>(static_cast<char*>(ws) + xm_bytes(plan, B, C));
-  if (sfno_c64_to_sp(coeffs_c64, B, C, plan->lmax, plan->mmax, 0, plan->m_offset, sp, stream)) return 1;
+  if (sfno_c64_to_sp(coeffs_c64, B, C, plan->lmax, plan->mmax, 0, plan->m_offset, 1, sp, stream)) return 1;
   if (legendre_synthesis(plan, sp, B, C, C, 0, xm, s)) return 1;
   return dft_inv(xm, B, C, C, plan->nlat, plan->nlon, plan->mmax, plan->mmax, plan->mscale + (plan->nlon / 2 + 1), y,
                  y_dtype, s);

@@ -54,7 +54,7 @@ __global__ void sp_to_c64_kernel(const float* __restrict__ sp, float2* __restric
 }
 
 __global__ void c64_to_sp_kernel(const float2* __restrict__ in, float* __restrict__ sp, int B, int C, int L, int M,
-                                 int l_off, int m_off) {
+                                 int l_off, int m_off, int round_out) {
   __shared__ float tr[32][33], ti[32][33];
   const int Cp = (C + 3) & ~3;
   const long long RS = 2LL * B * Cp;
@@ -73,8 +73,9 @@ __global__ void c64_to_sp_kernel(const float2* __restrict__ in, float* __restric
     const int m = m0 + j, c = c0 + threadIdx.x;
     if (m < M && c < Cp) {      // pad channels are written as zeros so the whole SP tensor is defined
       const long long base = ((long long)l * M + m) * RS + (long long)(b * 2) * Cp + c;
-      sp[base] = (c < C) ? tf32_rn(tr[threadIdx.x][j]) : 0.f;        // operands of TF32 GEMMs: pre-rounded
-      sp[base + Cp] = (c < C) ? tf32_rn(ti[threadIdx.x][j]) : 0.f;
+      const float vr = tr[threadIdx.x][j], vi = ti[threadIdx.x][j];
+      sp[base] = (c < C) ? (round_out ? tf32_rn(vr) : vr) : 0.f;     // operands of TF32 GEMMs: pre-rounded
+      sp[base + Cp] = (c < C) ? (round_out ? tf32_rn(vi) : vi) : 0.f;
     }
   }
 }
@@ -499,11 +500,11 @@ int sfno_sp_to_c64(const float* sp, int B, int C, int lmax, int mmax, int l_offs
   SFNO_LAUNCHED();
   return 0;
 }
-int sfno_c64_to_sp(const void* in_c64, int B, int C, int lmax, int mmax, int l_offset, int m_offset, float* sp,
-                   void* stream) {
+int sfno_c64_to_sp(const void* in_c64, int B, int C, int lmax, int mmax, int l_offset, int m_offset, int round_tf32,
+                   float* sp, void* stream) {
   const int Cp = (C + 3) & ~3;
   dim3 grid((mmax + 31) / 32, (Cp + 31) / 32, lmax * B), block(32, 8);
-  c64_to_sp_kernel<<<grid, block, 0, (cudaStream_t)stream>>>((const float2*)in_c64, sp, B, C, lmax, mmax, l_offset, m_offset);
+  c64_to_sp_kernel<<<grid, block, 0, (cudaStream_t)stream>>>((const float2*)in_c64, sp, B, C, lmax, mmax, l_offset, m_offset, round_tf32);
   SFNO_LAUNCHED();
   return 0;
 }

@@ -155,10 +155,15 @@ def legendre_synthesis(plan: Plan, sp: torch.Tensor, B: int, Cn: int, out: torch
 # (178 MB at 240x480, 536 MB at 721x1440 for C = 384) stays in the 126 MB L2 instead of being written to HBM by one
 # kernel and read back by the next: this is the fusion across the RFFT -> Legendre and Legendre -> inverse-RFFT
 # boundaries of makani/models/common/spectral_convolution.py:131-141 (see include/makani_b200.h, "channel-window
-# variants").  MAKANI_B200_WINDOW_MB sets the size of the window buffer (default 60; 0 disables windows).
+# variants").  MAKANI_B200_WINDOW_MB sets the size of the window buffer; 0 (the default) runs every stage once over all
+# channels.  MEASURED on B200 (round 2, profiles/r2a_window_ab.txt): the windows do take XM out of the DRAM traffic, but
+# the step gets SLOWER (11.2 ms -> 13.3 ms at 120 MB, 15.3 ms at 60 MB): every extra launch costs ~15 us of ramp-up and
+# tail (a window's kernels last only 20 - 35 us, a GEMM tile ~8 us), far more than the saved traffic is worth to
+# kernels that are not DRAM-bound; and at 721x1440 the 167 MB Legendre table does not fit L2 next to a window, so
+# every window re-reads it from DRAM.  Kept as an option (bit-identical results, tests/test_gpu_modules.py).
 import os as _os
 
-_WINDOW_MB = float(_os.environ.get("MAKANI_B200_WINDOW_MB", "60"))
+_WINDOW_MB = float(_os.environ.get("MAKANI_B200_WINDOW_MB", "0"))
 _WINDOW_BUFFERS = {}
 
 
@@ -246,15 +251,17 @@ def sp_to_c64(sp, B, Cn, lmax, mmax, l_offset=0, m_offset=0) -> torch.Tensor:
     return out
 
 
-def c64_to_sp(c: torch.Tensor, l_offset: int = 0, m_offset: int = 0) -> torch.Tensor:
-    """complex64 [B, C, L, M] -> SP.  Entries with m + m_offset > l + l_offset are taken as zero (not read)."""
+def c64_to_sp(c: torch.Tensor, l_offset: int = 0, m_offset: int = 0, round_tf32: bool = True) -> torch.Tensor:
+    """complex64 [B, C, L, M] -> SP.  Entries with m + m_offset > l + l_offset are taken as zero (not read).
+    round_tf32: the consumer is a TF32 tensor-core contraction (store round-to-nearest TF32 values)."""
     _need_cuda(c, "coefficients")
     B, Cn, L, M = c.shape
     c = c.contiguous()
     if c.dtype != torch.complex64:
         raise TypeError(f"makani_b200: spectral coefficients must be complex64, got {c.dtype}")
     sp = torch.empty(sp_elems(L, M, B, Cn), dtype=torch.float32, device=c.device)
-    _ext.check(_ext.load().sfno_c64_to_sp(_ptr(c), B, Cn, L, M, l_offset, m_offset, _ptr(sp), _stream()),
+    _ext.check(_ext.load().sfno_c64_to_sp(_ptr(c), B, Cn, L, M, l_offset, m_offset, int(round_tf32), _ptr(sp),
+                                          _stream()),
                "sfno_c64_to_sp")
     return sp
 

@@ -10,20 +10,10 @@
 #include <algorithm>
 #include <type_traits>
 
-#include "wpack.cuh"
 #include <cstdlib>
 
 namespace sfno {
 
-// SFNO_WPACK_TL=32 selects the 16 KB-tile pack / unpack kernels of wpack.cuh (default: the 64 x 64 kernels below)
-static int wpack_tile() {
-  static int v = -1;
-  if (v < 0) {
-    const char* env = getenv("SFNO_WPACK_TL");
-    v = (env && atoi(env) == 32) ? 32 : 64;
-  }
-  return v;
-}
 
 
 // ------------------------------------------------------------------ SP <-> complex64 [B][C][L][M]
@@ -293,6 +283,7 @@ __global__ void xm_add_dc_kernel(float* __restrict__ xm, const float* __restrict
 //   MODE 2  : blockIdx.z = chunk of Cc output channels o; the batch is walked in chunks of Bc inside the kernel and
 //             the partial sums go through the (L2-resident) result
 constexpr int kDiagBc = 4;
+constexpr int kDiagCi = 128;   // MODE 2: input channels per CTA
 template <int MODE>
 __global__ void diag_kernel(const float* __restrict__ spa, const void* __restrict__ wb, void* __restrict__ outp,
                             int B, int Cin, int Cout, int L, int M, int l_off, int m_off, int Bc, int Cc) {
@@ -370,29 +361,45 @@ __global__ void diag_kernel(const float* __restrict__ spa, const void* __restric
         out[((long long)l * M + m0 + mm) * RSb + (long long)(b0 * 2 + j) * Cresp + c0 + c] = tb[mm * (nt + 1) + j * Cc + c];
     }
   } else {
-    const int o0 = blockIdx.z * Cc, nco = min(Cc, Cout - o0);
+    // blockIdx.z = (chunk of kDiagCi input channels) x (chunk of Cc output channels); both staged tiles hold one batch
+    // chunk of their channel chunk only
+    const int nic = (Cin + kDiagCi - 1) / kDiagCi;
+    const int i0 = (blockIdx.z % nic) * kDiagCi, nci = min(kDiagCi, Cin - i0);
+    const int o0 = (blockIdx.z / nic) * Cc, nco = min(Cc, Cout - o0);
     float2* gw = static_cast<float2*>(outp);
     const float* spg = static_cast<const float*>(wb);
+    float* ta = smd;                                    // [32][2*Bc*kDiagCi + 1]  x of this batch / channel chunk
+    float* tb = smd + 32 * (2 * Bc * kDiagCi + 1);      // [32][2*Bc*Cc + 1]       g of this batch / channel chunk
+    // stage channels [c0, c0 + nc) of batch entries [b0, b0 + nb): t[mm][(bb*2 + reim)*nc + c]
+    auto stage_ch = [&](float* t, const float* sp, int RS, int Cp, int b0, int nb, int c0, int nc) {
+      const int n = 2 * nb * nc;
+      for (int idx = tid; idx < 32 * n; idx += 256) {
+        const int mm = idx / n, r = idx - mm * n;
+        const int j = r / nc, c = r - j * nc;
+        float v = 0.f;
+        if (m0 + mm < mhi_l && (m0 + mm + m_off) <= (l + l_off))
+          v = sp[((long long)l * M + m0 + mm) * RS + (long long)(b0 * 2 + j) * Cp + c0 + c];
+        t[mm * (n + 1) + r] = v;
+      }
+    };
     for (int b0 = 0; b0 < B; b0 += Bc) {
       const int nb = min(Bc, B - b0);
-      const int na = 2 * nb * Cinp, nt = 2 * nb * Coutp;
-      float* ta = smd;                                  // [32][na + 1]  x of this batch chunk
-      float* tb = smd + 32 * (2 * Bc * Cinp + 1);       // [32][nt + 1]  g of this batch chunk (all o: rows are contiguous)
+      const int na = 2 * nb * nci, nt = 2 * nb * nco;
       __syncthreads();
-      stage(ta, spa, RSi, b0 * 2 * Cinp, na);
-      stage(tb, spg, RSo, b0 * 2 * Coutp, nt);
+      stage_ch(ta, spa, RSi, Cinp, b0, nb, i0, nci);
+      stage_ch(tb, spg, RSo, Coutp, b0, nb, o0, nco);
       __syncthreads();
-      for (int idx = threadIdx.y; idx < Cin * nco; idx += 8) {
-        const int i = idx / nco, o = o0 + idx - i * nco;
+      for (int idx = threadIdx.y; idx < nci * nco; idx += 8) {
+        const int i = idx / nco, o = idx - i * nco;
         float re = 0.f, im = 0.f;
         for (int bb = 0; bb < nb; ++bb) {
-          const float xr = ta[mloc * (na + 1) + (bb * 2) * Cinp + i], xi = ta[mloc * (na + 1) + (bb * 2 + 1) * Cinp + i];
-          const float gr = tb[mloc * (nt + 1) + (bb * 2) * Coutp + o], gi = tb[mloc * (nt + 1) + (bb * 2 + 1) * Coutp + o];
+          const float xr = ta[mloc * (na + 1) + (bb * 2) * nci + i], xi = ta[mloc * (na + 1) + (bb * 2 + 1) * nci + i];
+          const float gr = tb[mloc * (nt + 1) + (bb * 2) * nco + o], gi = tb[mloc * (nt + 1) + (bb * 2 + 1) * nco + o];
           re += xr * gr + xi * gi;
           im += xr * gi - xi * gr;
         }
         if (m < M) {
-          float2* dst = gw + ((long long)i * Cout + o) * LM + (long long)l * M + m;
+          float2* dst = gw + ((long long)(i0 + i) * Cout + o0 + o) * LM + (long long)l * M + m;
           if (b0 > 0) {                                 // same thread wrote it in the previous pass
             const float2 prev = *dst;
             re += prev.x;
@@ -524,24 +531,12 @@ int sfno_c64_to_xm(const void* in_c64, int B, int C, int nlat, int mmax, float* 
 }
 int sfno_dhconv_pack_weight(const void* w_c64, int Cin, int Cout, int L, float* wp, void* stream) {
   const int Cinp = (Cin + 3) & ~3;
-  if (wpack_tile() == 32) {                        // 16 KB tile: can share an SM with a persistent GEMM CTA (wpack.cuh)
-    dim3 grid((L + 31) / 32, (Cinp + wpack::kTI - 1) / wpack::kTI, Cout);
-    wpack::pack_weight_tl_kernel<32><<<grid, 256, 0, (cudaStream_t)stream>>>((const float2*)w_c64, wp, Cin, Cout, L);
-    SFNO_LAUNCHED();
-    return 0;
-  }
   dim3 grid((L + kWT - 1) / kWT, (Cinp + kWT - 1) / kWT, Cout);
   pack_weight_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const float2*)w_c64, wp, Cin, Cout, L);
   SFNO_LAUNCHED();
   return 0;
 }
 int sfno_dhconv_unpack_wgrad(const float* gwp, int Cin, int Cout, int L, void* gw_c64, void* stream) {
-  if (wpack_tile() == 32) {
-    dim3 grid32((L + 31) / 32, (Cin + wpack::kTI - 1) / wpack::kTI, Cout);
-    wpack::unpack_wgrad_tl_kernel<32><<<grid32, 256, 0, (cudaStream_t)stream>>>(gwp, (float2*)gw_c64, Cin, Cout, L);
-    SFNO_LAUNCHED();
-    return 0;
-  }
   dim3 grid((L + kWT - 1) / kWT, (Cin + kWT - 1) / kWT, Cout);
   unpack_wgrad_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(gwp, (float2*)gw_c64, Cin, Cout, L);
   SFNO_LAUNCHED();
@@ -589,13 +584,9 @@ int sfno_diag_contract(int mode, const float* sp_a, const void* w_or_spb, void* 
   int Bc = std::min(B, kDiagBc), Cc = 0, nz = 0;
   size_t smem = 0;
   if (mode == 2) {
-    for (; Bc >= 1; --Bc) {
-      smem = (size_t)32 * (2 * Bc * Cinp + 2 * Bc * Coutp + 2) * 4;
-      if (smem <= cap) break;
-    }
-    SFNO_CHECK(Bc >= 1, "diagonal contraction: Cin + Cout too large for the shared-memory tile (> 799)");
-    Cc = std::min(Cout, 64);                       // output-channel chunk per CTA (only splits the work)
-    nz = (Cout + Cc - 1) / Cc;
+    Cc = 64;                                       // output channels per CTA: 32*(2*4*128 + 2*4*64 + 2)*4 B = 197 KB
+    smem = (size_t)32 * (2 * Bc * kDiagCi + 2 * Bc * Cc + 2) * 4;
+    nz = ((Cin + kDiagCi - 1) / kDiagCi) * ((Cout + Cc - 1) / Cc);
   } else {
     const int Credp = mode == 0 ? Cinp : Coutp, Cresp = mode == 0 ? Coutp : Cinp;
     for (; Bc >= 1 && !Cc; --Bc) {

@@ -496,7 +496,7 @@ class PolarSpectralConvFunction(torch.autograd.Function):
     module's cache.  Backward is the adjoint chain with the same four exchanges in the reverse roles."""
 
     @staticmethod
-    def forward(ctx, x, weight, mod):
+    def forward(ctx, x, weight, mod, wp):
         fwd, inv = mod.forward_transform, mod.inverse_transform
         B, Cin, Cout = x.shape[0], mod.in_channels, mod.out_channels
         M = mod.modes_lon
@@ -507,7 +507,6 @@ class PolarSpectralConvFunction(torch.autograd.Function):
         residual = None
         if mod.scale_residual:
             residual = _polar_synthesis_sp(sp_l, B, Cin, inv, "one", x.dtype)
-        wp = mod._packed_weight(weight)
         sp2_l = ops.dhconv_fwd(sp_l, wp, B, Cin, Cout, Lloc, M, l0, 0, round_tf32=True)
         y = _polar_synthesis_sp(sp2_l, B, Cout, inv, "one", x.dtype)
         ctx.mod, ctx.in_dtype, ctx.dims = mod, x.dtype, (B, Cin, Cout, Lloc, M, l0)
@@ -532,7 +531,7 @@ class PolarSpectralConvFunction(torch.autograd.Function):
                 gr_l, _ = _polar_analysis_sp(gres, inv, "irfft_adj", round_tf32=True)
                 ops.sp_band_add_(gsp_l, gr_l, B, Cin, Lloc, M, l0)
             gx = _polar_synthesis_sp(gsp_l, B, Cin, fwd, "rfft_adj", ctx.in_dtype)
-        return gx, gw, None
+        return gx, gw, None, None
 
 
 def polar_spectral_conv_ok(mod, x) -> bool:

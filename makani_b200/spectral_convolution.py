@@ -12,7 +12,6 @@ stages, and its backward is a single hand-written adjoint chain (one autograd no
 from __future__ import annotations
 
 import math
-import os
 
 import torch
 import torch.nn as nn
@@ -22,22 +21,6 @@ from . import ops
 from .sht import InverseRealSHT, RealSHT, _TransformBase
 
 __all__ = ["SpectralConv", "SpectralConvS2"]
-
-
-# Opt-in (MAKANI_B200_OVERLAP_WEIGHTS=1, default off until measured - DESIGN.md 7.1 item 4): run the two pure
-# streaming kernels of the weight path on a side stream, next to the latency-bound persistent kernels of the main
-# stream - the gradient unpack while the rest of the block's backward runs, the weight re-pack (prepack_async) while
-# earlier layers run.  Pair it with SFNO_WPACK_TL=32 so that their CTAs fit beside a GEMM CTA (csrc/wpack.cuh).
-_OVERLAP_WEIGHTS = os.environ.get("MAKANI_B200_OVERLAP_WEIGHTS", "0") == "1"
-_SIDE_STREAMS = {}
-
-
-def _side_stream(device) -> "torch.cuda.Stream":
-    key = torch.device(device).index
-    st = _SIDE_STREAMS.get(key)
-    if st is None:
-        st = _SIDE_STREAMS[key] = torch.cuda.Stream(device=device)
-    return st
 
 
 def _distributed_classes():
@@ -54,7 +37,9 @@ class _SpectralConvFunction(torch.autograd.Function):
     m = 0 Fourier coefficient, a position bias by one pass over y (spectral_convolution.py:143-146)."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias, mod):
+    def forward(ctx, x, weight, bias, mod, wp):
+        # wp: packed dhconv weight, made by the module BEFORE entering the Function (grad mode is off in here, and
+        # whether the weight is being trained decides if the packed copy may come from the cache)
         fwd, inv = mod.forward_transform, mod.inverse_transform
         dev = x.device
         B, Cin = x.shape[0], x.shape[1]
@@ -67,7 +52,6 @@ class _SpectralConvFunction(torch.autograd.Function):
         if mod.scale_residual:
             residual = ops.sp_to_field(pi, sp, B, Cin, inv.nlon, one, x.dtype)
         if mod.operator_type == "dhconv":
-            wp = mod._packed_weight(weight)
             sp2 = ops.dhconv_fwd(sp, wp, B, Cin, Cout, L, M, round_tf32=True)
         else:
             wp = None
@@ -103,7 +87,6 @@ class _SpectralConvFunction(torch.autograd.Function):
         dev = gy.device
         pf, pi = fwd._plan(dev), inv._plan(dev)
         adj = inv._scale(dev, "irfft_adj")
-        unpack_done = None
 
         gbias = None
         if ctx.bias_shape is not None and ctx.needs_input_grad[2]:
@@ -114,19 +97,8 @@ class _SpectralConvFunction(torch.autograd.Function):
         if mod.operator_type == "dhconv":
             if ctx.needs_input_grad[1]:
                 gwp = ops.dhconv_bwd_w(sp, gsp2, B, Cin, Cout, L, M)
-                if _OVERLAP_WEIGHTS:
-                    main, side = torch.cuda.current_stream(), _side_stream(dev)
-                    side.wait_stream(main)                       # gwp is complete on the main stream
-                    with torch.cuda.stream(side):
-                        gw = ops.unpack_wgrad(gwp, Cin, Cout, L)
-                        unpack_done = torch.cuda.Event()
-                        unpack_done.record(side)
-                    gwp.record_stream(side)                      # allocated on main, read on side
-                    gw.record_stream(main)                       # allocated on side, consumed on main
-                    del gwp
-                else:
-                    gw = ops.unpack_wgrad(gwp, Cin, Cout, L)
-                    del gwp
+                gw = ops.unpack_wgrad(gwp, Cin, Cout, L)
+                del gwp
             gsp = ops.dhconv_bwd_x(gsp2, wsaved, B, Cin, Cout, L, M, round_tf32=True) if ctx.needs_input_grad[0] else None
         else:
             if ctx.needs_input_grad[1]:
@@ -140,9 +112,7 @@ class _SpectralConvFunction(torch.autograd.Function):
                 # are defined on the same band of SP; no separate add pass)
                 ops.sht_to_sp(pi, gres, adj, round_tf32=True, out=gsp, accumulate=True)
             gx = ops.sp_to_field(pf, gsp, B, Cin, fwd.nlon, fwd._scale(dev, "rfft_adj"), ctx.in_dtype)
-        if unpack_done is not None:
-            torch.cuda.current_stream().wait_event(unpack_done)   # join: whatever consumes gw runs after the unpack
-        return gx, gw, gbias, None
+        return gx, gw, gbias, None, None
 
 
 class SpectralConv(nn.Module):
@@ -249,12 +219,6 @@ class SpectralConv(nn.Module):
         key = (weight._version, weight.data_ptr(), weight.device)
         cache = self._wp_cache
         training = torch.is_grad_enabled() and weight.requires_grad
-        if cache is not None and cache[0] == key and len(cache) > 2 and cache[2] is not None:
-            cur = torch.cuda.current_stream()                    # packed by prepack_async for exactly this forward
-            cur.wait_event(cache[2])
-            cache[1].record_stream(cur)
-            self._wp_cache = None if training else (key, cache[1])
-            return cache[1]
         if (cache is not None and cache[0] == key and not training
                 and not torch.cuda.is_current_stream_capturing()):
             return cache[1]
@@ -265,23 +229,6 @@ class SpectralConv(nn.Module):
     def invalidate(self):
         """Drop the cached packed weight (inference only; training re-packs every forward)."""
         self._wp_cache = None
-
-    def prepack_async(self):
-        """Start re-packing the dhconv weight on the side stream; the next forward waits for it instead of packing on
-        the main stream.  Call right after the optimizer step (the update must have been enqueued on the current
-        stream): the 283 MB streaming pass then runs beside whatever the main stream does before this layer."""
-        if self.operator_type != "dhconv":
-            return
-        w = self.weight
-        ops._need_cuda(w, "weight")
-        key = (w._version, w.data_ptr(), w.device)
-        side = _side_stream(w.device)
-        side.wait_stream(torch.cuda.current_stream())
-        with torch.cuda.stream(side):
-            wp = ops.pack_weight(w)
-            done = torch.cuda.Event()
-            done.record(side)
-        self._wp_cache = (key, wp, done)
 
     def _fused_ok(self):
         return (isinstance(self.forward_transform, _TransformBase) and isinstance(self.inverse_transform, _TransformBase)
@@ -298,12 +245,14 @@ class SpectralConv(nn.Module):
         ops._need_cuda(x, "SpectralConv input")
         ops.dtype_code(dtype)
         if self._fused_ok():
-            y, residual = _SpectralConvFunction.apply(x.contiguous(), self.weight, getattr(self, "bias", None), self)
+            wp = self._packed_weight(self.weight) if self.operator_type == "dhconv" else None
+            y, residual = _SpectralConvFunction.apply(x.contiguous(), self.weight, getattr(self, "bias", None), self, wp)
             if residual is None:
                 residual = x
         elif self._distributed and not hasattr(self, "bias") and self._polar_fused_ok(x):
             from .distributed import PolarSpectralConvFunction
-            y, residual = PolarSpectralConvFunction.apply(x.contiguous(), self.weight, self)
+            y, residual = PolarSpectralConvFunction.apply(x.contiguous(), self.weight, self,
+                                                          self._packed_weight(self.weight))
             if residual is None:
                 residual = x
         else:

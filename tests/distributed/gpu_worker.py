@@ -140,6 +140,53 @@ def main():
     assert max(norm_errs.values()) < 1e-4, norm_errs                  # fp32 pointwise arithmetic, different summation order
     errs.update({k: v * (TOL / 1e-4) * 0.5 for k, v in norm_errs.items()})   # reported on the common scale below
 
+    # ---- CUDA-graph replay of the h-sharded SpectralConv over peer memory (the reference captures forward + backward,
+    # makani/utils/trainer.py:84-152): the barrier number lives on the device and every captured exchange is preceded
+    # by a barrier, so replays with NEW inputs and ranks skewed in time must reproduce the eager results bit for bit.
+    st = thd.p2p.status()
+    if h > 1 and w == 1 and st["enabled"]:
+        xs = [torch.randn(B, C, dfwd.lat_shapes[ih], nlon, generator=torch.Generator().manual_seed(50 + k + 10 * rank)).to(dev)
+              for k in range(3)]
+        g_loc = gx_full[:, :, sl_lat, sl_lon].contiguous()
+        x_static = xs[0].clone().requires_grad_(True)
+
+        def gstep():
+            x_static.grad = None
+            dconv.weight.grad = None
+            y, _ = dconv(x_static)
+            torch.autograd.backward([y], [g_loc])
+            return y
+
+        eager = []
+        for k in range(3):
+            with torch.no_grad():
+                x_static.copy_(xs[k])
+            y = gstep()
+            eager.append((y.detach().clone(), x_static.grad.clone(), dconv.weight.grad.clone()))
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            gstep()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        dist.barrier()
+        graph = torch.cuda.CUDAGraph()
+        x_static.grad = None
+        dconv.weight.grad = None
+        with torch.cuda.graph(graph):
+            y_g = gstep()
+        for k in (1, 2, 0, 2):
+            with torch.no_grad():
+                x_static.copy_(xs[k])
+            torch.cuda._sleep(int(2e8) * (rank % 2 if k % 2 else (rank + 1) % 2))      # skew the ranks (~0.1 s)
+            graph.replay()
+            torch.cuda.synchronize()
+            ye, gxe, gwe = eager[k]
+            assert torch.equal(y_g, ye), ("graph replay: y differs", k)
+            assert torch.equal(x_static.grad, gxe), ("graph replay: dx differs", k)
+            assert torch.equal(torch.view_as_real(dconv.weight.grad), torch.view_as_real(gwe)), ("graph replay: dw", k)
+        errs["graph_replay"] = 0.0
+
     # h-sharded runs must have gone through the peer-memory exchange unless it was switched off
     st = thd.p2p.status()
     if h > 1 and w == 1:

@@ -177,3 +177,35 @@ def test_chained_step_with_gradient_averaging_gloo():
         s.bind(("127.0.0.1", 0))
         port = s.getsockname()[1]
     mp.spawn(_chained_dp_worker, args=(2, port), nprocs=2, join=True)
+
+
+def _spatial_helpers_worker(rank, world, port):
+    import sys
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        from benchlib import spatial
+        h, polar, replica = spatial.make_groups(world, rank)
+        assert h == world and replica == 0 and dist.get_world_size(group=polar) == world
+        sizes = [3, 2]                                         # uneven shards, like 721 -> 181,181,181,178
+        full = torch.arange(2 * 5 * 4, dtype=torch.float32).reshape(2, 5, 4)
+        off = sum(sizes[:rank])
+        got = spatial._gather_cat(full[:, off:off + sizes[rank]].contiguous(), 1, sizes, polar, h)
+        assert torch.equal(got, full)
+        cfull = torch.complex(full, -full)
+        got = spatial._gather_cat(cfull[:, off:off + sizes[rank]].contiguous(), 1, sizes, polar, h)
+        assert torch.equal(got, cfull)
+    finally:
+        dist.destroy_process_group()
+
+
+def test_spatial_bench_helpers_gloo():
+    """tools/benchlib/spatial.py: polar groups and the uneven gather used by the `parity` key of bench.py --gpus N."""
+    import socket
+    import torch.multiprocessing as mp
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    mp.spawn(_spatial_helpers_worker, args=(2, port), nprocs=2, join=True)

@@ -119,14 +119,3 @@ def test_compat_shim(built_lib):
         for k in [k for k in sys.modules if k.startswith("torch_harmonics")]:
             del sys.modules[k]
         sys.modules.update(saved)
-
-
-def test_wpack_host_emulation(tmp_path):
-    """csrc/wpack.cuh (the 16 KB-tile pack / unpack variant, SFNO_WPACK_TL=32) compiled for the host: every CTA and
-    thread of the grid against a plain loop, TL = 64 and 32, even / odd L, ragged channel counts."""
-    exe = str(tmp_path / "wpack_host_test")
-    subprocess.run(["g++", "-O2", "-std=c++17", "-I/usr/local/cuda/include",
-                    os.path.join(ROOT, "tests", "cpp", "wpack_host_test.cpp"), "-o", exe], check=True)
-    r = subprocess.run([exe], capture_output=True, text=True)
-    assert r.returncode == 0 and "FAILED" not in r.stdout, r.stdout
-    assert r.stdout.count(": ok") == 10

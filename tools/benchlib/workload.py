@@ -8,11 +8,8 @@
 
 chained as inside the model, forward + backward, bf16 spatial tensors - plus the ALGORITHMIC byte counts the
 rooflines are computed against."""
-import os
-
 import torch
 
-_OVERLAP_WEIGHTS = os.environ.get("MAKANI_B200_OVERLAP_WEIGHTS", "0") == "1"
 C_EMBED, L_MODES, M_MODES = 384, 240, 241
 GRID_IN = (721, 1440, "equiangular")
 GRID_INT = (240, 480, "legendre-gauss")
@@ -91,9 +88,6 @@ def gpu_step_chained(blocks, x0, grads):
     x0.grad = None
     outs, gouts = [], []
     x = x0
-    if _OVERLAP_WEIGHTS:               # opt-in A/B: all eight re-packs start on the side stream right away
-        for blk in blocks:
-            blk.prepack_async()
     for blk, (gy, gr) in zip(blocks, grads):
         blk.weight.grad = None
         y, res = blk(x)

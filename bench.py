@@ -364,6 +364,7 @@ def run_ours(args):
     # ---- BASELINE config 4: h-sharded SpectralConv blocks (N >= 2)
     spatial_out = None
     if distributed and not args.no_spatial:
+        sync.remove()                                   # the single-GPU reference times below must not all-reduce
         spatial_out = spatial.timings(dev, rank, h, polar, blocks, steps=6, warmup=2)
         if world > h:
             spatial_out["layout"] = f"{world // h} data-parallel replicas x h = {h}"

@@ -40,4 +40,6 @@ def test_distributed_matches_single_gpu(built_lib, h, w, nlat, nlon, grid, C, lm
     env = dict(os.environ, MAKANI_B200_P2P=p2p, MAKANI_B200_P2P_FUSED_DFT="all")   # fused kernels at 480 and 1440
     res = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env)
     out = res.stdout + res.stderr
-    assert res.returncode == 0 and "DIST_GPU_OK" in out, out[-3000:]
+    if not (res.returncode == 0 and "DIST_GPU_OK" in out):
+        keep = [ln for ln in out.splitlines() if any(k in ln for k in ("Error", "error", "rank", "assert", "DIST_GPU", "File "))]
+        raise AssertionError("\n".join(keep[:60]) + "\n...\n" + out[-1500:])

@@ -141,7 +141,8 @@ def _time(fn, steps, warmup, dev, group):
 
 
 def timings(dev, rank, h, polar, single_blocks, steps=8, warmup=2):
-    """ms per block fwd+bwd on h ranks and on one GPU; `single_blocks` are the plain modules of the DP arm."""
+    """ms per block fwd+bwd on h ranks and on one GPU; `single_blocks` are the plain modules of the DP arm (the caller
+    must have removed the gradient-averaging hooks from them: these runs are single-GPU work, no all-reduce)."""
     import makani_b200 as mk
     import makani_b200.distributed as thd
     C, L, M = W.C_EMBED, W.L_MODES, W.M_MODES

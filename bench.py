@@ -242,15 +242,44 @@ def run_ours(args):
 
     blocks = build_gpu(dev)
 
-    # data-parallel replicas: the only exchange is the weight-gradient all-reduce (DDP's job in the reference,
-    # makani/mpu/mappings.py:104-172); issued per block as soon as its gradient exists so NCCL overlaps the
-    # remaining backward work.
+    # data-parallel replicas: the only exchange is the average of the weight gradients (DDP's job in the reference,
+    # makani/mpu/mappings.py:104-172), started per block as soon as its gradient exists so that it overlaps the
+    # remaining backward work.  On one NVLink node it runs over peer memory with copy engines
+    # (distributed/grad_exchange.py); MAKANI_B200_DP_EXCHANGE=nccl keeps the NCCL all-reduce from autograd hooks.
     from makani_b200.distributed.grad_sync import GradientAverager
-    sync = GradientAverager([blk.weight for blk in blocks]) if distributed else None
-
     grads = make_grads(batch, dtype, dev, chained=True)
     xs_host = make_inputs(batch, dtype, pinned=True, chained=True)
     x_dev = xs_host[0].to(dev).requires_grad_(True)
+    sync, dp_exchange = None, "none (single GPU)"
+    if distributed:
+        from makani_b200.distributed import p2p
+        sync = GradientAverager([blk.weight for blk in blocks])
+        dp_exchange = "NCCL all-reduce (AVG) of view_as_real(weight.grad), from post-accumulate hooks"
+        if os.environ.get("MAKANI_B200_DP_EXCHANGE", "peer") == "peer" and p2p.available(dist.group.WORLD, dev):
+            from makani_b200.distributed.grad_exchange import PeerGradientAverager
+            # parity of the peer-memory exchange against the NCCL all-reduce on the same step (blocks 0 and 7)
+            gpu_step_chained(blocks, x_dev, grads)
+            sync.wait()
+            want = [blocks[i].weight.grad.clone() for i in (0, 7)]
+            sync.remove()
+            sync = PeerGradientAverager(blocks)
+            gpu_step_chained(blocks, x_dev, grads)
+            sync.wait()
+            torch.cuda.synchronize()
+            err = max(float((blocks[i].weight.grad - w).abs().max() / w.abs().max()) for i, w in zip((0, 7), want))
+            errt = torch.tensor([err], device=dev)
+            dist.all_reduce(errt, op=dist.ReduceOp.MAX)
+            del want
+            dp_exchange = ("peer memory: copy-engine reduce-scatter + all-gather of the packed gradient over NVLink "
+                           "(CUDA IPC), averaging kernel + unpack on a communication stream; no NCCL kernel")
+            if parity is None and rank == 0:
+                parity = {}
+            if parity is not None:
+                parity["dp_grad_exchange_vs_nccl_max_rel"] = float(errt)
+            if not float(errt) < 1e-5:
+                parity_ok = False
+                if parity is not None:
+                    parity.setdefault("failed", []).append("dp_grad_exchange")
 
     def step(x=None, g=None):
         out = gpu_step_chained(blocks, x_dev if x is None else x, grads if g is None else g)
@@ -425,7 +454,7 @@ def run_ours(args):
         cfg = base_config(world, batch)
         cfg.update({"l2": f"inputs ({h2d / 1e9:.1f} GB/step), weights (2.27 GB) and intermediates (XM / SP 178-536 MB per kernel) "
                           "are far larger than the 126 MB L2",
-                    "window_mb": float(os.environ.get("MAKANI_B200_WINDOW_MB", "0")),
+                    "window_mb": float(os.environ.get("MAKANI_B200_WINDOW_MB", "0")), "dp_gradient_exchange": dp_exchange,
                     "e2e": "pinned-host input (block 0's field) copied every step on a copy stream, double buffered "
                            "against compute; the step's results (output field, input gradient, weight gradients) stay on "
                            "the device as in a training step - a 16-byte checksum of output and input gradient is read back",

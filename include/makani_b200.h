@@ -217,6 +217,19 @@ int sfno_rows_scatter(const float* src, const sfno_copy_desc* descs_host, int nd
  * (+1 per barrier on the same arrays) - NOT replayable from a captured graph.                                    */
 int sfno_peer_barrier(int* const* flags_host, int rank, int size, int epoch, void* stream);
 
+/* ---- data-parallel exchange of the weight gradients over NVLink peer memory --------------------------------
+ * Replaces the NCCL all-reduce that DDP issues for the spectral weights (makani/mpu/mappings.py:104-172; 8 x 283 MB per
+ * step) by copy-engine transfers between CUDA-IPC mapped buffers plus one small kernel, so that the exchange takes no
+ * SMs away from the backward kernels it overlaps with (makani_b200/distributed/grad_exchange.py):
+ *   reduce-scatter : every rank pulls ITS slice of the packed gradient from every peer (sfno_peer_copy, copy engines),
+ *                    then  own slice = (own slice + pulled slices) * scale            (sfno_slices_average)
+ *   all-gather     : every rank pulls the averaged slices of the others                  (sfno_peer_copy)
+ * ordered by sfno_peer_barrier on the communication stream.
+ * sfno_peer_copy     : cudaMemcpyAsync(dst, src, bytes) where either side may be a buffer mapped with sfno_ipc_open
+ * sfno_slices_average: dst[i] = (dst[i] + sum_k srcs_host[k][i]) * scale,  k < nsrc <= 7, n % 4 == 0, 16-byte aligned */
+int sfno_peer_copy(void* dst, const void* src, size_t bytes, void* stream);
+int sfno_slices_average(float* dst, const float* const* srcs_host, int nsrc, long long n, float scale, void* stream);
+
 /* ---- longitude DFT fused with the latitude <-> channel exchange of the h-sharded transforms --------
  * xm_ch_host[p] (p < nranks <= 8) is rank p's channel-sharded XM buffer  [mmax][2B][round_up(chan_shapes[p],4)][Kg]
  * in peer memory (sfno_ipc_open); this rank's nlat_loc latitudes occupy columns [lat_off, lat_off + lat_span) of

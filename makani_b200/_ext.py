@@ -44,6 +44,8 @@ _PROTOTYPES = {
     "sfno_xm_to_c64": (_i, [_vp, _i, _i, _i, _i, _vp, _vp]),
     "sfno_c64_to_xm": (_i, [_vp, _i, _i, _i, _i, _vp, _vp]),
     "sfno_add_bias": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _i, _vp]),
+    "sfno_peer_copy": (_i, [_vp, _vp, C.c_size_t, _vp]),
+    "sfno_slices_average": (_i, [_vp, _vp, _i, _ll, C.c_float, _vp]),
     "sfno_add_inplace": (_i, [_vp, _vp, _ll, _vp]),
     "sfno_xm_add_dc": (_i, [_vp, _i, _i, _i, _vp, _vp]),
     "sfno_workspace_bytes": (C.c_size_t, [_vp, _vp, _i, _i, _i]),

@@ -257,6 +257,28 @@ __global__ void __launch_bounds__(256) add_inplace_kernel(float4* __restrict__ d
   }
 }
 
+// dst = (dst + sum_k src[k]) * scale over n floats: the reduction step of the peer-memory gradient exchange (this
+// rank's slice of the packed weight gradient plus the same slice pulled from every other rank)
+constexpr int kMaxAvgSrc = 7;
+struct AvgArgs {
+  const float4* src[kMaxAvgSrc];
+};
+__global__ void __launch_bounds__(256) slices_average_kernel(float4* __restrict__ dst, const AvgArgs args, int nsrc,
+                                                             long long n4, float scale) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
+    float4 a = dst[i];
+#pragma unroll
+    for (int k = 0; k < kMaxAvgSrc; ++k) {
+      if (k < nsrc) {
+        const float4 b = args.src[k][i];
+        a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+      }
+    }
+    a.x *= scale; a.y *= scale; a.z *= scale; a.w *= scale;
+    dst[i] = a;
+  }
+}
+
 // constant bias as the m = 0 Fourier coefficient: irfft(norm="forward") adds Re XM[0][b][c][k] to every longitude of
 // latitude k, so  y + bias[c]  ==  irfft(XM with XM[0].re += bias[c])  - the add happens in fp32 before the cast to the
 // output dtype, as the reference does (spectral_convolution.py:143-146), and costs B*C*nlat elements instead of a pass
@@ -564,6 +586,33 @@ int sfno_add_inplace(float* dst, const float* src, long long n, void* stream) {
   const int grid = (int)std::min<long long>((n4 + 255) / 256, 148 * 16);
   add_inplace_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(reinterpret_cast<float4*>(dst), reinterpret_cast<const float4*>(src), n4);
   SFNO_LAUNCHED();
+  return 0;
+}
+
+int sfno_slices_average(float* dst, const float* const* srcs_host, int nsrc, long long n, float scale, void* stream) {
+  SFNO_CHECK(dst && (nsrc == 0 || srcs_host) && nsrc >= 0 && nsrc <= kMaxAvgSrc && n % 4 == 0,
+             "sfno_slices_average: bad arguments (nsrc <= 7, n % 4 == 0)");
+  if (n == 0) return 0;
+  AvgArgs args;
+  uintptr_t align = reinterpret_cast<uintptr_t>(dst);
+  for (int k = 0; k < kMaxAvgSrc; ++k) {
+    args.src[k] = reinterpret_cast<const float4*>(srcs_host[k < nsrc ? k : 0]);
+    if (nsrc) align |= reinterpret_cast<uintptr_t>(args.src[k]);
+  }
+  SFNO_CHECK((align & 15) == 0, "sfno_slices_average: 16-byte alignment");
+  const long long n4 = n / 4;
+  // a modest grid: this kernel runs on the communication stream next to the backward kernels of the main stream
+  const int grid = (int)std::min<long long>((n4 + 255) / 256, 32 * 8);
+  slices_average_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(reinterpret_cast<float4*>(dst), args, nsrc, n4, scale);
+  SFNO_LAUNCHED();
+  return 0;
+}
+
+// device-to-device copy that may cross NVLink (src or dst mapped with sfno_ipc_open): runs on a copy engine, no SMs
+int sfno_peer_copy(void* dst, const void* src, size_t bytes, void* stream) {
+  SFNO_CHECK(dst && src, "null argument");
+  if (bytes == 0) return 0;
+  SFNO_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDefault, (cudaStream_t)stream));
   return 0;
 }
 

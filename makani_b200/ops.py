@@ -333,8 +333,11 @@ def dhconv_bwd_x(gsp_out, wp, B, Cin, Cout, lmax, mmax, l_offset=0, m_offset=0, 
     return gsp_in
 
 
-def dhconv_bwd_w(sp_in, gsp_out, B, Cin, Cout, lmax, mmax, l_offset=0, m_offset=0) -> torch.Tensor:
-    gwp = torch.empty(wp_elems(lmax, Cin, Cout), dtype=torch.float32, device=sp_in.device)
+def dhconv_bwd_w(sp_in, gsp_out, B, Cin, Cout, lmax, mmax, l_offset=0, m_offset=0, out=None) -> torch.Tensor:
+    n = wp_elems(lmax, Cin, Cout)
+    if out is not None and (out.numel() != n or out.dtype != torch.float32 or not out.is_contiguous()):
+        raise ValueError("dhconv_bwd_w: `out` must be a contiguous float32 buffer of wp_elems() floats")
+    gwp = out if out is not None else torch.empty(n, dtype=torch.float32, device=sp_in.device)
     _ext.check(_ext.load().sfno_dhconv_bwd_w(_ptr(sp_in), _ptr(gsp_out), _ptr(gwp), B, Cin, Cout, lmax, mmax,
                                              l_offset, m_offset, _stream()), "sfno_dhconv_bwd_w")
     return gwp

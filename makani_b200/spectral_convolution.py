@@ -96,8 +96,16 @@ class _SpectralConvFunction(torch.autograd.Function):
         gw = None
         if mod.operator_type == "dhconv":
             if ctx.needs_input_grad[1]:
-                gwp = ops.dhconv_bwd_w(sp, gsp2, B, Cin, Cout, L, M)
-                gw = ops.unpack_wgrad(gwp, Cin, Cout, L)
+                ex = getattr(mod, "_grad_exchange", None)
+                if ex is not None:
+                    # data-parallel replicas on one NVLink node: the GEMM writes the packed gradient straight into the
+                    # exchange buffer; averaging over the ranks + unpack run on the communication stream and
+                    # `weight.grad` is assigned by ex.wait()  (distributed/grad_exchange.py)
+                    gwp = ops.dhconv_bwd_w(sp, gsp2, B, Cin, Cout, L, M, out=ex.gwp_out())
+                    ex.reduce(mod, gwp)
+                else:
+                    gwp = ops.dhconv_bwd_w(sp, gsp2, B, Cin, Cout, L, M)
+                    gw = ops.unpack_wgrad(gwp, Cin, Cout, L)
                 del gwp
             gsp = ops.dhconv_bwd_x(gsp2, wsaved, B, Cin, Cout, L, M, round_tf32=True) if ctx.needs_input_grad[0] else None
         else:
@@ -208,6 +216,7 @@ class SpectralConv(nn.Module):
             self.bias.sharded_dims_mp = [None, None, "h", "w"]
 
         self._wp_cache = None     # (weight version, data_ptr, packed tensor)
+        self._grad_exchange = None   # set by distributed.grad_exchange.PeerGradientAverager
 
     # Packed planar copy of the dhconv weight (the tensor-core GEMMs cannot read the checkpoint layout).
     # While the weight is being trained (grad mode on and weight.requires_grad) it is re-packed on EVERY forward: an

@@ -206,6 +206,9 @@ int sfno_ipc_open(const unsigned char handle[64], void** ptr);
 int sfno_ipc_close(void* ptr);
 int sfno_ipc_free(void* ptr);
 int sfno_rows_scatter(const float* src, const sfno_copy_desc* descs_host, int ndesc, void* stream);
+/* sfno_rows_scatter's copy on the copy engines (descriptors with tri_l0 < 0 whose strides form a pitched 3-D box: ss0 ==
+ * n1*ss1, ss1 % ss2 == 0, same for ds): one strided 3-D async copy per descriptor, no SMs.                      */
+int sfno_rows_copy_ce(const float* src, const sfno_copy_desc* descs_host, int ndesc, void* stream);
 /* Stream-ordered barrier between the `size` (<= 8) ranks of one node through peer memory: rank r stores the barrier
  * number into slot r of every rank's flag array (flags_host[p] = pointer to rank p's array of >= 64 ints, zero at
  * allocation, mapped with sfno_ipc_open) and waits until all slots of its own array have reached it.
@@ -221,13 +224,19 @@ int sfno_peer_barrier(int* const* flags_host, int rank, int size, int epoch, voi
  * Replaces the NCCL all-reduce that DDP issues for the spectral weights (makani/mpu/mappings.py:104-172; 8 x 283 MB per
  * step) by copy-engine transfers between CUDA-IPC mapped buffers plus one small kernel, so that the exchange takes no
  * SMs away from the backward kernels it overlaps with (makani_b200/distributed/grad_exchange.py):
- *   reduce-scatter : every rank pulls ITS slice of the packed gradient from every peer (sfno_peer_copy, copy engines),
- *                    then  own slice = (own slice + pulled slices) * scale            (sfno_slices_average)
- *   all-gather     : every rank pulls the averaged slices of the others                  (sfno_peer_copy)
+ *   reduce-scatter : own slice = (own slice + the same slice of every peer) * scale     (sfno_slices_average: the peers'
+ *                    slices are read straight from their buffers over NVLink, or pulled first with sfno_peer_copy)
+ *   all-gather     : folded into the layout change packed -> complex64 that backward needs anyway: it reads every
+ *                    averaged slice from its owner                                    (sfno_dhconv_unpack_wgrad_gather)
  * ordered by sfno_peer_barrier on the communication stream.
  * sfno_peer_copy     : cudaMemcpyAsync(dst, src, bytes) where either side may be a buffer mapped with sfno_ipc_open
  * sfno_slices_average: dst[i] = (dst[i] + sum_k srcs_host[k][i]) * scale,  k < nsrc <= 7, n % 4 == 0, 16-byte aligned */
 int sfno_peer_copy(void* dst, const void* src, size_t bytes, void* stream);
+/* sfno_dhconv_unpack_wgrad reading slice k (flat WP offsets [k*slice_floats, (k+1)*slice_floats)) from
+ * gwp_slices_host[k] - BASE pointers of WP-sized buffers, typically one per rank, mapped with sfno_ipc_open: the
+ * all-gather of the averaged slices happens inside the layout change, nothing is gathered into a local packed copy. */
+int sfno_dhconv_unpack_wgrad_gather(const float* const* gwp_slices_host, int nslices, long long slice_floats, int Cin,
+                                    int Cout, int L, void* gw_c64, void* stream);
 int sfno_slices_average(float* dst, const float* const* srcs_host, int nsrc, long long n, float scale, void* stream);
 
 /* ---- longitude DFT fused with the latitude <-> channel exchange of the h-sharded transforms --------

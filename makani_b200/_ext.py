@@ -44,6 +44,7 @@ _PROTOTYPES = {
     "sfno_xm_to_c64": (_i, [_vp, _i, _i, _i, _i, _vp, _vp]),
     "sfno_c64_to_xm": (_i, [_vp, _i, _i, _i, _i, _vp, _vp]),
     "sfno_add_bias": (_i, [_vp, _i, _vp, _i, _i, _i, _i, _i, _vp]),
+    "sfno_dhconv_unpack_wgrad_gather": (_i, [_vp, _i, _ll, _i, _i, _i, _vp, _vp]),
     "sfno_peer_copy": (_i, [_vp, _vp, C.c_size_t, _vp]),
     "sfno_slices_average": (_i, [_vp, _vp, _i, _ll, C.c_float, _vp]),
     "sfno_add_inplace": (_i, [_vp, _vp, _ll, _vp]),
@@ -57,6 +58,7 @@ _PROTOTYPES = {
     "sfno_ipc_close": (_i, [_vp]),
     "sfno_ipc_free": (_i, [_vp]),
     "sfno_rows_scatter": (_i, [_vp, _vp, _i, _vp]),
+    "sfno_rows_copy_ce": (_i, [_vp, _vp, _i, _vp]),
     "sfno_peer_barrier": (_i, [_vp, _i, _i, _i, _vp]),
     "sfno_dft_peer_supported": (_i, [_i, _i]),
     "sfno_dft_fwd_peer": (_i, [_vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp]),

@@ -172,8 +172,19 @@ pack_weight_kernel(const float2* __restrict__ w, float* __restrict__ wp, int Cin
   }
 }
 
+// Source of the packed gradient: one buffer, or (gradient exchange over peer memory) slice k of the flat WP index
+// space lives in bases[k] - this rank's own averaged slice locally, the others in the peers' buffers, read over
+// NVLink.  slice is a multiple of 4 floats, so a 16-byte vector never straddles two slices.
+struct WpSource {
+  const float* bases[8];
+  long long slice;          // floats per slice; 0: everything in bases[0]
+  __device__ __forceinline__ const float* at(long long off) const {
+    return (slice ? bases[off / slice] : bases[0]) + off;
+  }
+};
+
 __global__ void __launch_bounds__(256)
-unpack_wgrad_kernel(const float* __restrict__ gwp, float2* __restrict__ gw, int Cin, int Cout, int L) {
+unpack_wgrad_kernel(const WpSource src, float2* __restrict__ gw, int Cin, int Cout, int L) {
   __shared__ float tr[kWT][kWT], ti[kWT][kWT];
   const int Cinp = (Cin + 3) & ~3, Coutp = (Cout + 3) & ~3;
   const int o = blockIdx.z;
@@ -188,7 +199,7 @@ unpack_wgrad_kernel(const float* __restrict__ gwp, float2* __restrict__ gw, int 
       const int row = lb + 16 * p;
       const int l = l0 + (row >> 1), reim = row & 1;
       v[p] = (iok && l < L)
-                 ? *reinterpret_cast<const float4*>(gwp + (((long long)l * 2 + reim) * Coutp + o) * Cinp + i0 + iq)
+                 ? *reinterpret_cast<const float4*>(src.at((((long long)l * 2 + reim) * Coutp + o) * Cinp + i0 + iq))
                  : make_float4(0.f, 0.f, 0.f, 0.f);
     }
 #pragma unroll
@@ -560,7 +571,22 @@ int sfno_dhconv_pack_weight(const void* w_c64, int Cin, int Cout, int L, float* 
 }
 int sfno_dhconv_unpack_wgrad(const float* gwp, int Cin, int Cout, int L, void* gw_c64, void* stream) {
   dim3 grid((L + kWT - 1) / kWT, (Cin + kWT - 1) / kWT, Cout);
-  unpack_wgrad_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(gwp, (float2*)gw_c64, Cin, Cout, L);
+  WpSource src = {};
+  src.bases[0] = gwp;
+  unpack_wgrad_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(src, (float2*)gw_c64, Cin, Cout, L);
+  SFNO_LAUNCHED();
+  return 0;
+}
+int sfno_dhconv_unpack_wgrad_gather(const float* const* gwp_slices_host, int nslices, long long slice_floats, int Cin,
+                                    int Cout, int L, void* gw_c64, void* stream) {
+  SFNO_CHECK(gwp_slices_host && gw_c64 && nslices >= 1 && nslices <= 8 && slice_floats > 0 && slice_floats % 4 == 0,
+             "sfno_dhconv_unpack_wgrad_gather: bad arguments (1..8 slices of a multiple of 4 floats)");
+  SFNO_CHECK(slice_floats * nslices >= sfno_wp_elems(L, Cin, Cout), "sfno_dhconv_unpack_wgrad_gather: slices do not cover WP");
+  WpSource src = {};
+  for (int k = 0; k < 8; ++k) src.bases[k] = gwp_slices_host[k < nslices ? k : 0];
+  src.slice = slice_floats;
+  dim3 grid((L + kWT - 1) / kWT, (Cin + kWT - 1) / kWT, Cout);
+  unpack_wgrad_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(src, (float2*)gw_c64, Cin, Cout, L);
   SFNO_LAUNCHED();
   return 0;
 }
@@ -718,6 +744,30 @@ int sfno_rows_scatter(const float* src, const sfno_copy_desc* descs_host, int nd
   else
     rows_scatter_kernel<false><<<grid, 256, 0, (cudaStream_t)stream>>>(src, args);
   SFNO_LAUNCHED();
+  return 0;
+}
+
+// Same copy as sfno_rows_scatter (descriptors without the triangular skip) on the COPY ENGINES: one strided 3-D
+// cudaMemcpy3DAsync per descriptor, rows of `len` floats, n2 rows per slice, n0 * n1 slices.  No SM is used, so the
+// transfer can overlap kernels of other streams; whether a copy engine moves short rows over NVLink as fast as the
+// SM kernel does is measured, not assumed (tools/benchlib/spatial.py).
+int sfno_rows_copy_ce(const float* src, const sfno_copy_desc* descs_host, int ndesc, void* stream) {
+  SFNO_CHECK(src && descs_host, "null argument");
+  SFNO_CHECK(ndesc >= 1 && ndesc <= kMaxScatterDesc, "sfno_rows_copy_ce: 1..8 descriptors");
+  for (int i = 0; i < ndesc; ++i) {
+    const sfno_copy_desc& d = descs_host[i];
+    SFNO_CHECK(d.dst && d.n0 > 0 && d.n1 > 0 && d.n2 > 0 && d.len > 0 && d.tri_l0 < 0, "sfno_rows_copy_ce: bad descriptor");
+    SFNO_CHECK(d.ss0 == d.n1 * d.ss1 && d.ds0 == d.n1 * d.ds1 && d.ss1 % d.ss2 == 0 && d.ds1 % d.ds2 == 0 &&
+               d.ss2 >= d.len && d.ds2 >= d.len, "sfno_rows_copy_ce: strides do not form a pitched 3-D box");
+    cudaMemcpy3DParms p = {};
+    p.srcPtr = make_cudaPitchedPtr(const_cast<float*>(src) + d.src_off, (size_t)d.ss2 * 4, (size_t)d.ss2 * 4,
+                                   (size_t)(d.ss1 / d.ss2));
+    p.dstPtr = make_cudaPitchedPtr(static_cast<float*>(d.dst) + d.dst_off, (size_t)d.ds2 * 4, (size_t)d.ds2 * 4,
+                                   (size_t)(d.ds1 / d.ds2));
+    p.extent = make_cudaExtent((size_t)d.len * 4, (size_t)d.n2, (size_t)d.n0 * d.n1);
+    p.kind = cudaMemcpyDefault;
+    SFNO_CUDA(cudaMemcpy3DAsync(&p, (cudaStream_t)stream));
+  }
   return 0;
 }
 

@@ -332,7 +332,7 @@ class _PolarExchange:
         b = pb.next()
         fence.pre_write()
         if arrs[b] is not None:
-            p2p.scatter(src, arrs[b])
+            p2p.scatter(src, arrs[b], boxed=key in ("xm_ch", "xm_lat"))
         fence()
         return pb.local[b][:out_floats]
 

@@ -4,12 +4,14 @@ What it replaces: DDP's all-reduce of the complex64 weight gradients viewed as r
 for the named SFNO config that is 8 x 283 MB per step.  An NCCL all-reduce overlapping the backward pass takes SMs and
 HBM bandwidth away from the backward kernels (round 1: 12.0 -> 16.2 ms per step at 8 GPUs).  Here the exchange is
 
-    reduce-scatter : every rank PULLS its 1/N slice of the packed gradient from each peer with copy-engine transfers
-                     (sfno_peer_copy: cudaMemcpyAsync between CUDA-IPC mapped buffers, no SMs), then one small kernel
-                     (sfno_slices_average) forms  (own + pulled) / N  in place;
-    all-gather     : every rank pulls the averaged slices of the others (copy engines again);
-    unpack         : the layout change packed-planar -> complex64 [Cin, Cout, L] that the backward needs anyway runs
-                     once, on the averaged result.
+    reduce-scatter : one small kernel (sfno_slices_average) forms  (own 1/N slice + the same slice of every peer) / N  in
+                     place, reading the peers' slices straight from their CUDA-IPC mapped buffers over NVLink;
+    all-gather     : folded into the layout change packed-planar -> complex64 [Cin, Cout, L] that the backward needs
+                     anyway (sfno_dhconv_unpack_wgrad_gather): it reads every averaged slice from its owner, so nothing
+                     is gathered into a local packed copy and the gradient crosses local HBM as few times as possible
+                     (the exchange shares HBM with the backward kernels it overlaps with: at 2 GPUs a variant that
+                     pulled the slices with copy engines into staging buffers first - MAKANI_B200_DP_EXCHANGE_COPY=ce,
+                     kept for comparison - moved 1.5 GB per block through local HBM and was no faster than NCCL).
 
 All of it is enqueued on a communication stream the moment `dhconv_bwd_w` of a block has been enqueued, ordered between
 the ranks by `sfno_peer_barrier` (three per block: gradients complete / averaged slices complete / pulls complete),
@@ -22,6 +24,7 @@ through autograd: its contents only exist once the communication stream has run.
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import List
 
 import torch
@@ -59,6 +62,7 @@ class PeerGradientAverager:
         self.fence = p2p.PeerFence(self.group, self.device)                   # own flags: lives on the communication stream
         self.staging = torch.empty((self.size - 1) * self.slice, dtype=torch.float32, device=self.device)
         self.stream = torch.cuda.Stream(device=self.device)
+        self.use_ce = os.environ.get("MAKANI_B200_DP_EXCHANGE_COPY", "direct") == "ce"
         self.free = [None, None]                                  # event: buffer b may be overwritten by the next GEMM
         self.count = 0
         self._ready: List = []
@@ -91,24 +95,34 @@ class PeerGradientAverager:
             for p in range(size):
                 if p == me or hi <= lo:
                     continue
-                dst = self.staging.data_ptr() + k * self.slice * n4
-                _ext.check(lib.sfno_peer_copy(C.c_void_p(dst), C.c_void_p(self.buffers.peer_ptrs[b][p] + lo * n4),
-                                              (hi - lo) * n4, cs), "sfno_peer_copy")
-                srcs.append(dst)
+                src = self.buffers.peer_ptrs[b][p] + lo * n4
+                if self.use_ce:                                    # pull into local staging with a copy engine first
+                    dst = self.staging.data_ptr() + k * self.slice * n4
+                    _ext.check(lib.sfno_peer_copy(C.c_void_p(dst), C.c_void_p(src), (hi - lo) * n4, cs), "sfno_peer_copy")
+                    src = dst
+                srcs.append(src)
                 k += 1
             if hi > lo:
                 arr = (C.c_void_p * max(1, len(srcs)))(*srcs)
                 _ext.check(lib.sfno_slices_average(C.c_void_p(gwp.data_ptr() + lo * n4), C.cast(arr, C.c_void_p), len(srcs),
                                                    hi - lo, 1.0 / size, cs), "sfno_slices_average")
             self.fence()                                           # 2: every rank's averaged slice is complete
-            for p in range(size):
-                plo, phi = self.bounds[p]
-                if p == me or phi <= plo:
-                    continue
-                _ext.check(lib.sfno_peer_copy(C.c_void_p(gwp.data_ptr() + plo * n4),
-                                              C.c_void_p(self.buffers.peer_ptrs[b][p] + plo * n4), (phi - plo) * n4, cs),
-                           "sfno_peer_copy")
-            gw = ops.unpack_wgrad(gwp, self.Cin, self.Cout, self.L)
+            gw = torch.empty((self.Cin, self.Cout, self.L), dtype=torch.complex64, device=self.device)
+            if self.use_ce:
+                for p in range(size):
+                    plo, phi = self.bounds[p]
+                    if p == me or phi <= plo:
+                        continue
+                    _ext.check(lib.sfno_peer_copy(C.c_void_p(gwp.data_ptr() + plo * n4),
+                                                  C.c_void_p(self.buffers.peer_ptrs[b][p] + plo * n4), (phi - plo) * n4, cs),
+                               "sfno_peer_copy")
+                _ext.check(lib.sfno_dhconv_unpack_wgrad(C.c_void_p(gwp.data_ptr()), self.Cin, self.Cout, self.L,
+                                                        C.c_void_p(gw.data_ptr()), cs), "sfno_dhconv_unpack_wgrad")
+            else:                                                  # slice p is read from rank p's buffer (own slice locally)
+                bases = (C.c_void_p * size)(*[self.buffers.peer_ptrs[b][p] for p in range(size)])
+                _ext.check(lib.sfno_dhconv_unpack_wgrad_gather(C.cast(bases, C.c_void_p), size, self.slice, self.Cin,
+                                                               self.Cout, self.L, C.c_void_p(gw.data_ptr()), cs),
+                           "sfno_dhconv_unpack_wgrad_gather")
             self.fence()                                           # 3: nobody reads this buffer any more
             self.free[b] = torch.cuda.Event()
             self.free[b].record(self.stream)

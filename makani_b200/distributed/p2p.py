@@ -185,9 +185,19 @@ def desc_array(descs: List[_ext.CopyDesc]):
     return (_ext.CopyDesc * len(descs))(*descs)
 
 
-def scatter(src: torch.Tensor, arr):
-    """arr: ctypes array of sfno_copy_desc (desc_array); one kernel moves every row to its owner."""
+# MAKANI_B200_P2P_COPY=ce moves the exchanges whose rows form a plain strided box (the two XM exchanges: latitude <->
+# channel) with the copy engines (sfno_rows_copy_ce) instead of the SM kernel; default "sm" (measured)
+_COPY = os.environ.get("MAKANI_B200_P2P_COPY", "sm")
+
+
+def scatter(src: torch.Tensor, arr, boxed: bool = False):
+    """arr: ctypes array of sfno_copy_desc (desc_array); one kernel moves every row to its owner.  boxed: the
+    descriptors are plain strided boxes (no triangular skip), eligible for the copy-engine variant."""
     stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
-    _ext.check(_ext.load().sfno_rows_scatter(C.c_void_p(src.data_ptr()), C.cast(arr, C.c_void_p), len(arr), stream),
-               "sfno_rows_scatter")
+    if boxed and _COPY == "ce":
+        _ext.check(_ext.load().sfno_rows_copy_ce(C.c_void_p(src.data_ptr()), C.cast(arr, C.c_void_p), len(arr), stream),
+                   "sfno_rows_copy_ce")
+    else:
+        _ext.check(_ext.load().sfno_rows_scatter(C.c_void_p(src.data_ptr()), C.cast(arr, C.c_void_p), len(arr), stream),
+                   "sfno_rows_scatter")
     _STATUS["exchanges"] += 1

@@ -55,6 +55,14 @@ def _d_pack(a):          # w, Cin, Cout, L, wp, stream
     return dict(Cin=a[1], Cout=a[2], L=a[3])
 
 
+def _d_gather(a):        # slices, nslices, slice_floats, Cin, Cout, L, gw, stream
+    return dict(Cin=a[3], Cout=a[4], L=a[5], peers=a[1])
+
+
+def _d_avg(a):           # dst, srcs, nsrc, n, scale, stream
+    return dict(n=a[3], nsrc=a[2])
+
+
 CALLS = {
     "sfno_dft_fwd": ("dft_fwd", _d_dft_fwd), "sfno_dft_fwd_win": ("dft_fwd", _d_dft_fwd_win),
     "sfno_dft_inv": ("dft_inv", _d_dft_inv), "sfno_dft_inv_win": ("dft_inv", _d_dft_inv_win),
@@ -63,6 +71,7 @@ CALLS = {
     "sfno_dhconv_fwd": ("dhconv_fwd", _d_dh), "sfno_dhconv_bwd_x": ("dhconv_bwd_x", _d_dh),
     "sfno_dhconv_bwd_w": ("dhconv_bwd_w", _d_dh),
     "sfno_dhconv_pack_weight": ("pack_weight", _d_pack), "sfno_dhconv_unpack_wgrad": ("unpack_wgrad", _d_pack),
+    "sfno_dhconv_unpack_wgrad_gather": ("unpack_wgrad_gather", _d_gather), "sfno_slices_average": ("grad_slice_average", _d_avg),
 }
 
 

@@ -126,8 +126,10 @@ def kernel_bytes(name, a):
         return a["B"] * a["C"] * 8 * (a["K"] * a["M"] + tri(a["L"], a["M"])) + tab
     if name in ("dhconv_fwd", "dhconv_bwd_x", "dhconv_bwd_w"):
         return 8 * a["B"] * (a["Cin"] + a["Cout"]) * tri(a["L"], a["M"]) + 8 * a["Cin"] * a["Cout"] * a["L"]
-    if name in ("pack_weight", "unpack_wgrad"):
+    if name in ("pack_weight", "unpack_wgrad", "unpack_wgrad_gather"):
         return 16 * a["Cin"] * a["Cout"] * a["L"]
+    if name == "grad_slice_average":
+        return 4 * a["n"] * (a["nsrc"] + 2)
     return 0
 
 

@@ -244,8 +244,10 @@ def run_ours(args):
 
     # data-parallel replicas: the only exchange is the average of the weight gradients (DDP's job in the reference,
     # makani/mpu/mappings.py:104-172), started per block as soon as its gradient exists so that it overlaps the
-    # remaining backward work.  On one NVLink node it runs over peer memory with copy engines
-    # (distributed/grad_exchange.py); MAKANI_B200_DP_EXCHANGE=nccl keeps the NCCL all-reduce from autograd hooks.
+    # remaining backward work: an NCCL all-reduce from post-accumulate hooks (default), or - MAKANI_B200_DP_EXCHANGE=peer -
+    # the exchange over NVLink peer memory without any NCCL kernel (distributed/grad_exchange.py), whose result is
+    # checked against the NCCL all-reduce first.  Measured equal within 2-3 % at 2 and 4 GPUs
+    # (profiles/r2f_dp_gradient_exchange.txt).
     from makani_b200.distributed.grad_sync import GradientAverager
     grads = make_grads(batch, dtype, dev, chained=True)
     xs_host = make_inputs(batch, dtype, pinned=True, chained=True)
@@ -255,7 +257,7 @@ def run_ours(args):
         from makani_b200.distributed import p2p
         sync = GradientAverager([blk.weight for blk in blocks])
         dp_exchange = "NCCL all-reduce (AVG) of view_as_real(weight.grad), from post-accumulate hooks"
-        if os.environ.get("MAKANI_B200_DP_EXCHANGE", "peer") == "peer" and p2p.available(dist.group.WORLD, dev):
+        if os.environ.get("MAKANI_B200_DP_EXCHANGE", "nccl") == "peer" and p2p.available(dist.group.WORLD, dev):
             from makani_b200.distributed.grad_exchange import PeerGradientAverager
             # parity of the peer-memory exchange against the NCCL all-reduce on the same step (blocks 0 and 7)
             gpu_step_chained(blocks, x_dev, grads)
@@ -270,8 +272,8 @@ def run_ours(args):
             errt = torch.tensor([err], device=dev)
             dist.all_reduce(errt, op=dist.ReduceOp.MAX)
             del want
-            dp_exchange = ("peer memory: copy-engine reduce-scatter + all-gather of the packed gradient over NVLink "
-                           "(CUDA IPC), averaging kernel + unpack on a communication stream; no NCCL kernel")
+            dp_exchange = ("peer memory (CUDA IPC over NVLink): averaging kernel reads the peers' slices of the packed "
+                           "gradient, all-gather folded into the unpack, on a communication stream; no NCCL kernel")
             if parity is None and rank == 0:
                 parity = {}
             if parity is not None:

@@ -18,6 +18,12 @@ the ranks by `sfno_peer_barrier` (three per block: gradients complete / averaged
 and joined by `wait()` before the optimizer.  The packed gradient is written by the GEMM straight into the IPC buffer
 (two alternating buffers: the GEMM of block b+2 waits until every peer has finished pulling block b).
 
+Measured (round 2, profiles/r2f_dp_gradient_exchange.txt): 14.70 ms per step at 2 GPUs and 15.97 ms at 4 against 14.38
+/ 15.85 ms with the NCCL all-reduce (12.0 ms on one GPU) and bit-identical averaged gradients.  The loss against one GPU
+is therefore not NCCL's SM footprint: whichever way the gradients travel, the exchange shares HBM, L2 and NVLink latency
+with the backward kernels it overlaps with, and those run 15 - 30 % slower while it is in flight.  bench.py keeps NCCL as
+the default and selects this exchange with MAKANI_B200_DP_EXCHANGE=peer.
+
 The averaged gradient is assigned to `weight.grad` in `wait()` (added to it if one is already there), not returned
 through autograd: its contents only exist once the communication stream has run.
 """

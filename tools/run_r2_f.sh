@@ -15,5 +15,5 @@ except Exception as e: print('$tag failed',e)
 PY
 }
 run direct MAKANI_B200_DP_EXCHANGE=peer
-run ce MAKANI_B200_DP_EXCHANGE=peer MAKANI_B200_DP_EXCHANGE_COPY=ce
+
 run nccl MAKANI_B200_DP_EXCHANGE=nccl

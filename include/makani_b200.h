@@ -119,6 +119,21 @@ int sfno_dhconv_bwd_x(const float* gsp_out, const float* wp, float* gsp_in, int 
 /* dW[i,o,l] = sum_{b,m} conj(x[b,i,l,m]) * dY[b,o,l,m]   (packed layout WP) */
 int sfno_dhconv_bwd_w(const float* sp_in, const float* gsp_out, float* gwp, int B, int Cin, int Cout,
                       int lmax, int mmax, int l_offset, int m_offset, void* stream);
+/* The same contraction as sfno_dhconv_fwd for callers that may not allocate (code under CUDA graph capture, serving
+ * loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * It calls no cudaMalloc / cudaFree and no allocating library routine; the two things sfno_dhconv_fwd
+ * keeps in allocated device memory (the tile list of the shape, the tile scheduler's counter pair) live in one
+ * file-scope device array of 256 + 32 * SFNO_STATIC_MAX_TILES bytes (0.5 MB) that every GPU loading the library
+ * holds until exit.  Limits: lmax <= SFNO_STATIC_MAX_L and
+ *     sum_l ceil(B * min(mmax, round_up(l + l_offset + 1, 16) - m_offset) / 128) * ceil(Cout / 128) <= SFNO_STATIC_MAX_TILES
+ * (the named config needs 1 056 tiles at B = 1, 5 760 at B = 8, 11 520 at B = 16); beyond them the call returns 1 with a message.
+ * All calls share the array: it is rewritten at the start of every call (in stream order), so calls on one stream
+ * are safe back to back, calls that overlap on the GPU (different streams) race.  Results are bit-identical to
+ * sfno_dhconv_fwd's.                                                                                              */
+#define SFNO_STATIC_MAX_TILES 16384
+#define SFNO_STATIC_MAX_L 1024
+int sfno_dhconv_fwd_static(const float* sp_in, const float* wp, float* sp_out, int B, int Cin, int Cout,
+                           int lmax, int mmax, int l_offset, int m_offset, int round_tf32, void* stream);
 
 /* ---- K3' diagonal contraction (contractions.py:121-127, einsum "bixy,ioxy->boxy"): weights are used once,
  * so this is a bandwidth kernel.  w is complex64 [Cin][Cout][lmax][mmax].

@@ -36,6 +36,7 @@ _PROTOTYPES = {
     "sfno_dhconv_pack_weight": (_i, [_vp, _i, _i, _i, _vp, _vp]),
     "sfno_dhconv_unpack_wgrad": (_i, [_vp, _i, _i, _i, _vp, _vp]),
     "sfno_dhconv_fwd": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
+    "sfno_dhconv_fwd_static": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "sfno_dhconv_bwd_x": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "sfno_dhconv_bwd_w": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "sfno_diag_contract": (_i, [_i, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp]),

@@ -471,4 +471,126 @@ int dhconv_bwd_w(const float* sp_in, const float* gsp_out, float* gwp, int B, in
   return launch<DH_BWDW>(ma, mb, args, stream);
 }
 
+// ------------------------------------------------------------------ dhconv forward without any allocation
+// sfno_dhconv_fwd_static (include/makani_b200.h): the contraction of dhconv_fwd for callers that may not allocate
+// (CUDA-graph capture, serving loops).  What dhconv_fwd keeps in cudaMalloc'ed memory - the tile list of the shape and
+// the {next tile, finished CTAs} pair of the dynamic scheduler - lives here in one file-scope device array:
+//     bytes [0, 256)   : the scheduler pair (two ints, rest unused)
+//     bytes [256, ...) : up to SFNO_STATIC_MAX_TILES tiles of 32 bytes, written by dhfwd_static_tiles_kernel
+// Every GPU that loads the library holds the array (0.5 MB) until exit.  All calls share it and it keeps the previous
+// call's contents: the tile kernel rewrites the list and zeroes the scheduler pair at the start of every call, in
+// stream order before the GEMM.  Two calls that overlap on the GPU (different streams) race on it.
+constexpr int kStaticMaxTiles = SFNO_STATIC_MAX_TILES;
+constexpr int kStaticMaxL = SFNO_STATIC_MAX_L;
+constexpr int kStaticTileOffset = 256;
+constexpr size_t kStaticBytes = kStaticTileOffset + (size_t)kStaticMaxTiles * sizeof(GemmTile);
+static __device__ __align__(256) unsigned char g_dhfwd_static_scratch[kStaticBytes];
+
+// One block.  Tiles of degree l in the order dhconv_fwd builds them (columns outer, rows inner), degrees from the
+// highest down - the order its cost sort produces for all but the few lowest degrees; the order only affects the
+// load balance, every tile is computed independently.
+__global__ void __launch_bounds__(256)
+dhfwd_static_tiles_kernel(int L, int M, int B, int Cin, int Cout, int l_offset, int m_offset) {
+  __shared__ int start[kStaticMaxL + 1];
+  GemmTile* tiles = reinterpret_cast<GemmTile*>(g_dhfwd_static_scratch + kStaticTileOffset);
+  int* sched = reinterpret_cast<int*>(g_dhfwd_static_scratch);
+  const int row_tiles = (Cout + 127) / 128;
+  auto columns = [&](int l) {                  // sp_mhi(l) * B
+    int hi = (l + l_offset + 1 + 15) / 16 * 16 - m_offset;
+    hi = hi < 0 ? 0 : (hi > M ? M : hi);
+    return hi * B;
+  };
+  for (int p = threadIdx.x; p < L; p += blockDim.x) start[p + 1] = (columns(L - 1 - p) + 127) / 128 * row_tiles;
+  if (threadIdx.x == 0) {
+    start[0] = 0;
+    sched[0] = 0;
+    sched[1] = 0;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0)
+    for (int p = 0; p < L; ++p) start[p + 1] += start[p];
+  __syncthreads();
+  for (int p = threadIdx.x; p < L; p += blockDim.x) {
+    const int l = L - 1 - p, nn = columns(l);
+    int t = start[p];
+    for (int c0 = 0; c0 < nn; c0 += 128) {
+      const int ncols = nn - c0 < 128 ? nn - c0 : 128;
+      for (int r0 = 0; r0 < Cout; r0 += 128) {
+        if (t < kStaticMaxTiles) tiles[t] = GemmTile{l, r0, c0, (ncols + 15) / 16 * 16, 0, (Cin + 7) / 8, c0 + ncols, 0};
+        ++t;
+      }
+    }
+  }
+}
+
+// device address of the array on the current device (the name itself is only a host-side handle of the symbol)
+static int dhfwd_static_scratch(unsigned char** out) {
+  static unsigned char* addr[64];
+  static PerDeviceOnce looked_up;
+  static std::mutex mu;
+  std::lock_guard<std::mutex> lock(mu);
+  const int dev = PerDeviceOnce::device();
+  if (looked_up.needed()) {
+    void* p = nullptr;
+    SFNO_CUDA(cudaGetSymbolAddress(&p, g_dhfwd_static_scratch));
+    SFNO_CHECK(p != nullptr, "cudaGetSymbolAddress returned a null address for the static scratch array");
+    addr[dev] = static_cast<unsigned char*>(p);
+    looked_up.mark();
+  }
+  *out = addr[dev];
+  return 0;
+}
+
+static int dhconv_fwd_static(const float* sp_in, const float* wp, float* sp_out, int B, int Cin, int Cout, int L, int M,
+                             int l_offset, int m_offset, int round_out, cudaStream_t stream) {
+  using Cfg = GemmCfg<DH_FWD>;
+  SFNO_CHECK(B > 0 && Cin > 0 && Cout > 0 && L > 0 && M > 0, "sfno_dhconv_fwd_static: non-positive size");
+  SFNO_CHECK(L <= kStaticMaxL, "sfno_dhconv_fwd_static: lmax " + std::to_string(L) + " exceeds SFNO_STATIC_MAX_L = " +
+                                   std::to_string(kStaticMaxL) + " (use sfno_dhconv_fwd)");
+  long long count = 0;
+  for (int l = 0; l < L; ++l) count += (long long)((sp_mhi(l, l_offset, m_offset, M) * B + 127) / 128) * ((Cout + 127) / 128);
+  SFNO_CHECK(count <= kStaticMaxTiles,
+             "sfno_dhconv_fwd_static: the shape needs " + std::to_string(count) + " tiles, the static scratch holds " +
+                 "SFNO_STATIC_MAX_TILES = " + std::to_string(kStaticMaxTiles) + " (use sfno_dhconv_fwd)");
+  if (count == 0) return 0;
+  unsigned char* scratch = nullptr;
+  if (dhfwd_static_scratch(&scratch)) return 1;
+  CUtensorMap ma, mb;
+  if (wp_map(&ma, wp, Cin, Cout, L, false)) return 1;
+  if (sp_map_kmajor(&mb, sp_in, Cin, B, L, M)) return 1;
+  const int Coutp = round_up(Cout, 4);
+  GemmArgs args;
+  args.out = sp_out;
+  args.tiles = reinterpret_cast<const GemmTile*>(scratch + kStaticTileOffset);
+  args.num_tiles = (int)count;
+  args.row_limit = Cout;
+  args.out_g_stride = (long long)M * B * 2 * Coutp;
+  args.out_col_stride = 2 * Coutp;
+  args.out_im_offset = Coutp;
+  args.round_out = round_out;
+  args.accumulate = args.grp_rows = args.grp_stride = args.grp_off = 0;
+  set_policies(args, false, false, true, true, false, false);
+  args.sched = reinterpret_cast<int*>(scratch);
+  SFNO_CHECK(args.out_col_stride < (1LL << 31) / 32, "output column stride too large for the 32-bit epilogue addressing");
+  static PerDeviceOnce attr_set;
+  if (attr_set.needed()) {
+    SFNO_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<DH_FWD>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+    attr_set.mark();
+  }
+  dhfwd_static_tiles_kernel<<<1, 256, 0, stream>>>(L, M, B, Cin, Cout, l_offset, m_offset);
+  SFNO_LAUNCHED();
+  const int grid = std::min(args.num_tiles, num_sms());
+  // the GEMM reads the list and the scheduler pair only after its griddepcontrol.wait, i.e. after the tile kernel
+  SFNO_CUDA(launch_pdl(gemm_tc_kernel<DH_FWD>, dim3(grid), dim3(kGemmThreads), Cfg::kSmemBytes, stream, ma, mb, args));
+  SFNO_LAUNCHED();
+  return 0;
+}
+
 }  // namespace sfno
+
+extern "C" int sfno_dhconv_fwd_static(const float* sp_in, const float* wp, float* sp_out, int B, int Cin, int Cout,
+                                      int lmax, int mmax, int l_offset, int m_offset, int round_tf32, void* stream) {
+  SFNO_CHECK(sp_in && wp && sp_out, "null argument");
+  return sfno::dhconv_fwd_static(sp_in, wp, sp_out, B, Cin, Cout, lmax, mmax, l_offset, m_offset, round_tf32,
+                                 (cudaStream_t)stream);
+}

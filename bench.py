@@ -14,6 +14,7 @@ One JSON line on stdout (rank 0):
   gpu_baseline          the reference-equivalent torch path (cuFFT + cuBLAS einsums, TF32 allowed) on the same GPU
   cpu_baseline          the oracle port on the host cores, bounded sample (N = 1 only)
   rollout               BASELINE config 5: 40 chained forward passes, eager and CUDA-graph replay (N = 1 only)
+  full_model            the whole SFNO network of the named config, fwd + bwd under bf16 autocast (N = 1 only)
   config3               BASELINE config 3: global batch 8 split over the N GPUs
   parity / spatial      N >= 2: h-sharded transforms + SpectralConv against the fp64 oracle (exit code != 0 on mismatch)
                         and BASELINE config 4 timings (tools/benchlib/spatial.py)
@@ -433,7 +434,7 @@ def run_ours(args):
                 roofline["traffic_ratio"] = roofline["block"]["traffic_ratio"]
     barrier()
 
-    rollout = gpu_base = cpu = None
+    rollout = gpu_base = cpu = full_model = None
     if rank == 0 and world == 1:
         if not args.no_rollout:
             from benchlib import rollout as R
@@ -448,6 +449,21 @@ def run_ours(args):
                 gpu_base["speedup_of_this_repo"] = gpu_base["ms_per_step"] / (ms / args.steps)
             except Exception as e:                          # noqa: BLE001  (an OOM here must not lose the bench line)
                 gpu_base = {"error": f"{type(e).__name__}: {e}"[:300]}
+        if not args.no_full_model:
+            from benchlib import sfno_model
+            torch.cuda.empty_cache()
+            try:
+                full_model = {
+                    "workload": "whole SFNO network of the named config (73 -> 384 encoder, 8 blocks with instance norms, MLPs and "
+                                "skips, decoder, big skip; 721x1440, batch 1), forward + backward under bf16 autocast, random "
+                                "weights; restated from sfnonet.py with the reference's parameter names "
+                                "(tools/benchlib/sfno_model.py - the reference file itself cannot travel to this box); 1x1 "
+                                "convolutions / MLP GELU through torch (cuBLAS/cuDNN), the spectral path through this library",
+                    "fused_norm": sfno_model.measure(dev, steps=5, warmup=2, fused_norm=True),
+                    "torch_norm": sfno_model.measure(dev, steps=5, warmup=2, fused_norm=False)}
+                full_model["spectral_path_share"] = (ms / args.steps) / full_model["fused_norm"]["ms_per_step"]
+            except Exception as e:                          # noqa: BLE001
+                full_model = {"error": f"{type(e).__name__}: {e}"[:300]}
         if not args.no_cpu_baseline:
             cpu = cpu_baseline_sample()
 
@@ -468,7 +484,7 @@ def run_ours(args):
             "e2e": {"value": samples / (ms_e2e * 1e-3), "unit": "samples/s", "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e / args.steps},
             "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
-            "gpu_baseline": gpu_base, "rollout": rollout, "config3": config3, "parity": parity, "spatial": spatial_out,
+            "gpu_baseline": gpu_base, "rollout": rollout, "full_model": full_model, "config3": config3, "parity": parity, "spatial": spatial_out,
             "kernels": kernels,
         }
     if distributed:
@@ -492,6 +508,7 @@ def main():
     ap.add_argument("--no-gpu-baseline", action="store_true")
     ap.add_argument("--no-rollout", action="store_true")
     ap.add_argument("--no-config3", action="store_true")
+    ap.add_argument("--no-full-model", action="store_true")
     ap.add_argument("--no-spatial", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -134,11 +134,11 @@ constexpr int kWT = 64;
 __device__ __forceinline__ int wsw(int i, int l) { return l ^ (i >> 2); }
 
 __global__ void __launch_bounds__(256)
-pack_weight_kernel(const float2* __restrict__ w, float* __restrict__ wp, int Cin, int Cout, int L) {
+pack_weight_kernel(const float2* __restrict__ w, float* __restrict__ wp, int Cin, int Cout, int L, int o_fastest) {
   __shared__ float tr[kWT][kWT], ti[kWT][kWT];
   const int Cinp = (Cin + 3) & ~3, Coutp = (Cout + 3) & ~3;
-  const int o = blockIdx.z;
-  const int l0 = blockIdx.x * kWT, i0 = blockIdx.y * kWT;
+  const int o = o_fastest ? blockIdx.x : blockIdx.z;
+  const int l0 = (o_fastest ? blockIdx.z : blockIdx.x) * kWT, i0 = blockIdx.y * kWT;
   const int tid = threadIdx.x;
   {
     const int ll = tid & 63, ib = tid >> 6;           // 64 degrees x 4 rows per pass
@@ -184,11 +184,11 @@ struct WpSource {
 };
 
 __global__ void __launch_bounds__(256)
-unpack_wgrad_kernel(const WpSource src, float2* __restrict__ gw, int Cin, int Cout, int L) {
+unpack_wgrad_kernel(const WpSource src, float2* __restrict__ gw, int Cin, int Cout, int L, int o_fastest) {
   __shared__ float tr[kWT][kWT], ti[kWT][kWT];
   const int Cinp = (Cin + 3) & ~3, Coutp = (Cout + 3) & ~3;
-  const int o = blockIdx.z;
-  const int l0 = blockIdx.x * kWT, i0 = blockIdx.y * kWT;
+  const int o = o_fastest ? blockIdx.x : blockIdx.z;
+  const int l0 = (o_fastest ? blockIdx.z : blockIdx.x) * kWT, i0 = blockIdx.y * kWT;
   const int tid = threadIdx.x;
   {
     const int iq = (tid & 15) * 4, lb = tid >> 4;
@@ -562,18 +562,35 @@ int sfno_c64_to_xm(const void* in_c64, int B, int C, int nlat, int mmax, float* 
   SFNO_LAUNCHED();
   return 0;
 }
+// CTA order of the weight-layout kernels: which index changes fastest between CTAs that run at the same time.
+// 0: degree tiles (the CTAs of one wave cover whole rows of a few (i, o) pairs), 1: output channels (for a fixed i the
+// rows of consecutive o are adjacent in the complex64 tensor).  SFNO_WLAYOUT_ORDER=0|1 for A/B runs.
+static int wlayout_order() {
+  static int v = -1;
+  if (v < 0) {
+    const char* env = getenv("SFNO_WLAYOUT_ORDER");
+    v = (env && env[0] == '1') ? 1 : 0;
+  }
+  return v;
+}
+static dim3 wlayout_grid(int Cin_or_p, int Cout, int L, int order) {
+  const int lt = (L + kWT - 1) / kWT, it = (Cin_or_p + kWT - 1) / kWT;
+  return order ? dim3(Cout, it, lt) : dim3(lt, it, Cout);
+}
 int sfno_dhconv_pack_weight(const void* w_c64, int Cin, int Cout, int L, float* wp, void* stream) {
   const int Cinp = (Cin + 3) & ~3;
-  dim3 grid((L + kWT - 1) / kWT, (Cinp + kWT - 1) / kWT, Cout);
-  pack_weight_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const float2*)w_c64, wp, Cin, Cout, L);
+  const int order = wlayout_order();
+  dim3 grid = wlayout_grid(Cinp, Cout, L, order);
+  pack_weight_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const float2*)w_c64, wp, Cin, Cout, L, order);
   SFNO_LAUNCHED();
   return 0;
 }
 int sfno_dhconv_unpack_wgrad(const float* gwp, int Cin, int Cout, int L, void* gw_c64, void* stream) {
-  dim3 grid((L + kWT - 1) / kWT, (Cin + kWT - 1) / kWT, Cout);
+  const int order = wlayout_order();
+  dim3 grid = wlayout_grid(Cin, Cout, L, order);
   WpSource src = {};
   src.bases[0] = gwp;
-  unpack_wgrad_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(src, (float2*)gw_c64, Cin, Cout, L);
+  unpack_wgrad_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(src, (float2*)gw_c64, Cin, Cout, L, order);
   SFNO_LAUNCHED();
   return 0;
 }
@@ -585,8 +602,9 @@ int sfno_dhconv_unpack_wgrad_gather(const float* const* gwp_slices_host, int nsl
   WpSource src = {};
   for (int k = 0; k < 8; ++k) src.bases[k] = gwp_slices_host[k < nslices ? k : 0];
   src.slice = slice_floats;
-  dim3 grid((L + kWT - 1) / kWT, (Cin + kWT - 1) / kWT, Cout);
-  unpack_wgrad_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(src, (float2*)gw_c64, Cin, Cout, L);
+  const int order = wlayout_order();
+  dim3 grid = wlayout_grid(Cin, Cout, L, order);
+  unpack_wgrad_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(src, (float2*)gw_c64, Cin, Cout, L, order);
   SFNO_LAUNCHED();
   return 0;
 }

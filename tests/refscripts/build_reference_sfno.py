@@ -62,6 +62,22 @@ names_ref = {k: (tuple(v.shape), v.dtype) for k, v in model_ref.state_dict().ite
 assert names == names_ref, set(names) ^ set(names_ref)
 model.load_state_dict(model_ref.state_dict(), strict=True)
 
+# the restated network that bench.py's `full_model` key times on the GPU box (tools/benchlib/sfno_model.py; the
+# reference file cannot travel): same state-dict keys, shapes and dtypes as the reference network, strict load
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))), "tools"))
+from benchlib import sfno_model                                             # noqa: E402
+restated = sfno_model.SFNO(inp_shape=(91, 180), scale_factor=3, inp_chans=5, out_chans=4, embed_dim=16, num_layers=4,
+                           mlp_ratio=2)
+names_restated = {k: (tuple(v.shape), v.dtype) for k, v in restated.state_dict().items()}
+assert names_restated == names_ref, (set(names_restated) ^ set(names_ref))
+restated.load_state_dict(model_ref.state_dict(), strict=True)
+for a_, b_ in zip(restated.blocks, model_ref.blocks):                       # same initial scales (std within 25 %)
+    for n_ in ("outer_skip.weight", "mlp.fwd.0.weight", "mlp.fwd.3.weight", "filter.filter.weight"):
+        pa, pb = a_.get_parameter(n_), b_.get_parameter(n_)
+        ra = float(torch.view_as_real(pa).std() if pa.is_complex() else pa.std())
+        rb = float(torch.view_as_real(pb).std() if pb.is_complex() else pb.std())
+        assert 0.75 < ra / rb < 1.33, (n_, ra, rb)
+
 # block fusion on the reference's own FourierNeuralOperatorBlock instances: parameter names and
 # objects unchanged, norm0 + GELU and norm1 + outer skip rewired, idempotent
 before = {k: v.data_ptr() for k, v in model.state_dict().items()}

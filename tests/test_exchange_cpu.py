@@ -37,7 +37,7 @@ class FakeBuffers:
         return b
 
 
-def fake_scatter(src, arr):
+def fake_scatter(src, arr, boxed=False):
     """sfno_rows_scatter as the header defines it."""
     s = src.numpy().reshape(-1)
     for d in arr:

@@ -14,6 +14,6 @@ python bench.py --impl reference --steps 10 --warmup 3 > gpurun_out/g_reference.
 cut -c1-300 gpurun_out/g_reference.json
 if [ $rc -eq 0 ]; then
   ncu --metrics gpu__time_duration.sum --clock-control none -c 1600 --csv --log-file gpurun_out/g_launches_bench.csv \
-      python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-gpu-baseline --no-rollout --no-config3 > gpurun_out/g_ncu.log 2>&1
+      python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-gpu-baseline --no-rollout --no-config3 --no-full-model > gpurun_out/g_ncu.log 2>&1
   echo "ncu rc=$?"; wc -l gpurun_out/g_launches_bench.csv
 fi

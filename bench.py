@@ -453,15 +453,15 @@ def run_ours(args):
             from benchlib import sfno_model
             torch.cuda.empty_cache()
             try:
-                full_model = {
-                    "workload": "whole SFNO network of the named config (73 -> 384 encoder, 8 blocks with instance norms, MLPs and "
-                                "skips, decoder, big skip; 721x1440, batch 1), forward + backward under bf16 autocast, random "
-                                "weights; restated from sfnonet.py with the reference's parameter names "
-                                "(tools/benchlib/sfno_model.py - the reference file itself cannot travel to this box); 1x1 "
-                                "convolutions / MLP GELU through torch (cuBLAS/cuDNN), the spectral path through this library",
-                    "fused_norm": sfno_model.measure(dev, steps=5, warmup=2, fused_norm=True),
-                    "torch_norm": sfno_model.measure(dev, steps=5, warmup=2, fused_norm=False)}
-                full_model["spectral_path_share"] = (ms / args.steps) / full_model["fused_norm"]["ms_per_step"]
+                full_model = sfno_model.measure(dev, steps=5, warmup=2)
+                full_model["workload"] = (
+                    "whole SFNO network of the named config (73 -> 384 encoder, 8 blocks with instance norms, MLPs and skips, "
+                    "decoder, big skip; 721x1440, batch 1), forward + backward under bf16 autocast, random weights; restated "
+                    "from sfnonet.py with the reference's parameter names (tools/benchlib/sfno_model.py - the reference file "
+                    "itself cannot travel to this box).  torch_glue: torch convolutions / norms / GELU around this library's "
+                    "spectral path; fused_norm: + fused instance norms; fused: + 1x1-convolution stacks as GEMMs on NCHW "
+                    "(library GEMMs) with this library's bias / GELU kernels")
+                full_model["spectral_path_share"] = (ms / args.steps) / full_model["fused"]["ms_per_step"]
             except Exception as e:                          # noqa: BLE001
                 full_model = {"error": f"{type(e).__name__}: {e}"[:300]}
         if not args.no_cpu_baseline:

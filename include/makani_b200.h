@@ -301,6 +301,20 @@ int sfno_instnorm_bwd_apply(const void* g, const void* x, int dtype, int planes,
                             long long hw_total, const float* stats, const float* gamma, const float* beta,
                             const float* bsum, int act, void* dx, void* stream);
 
+
+/* ---- bias + activation around the 1x1 convolutions (the MLP of the block and the
+ * encoder / decoder, makani/models/common/layers.py:86-214 - Conv2d(1x1, bias) -> GELU -> Conv2d(1x1)).  The
+ * convolutions themselves are plain GEMMs on the NCHW tensor viewed as [C][H*W] (library GEMMs, no layout change);
+ * these two calls are the elementwise passes between them, on [planes = B*C] planes of hw contiguous elements:
+ *   sfno_bias_act     : out = act(x + bias[c]), c = plane % C; bias may be NULL; out may alias x.
+ *   sfno_bias_act_bwd : dx = g * act'(x + bias[c]) and partial[plane][SFNO_INSTNORM_SEGMENTS] = partial sums of dx
+ *                       (d bias[c] = sum over the batch and the segments).  act = NONE: x is not read and dx may be
+ *                       NULL (only the sums: the bias gradient of a convolution without activation).            */
+int sfno_bias_act(const void* x, int dtype, int planes, int C, long long hw, const float* bias, int act, void* out,
+                  void* stream);
+int sfno_bias_act_bwd(const void* g, const void* x, int dtype, int planes, int C, long long hw, const float* bias,
+                      int act, void* dx, float* partial, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

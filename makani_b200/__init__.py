@@ -12,10 +12,12 @@ from .sht import RealSHT, InverseRealSHT
 from .spectral_convolution import SpectralConv, SpectralConvS2
 from .instance_norm import FusedInstanceNorm2d, DistributedFusedInstanceNorm2d
 from .block import fuse_block, fuse_model
+from .pointwise_mlp import pointwise_linear, pointwise_mlp, fuse_pointwise
 from . import distributed
 from .compat import install_torch_harmonics_shim
 
 __all__ = ["RealSHT", "InverseRealSHT", "SpectralConv", "SpectralConvS2", "FusedInstanceNorm2d",
-           "DistributedFusedInstanceNorm2d", "fuse_block", "fuse_model", "distributed", "quadrature", "legendre",
+           "DistributedFusedInstanceNorm2d", "fuse_block", "fuse_model", "fuse_pointwise",
+           "pointwise_linear", "pointwise_mlp", "distributed", "quadrature", "legendre",
            "install_torch_harmonics_shim"]
 __version__ = "0.1.0"

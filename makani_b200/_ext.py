@@ -68,6 +68,8 @@ _PROTOTYPES = {
     "sfno_instnorm_apply": (_i, [_vp, _vp, _i, _i, _i, _ll, _vp, _vp, _vp, _i, _vp, _vp]),
     "sfno_instnorm_bwd_stats": (_i, [_vp, _vp, _i, _i, _i, _ll, _vp, _vp, _vp, _i, _vp, _vp]),
     "sfno_instnorm_bwd_apply": (_i, [_vp, _vp, _i, _i, _i, _ll, _ll, _vp, _vp, _vp, _vp, _i, _vp, _vp]),
+    "sfno_bias_act": (_i, [_vp, _i, _i, _i, _ll, _vp, _i, _vp, _vp]),
+    "sfno_bias_act_bwd": (_i, [_vp, _vp, _i, _i, _i, _ll, _vp, _i, _vp, _vp, _vp]),
 }
 
 

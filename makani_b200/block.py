@@ -26,6 +26,7 @@ import types
 import torch.nn as nn
 
 from .instance_norm import DistributedFusedInstanceNorm2d, FusedInstanceNorm2d
+from .pointwise_mlp import fuse_pointwise
 
 __all__ = ["fuse_block", "fuse_model", "fused_block_forward"]
 
@@ -88,8 +89,13 @@ def fused_block_forward(self, x):
     return x
 
 
-def fuse_block(block: nn.Module) -> nn.Module:
-    """In-place rewiring of one block; returns it.  Idempotent."""
+def fuse_block(block: nn.Module, pointwise: bool = True) -> nn.Module:
+    """In-place rewiring of one block; returns it.  Idempotent.  pointwise: also route the block's 1x1 convolutions
+    (``mlp``, ``outer_skip`` / ``inner_skip``) through the GEMM-on-NCHW path of pointwise_mlp.py."""
+    if pointwise:
+        for name in ("mlp", "outer_skip", "inner_skip"):
+            if hasattr(block, name):
+                fuse_pointwise(getattr(block, name))
     if getattr(block, "_makani_b200_fused", False):
         return block
     for name in ("filter", "norm0", "norm1", "drop_path"):
@@ -116,10 +122,15 @@ def fuse_block(block: nn.Module) -> nn.Module:
     return block
 
 
-def fuse_model(model: nn.Module) -> nn.Module:
-    """``fuse_block`` on every element of ``model.blocks`` (SphericalFourierNeuralOperatorNet, sfnonet.py:386-431)."""
+def fuse_model(model: nn.Module, pointwise: bool = True) -> nn.Module:
+    """``fuse_block`` on every element of ``model.blocks`` (SphericalFourierNeuralOperatorNet, sfnonet.py:386-431);
+    with ``pointwise`` also the encoder, the decoder and the big-skip convolution (sfnonet.py:356-363, 451-468)."""
     if not hasattr(model, "blocks"):
         raise TypeError(f"fuse_model: {type(model).__name__} has no .blocks")
     for blk in model.blocks:
-        fuse_block(blk)
+        fuse_block(blk, pointwise=pointwise)
+    if pointwise:
+        for name in ("encoder", "decoder", "residual_transform"):
+            if hasattr(model, name):
+                fuse_pointwise(getattr(model, name))
     return model

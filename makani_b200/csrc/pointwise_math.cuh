@@ -1,15 +1,16 @@
 // GELU arithmetic of the fused instance-norm kernels, host + device (the host build is what
 // tests/cpp/gelu_host_test.cpp checks against std::erf in double precision).
 //
-// Measured on B200 (profiles/pointwise_kernels_r1_run23.log): the kernels without GELU run at 0.79 - 0.96 of the HBM
-// peak, the ones with GELU at 0.44 - 0.59: libdevice's erff (a branchy ~40-instruction routine) makes them issue-bound.
-// pw_erf_fast is the rational approximation 7.1.26 of Abramowitz & Stegun,
+// libdevice's erff (a branchy ~40-instruction routine) makes the GELU kernels issue-bound; pw_erf_fast is the rational
+// approximation 7.1.26 of Abramowitz & Stegun,
 //     erf(x) = 1 - (a1 t + a2 t^2 + a3 t^3 + a4 t^4 + a5 t^5) exp(-x^2),  t = 1 / (1 + p x),  x >= 0,
 // |error| <= 1.5e-7 in exact arithmetic (about 3e-7 in fp32, below one bf16 / fp16 ulp of any GELU value by orders of
 // magnitude and inside the fp32 tolerance of the parity tests): one reciprocal, one exp2, six FMAs, branch-free, and
 // the exp(-x^2) it computes is the Gaussian the derivative needs anyway.
-// Selected at compile time with -DSFNO_FAST_ERF=1; the default stays erff until the variant has been through the GPU
-// parity tests and the microbenchmark (tools/bench_pointwise_kernels.py).
+// Measured on B200 (round 2, profiles/r2_gelu_erf_ab.txt; 384 x 721 x 1440 bf16, fraction of the HBM peak): norm + GELU
+// 0.59 -> 0.64, its backward statistics 0.44 -> 0.57, backward apply 0.57 -> 0.63, bias + GELU 0.58 -> 0.64, its
+// backward 0.54 -> 0.62; all GPU parity tests pass with it (fp32 I/O at 2e-6).  It is therefore the default;
+// -DSFNO_FAST_ERF=0 selects erff (kept for the host accuracy test, which checks both).
 #pragma once
 #include <math.h>
 
@@ -20,7 +21,7 @@
 #endif
 
 #ifndef SFNO_FAST_ERF
-#define SFNO_FAST_ERF 0
+#define SFNO_FAST_ERF 1
 #endif
 
 namespace sfno {

@@ -13,9 +13,9 @@ reference's parameter names, shapes and initial scales, so that a reference chec
 
 tests/refscripts/build_reference_sfno.py builds this class next to the UNMODIFIED reference network (in this container,
 where /root/reference exists) and asserts that the two state dicts have identical keys, shapes and dtypes and that the
-reference's state dict loads strictly.  The 1x1 convolutions and the GELU of the MLPs run through torch (cuBLAS /
-cuDNN library kernels - plain GEMMs); the spectral path and, with fused_norm=True, the instance norms (+ GELU / + skip)
-are this repository's kernels.
+reference's state dict loads strictly.  As built, the 1x1 convolutions, norms and GELUs are torch modules around the
+product's spectral path; makani_b200.fuse_model reroutes them (fused instance norms; 1x1-convolution stacks as library
+GEMMs on the NCHW tensor with this repository's bias / GELU kernels in between).
 """
 import math
 
@@ -129,15 +129,17 @@ class SFNO(nn.Module):
         return x + self.residual_transform(residual)
 
 
-def measure(dev, steps=5, warmup=2, fused_norm=True, batch=1):
+def measure(dev, steps=5, warmup=2, batch=1):
     """One training step of the whole network at the named size: forward + backward under bf16 autocast
     (amp_mode bf16, trainer.py:516-537 `with amp.autocast(...)`), loss = mean squared output (a stand-in for the
-    geometric L2 loss: one reduction over the output), gradients of all parameters; no optimizer update."""
+    geometric L2 loss: one reduction over the output), gradients of all parameters; no optimizer update.  The same
+    model instance is timed three times: as built (torch convolutions, norms and GELU around the product's spectral
+    path), after fuse_model(pointwise=False) (fused instance norms), after fuse_model() (+ the 1x1-convolution stacks
+    as GEMMs on the NCHW tensor with fused bias / GELU kernels)."""
     import makani_b200 as mk
+    from makani_b200 import _ext
     torch.manual_seed(0)
     model = SFNO().to(dev)
-    if fused_norm:
-        mk.fuse_model(model)
     nparams = sum(p.numel() * (2 if p.is_complex() else 1) for p in model.parameters())
     x = torch.randn(batch, 73, 721, 1440, device=dev)
 
@@ -150,24 +152,30 @@ def measure(dev, steps=5, warmup=2, fused_norm=True, batch=1):
         loss.backward()
         return loss
 
-    from makani_b200 import _ext
-    for _ in range(warmup):
-        step()
-    torch.cuda.synchronize()
-    torch.cuda.reset_peak_memory_stats()
-    l0 = _ext.launch_count()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(steps):
-        loss = step()
-    e1.record()
-    torch.cuda.synchronize()
-    ms = e0.elapsed_time(e1) / steps
-    out = {"ms_per_step": ms, "value": batch * 1e3 / ms, "unit": "samples/s", "steps": steps, "warmup": warmup,
-           "batch": batch, "own_launches_per_step": (_ext.launch_count() - l0) // steps,
-           "peak_mem_gb": torch.cuda.max_memory_allocated() / 1e9, "real_parameters": nparams,
-           "loss_finite": bool(torch.isfinite(loss).item()),
-           "instance_norm": "fused kernels of this repository (norm + GELU, norm + skip)" if fused_norm else "torch"}
+    def timed():
+        for _ in range(warmup):
+            step()
+        torch.cuda.synchronize()
+        torch.cuda.reset_peak_memory_stats()
+        l0 = _ext.launch_count()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            loss = step()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / steps
+        return {"ms_per_step": ms, "value": batch * 1e3 / ms, "unit": "samples/s", "steps": steps, "warmup": warmup,
+                "own_launches_per_step": (_ext.launch_count() - l0) // steps,
+                "peak_mem_gb": torch.cuda.max_memory_allocated() / 1e9, "loss": float(loss),
+                "loss_finite": bool(torch.isfinite(loss).item())}
+
+    out = {"batch": batch, "real_parameters": nparams}
+    out["torch_glue"] = timed()
+    mk.fuse_model(model, pointwise=False)
+    out["fused_norm"] = timed()
+    mk.fuse_model(model)
+    out["fused"] = timed()
     del model, x
     torch.cuda.empty_cache()
     return out

@@ -8,7 +8,7 @@ for v in 0 1; do
   make -C makani_b200/csrc EXTRA=-DSFNO_FAST_ERF=$v > /dev/null 2>&1 || { echo "build failed (variant $v)"; exit 1; }
   {
     echo "=== SFNO_FAST_ERF=$v"
-    timeout 120 python -m pytest tests/test_gpu_pointwise.py tests/test_gpu_z_block.py -m gpu -q 2>&1 | tail -3
+    timeout 200 python -m pytest tests/test_gpu_pointwise.py tests/test_gpu_pointwise_mlp.py tests/test_gpu_z_block.py -m gpu -q 2>&1 | tail -3
     timeout 60 python tools/bench_pointwise_kernels.py
   } > gpurun_out/ab_pointwise_$v.log 2>&1
   cat gpurun_out/ab_pointwise_$v.log

@@ -153,17 +153,27 @@ def _prepare(x: torch.Tensor):
     if dt not in (torch.float32, torch.bfloat16, torch.float16):
         raise TypeError(f"makani_b200: unsupported dtype {dt}")
     B, Cn, H, W = x.shape
-    return x.to(dt).contiguous().view(B, Cn, H * W), dt
+    x3 = x.to(dt).contiguous().view(B, Cn, H * W)
+    # 16-bit GEMM operands want leading dimensions that are multiples of 16 bytes: with 73 input channels (the ERA5
+    # variables: encoder, big skip) the library falls back to kernels three times slower.  Zero channels are appended
+    # to x and zero columns to the weight (one extra pass over the 73-channel field, 2 % of the encoder's traffic).
+    if dt != torch.float32 and Cn % 8:
+        x3 = torch.nn.functional.pad(x3, (0, 0, 0, 8 - Cn % 8))
+    return x3, dt
 
 
 def _w2d(w: torch.Tensor, dt, cin: int) -> torch.Tensor:
+    """2-D view of a 1x1 convolution weight in the compute dtype; cin = channels of the (possibly padded) input."""
     if w.dim() == 4:
         if w.shape[2:] != (1, 1):
             raise ValueError(f"only 1x1 convolution weights, got {tuple(w.shape)}")
         w = w.view(w.shape[0], w.shape[1])
+    w = w.to(dt)
+    if dt != torch.float32 and w.shape[1] % 8 and w.shape[1] + 8 - w.shape[1] % 8 == cin:
+        w = torch.nn.functional.pad(w, (0, cin - w.shape[1]))
     if w.shape[1] != cin:
         raise ValueError(f"weight {tuple(w.shape)} does not match {cin} input channels")
-    return w.to(dt)
+    return w
 
 
 def _b32(b):

@@ -125,8 +125,10 @@ def test_fuse_pointwise_leaves_other_modules_alone(mk):
 def test_fused_model_step_matches_the_unfused_network(mk):
     """The restated SFNO network (tools/benchlib/sfno_model.py, reference parameter names) at a small size: fuse_model
     with the pointwise path against the same network on torch convolutions / norms, fp32, values and every gradient.
-    Tolerance 1e-3: both runs go through the same TF32 spectral path, whose operand rounding turns 1e-7 differences of
-    its inputs into occasional 5e-4 differences of single values, and three instance norms re-scale them."""
+    Tolerance 5e-3: an integration check, the tight bounds are in the tests above.  Both runs go through the same
+    TF32 spectral path three times, and its operand rounding amplifies differences of its inputs: swapping only the
+    instance norms for the fused ones (equal to 1e-6) already moves the filter-weight gradients by 6e-4
+    (tools/dbg_model_noise.py on B200)."""
     import os
     import sys
     sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools"))
@@ -153,4 +155,4 @@ def test_fused_model_step_matches_the_unfused_network(mk):
     for n, a, b in zip(names, got, want):
         a, b = (torch.view_as_real(a), torch.view_as_real(b)) if a.is_complex() else (a, b)
         err = float((a.double() - b.double()).norm() / (b.double().norm() + (floor if n != "y" else 0.0)))
-        assert err < 1e-3, (n, err)
+        assert err < 5e-3, (n, err)

@@ -14,6 +14,7 @@ One JSON line on stdout (rank 0):
   gpu_baseline          the reference-equivalent torch path (cuFFT + cuBLAS einsums, TF32 allowed) on the same GPU
   cpu_baseline          the oracle port on the host cores, bounded sample (N = 1 only)
   rollout               BASELINE config 5: 40 chained forward passes, eager and CUDA-graph replay (N = 1 only)
+  packed_master         the same step with the opt-in packed master weights (no re-pack / unpack passes; N = 1 only)
   full_model            the whole SFNO network of the named config, fwd + bwd under bf16 autocast (N = 1 only)
   config3               BASELINE config 3: global batch 8 split over the N GPUs
   parity / spatial      N >= 2: h-sharded transforms + SpectralConv against the fp64 oracle (exit code != 0 on mismatch)
@@ -434,12 +435,39 @@ def run_ours(args):
                 roofline["traffic_ratio"] = roofline["block"]["traffic_ratio"]
     barrier()
 
-    rollout = gpu_base = cpu = full_model = None
+    rollout = gpu_base = cpu = full_model = packed_master = None
     if rank == 0 and world == 1:
         if not args.no_rollout:
             from benchlib import rollout as R
             x_dev.grad = None
             rollout = R.measure(blocks, x_dev.detach(), steps=40)
+        if not args.no_packed_master:
+            # SpectralConv.enable_packed_master(): the trained parameter is the GEMM-layout tensor, so the step has no
+            # weight re-pack and no gradient unpack (16 launches fewer); same chained step otherwise
+            for blk in blocks:
+                blk.enable_packed_master()
+
+            def pstep():
+                for blk in blocks:
+                    blk.weight_packed.grad = None
+                return gpu_step_chained(blocks, x_dev, grads)
+
+            for _ in range(3):
+                pstep()
+            torch.cuda.synchronize()
+            l0 = _ext.launch_count()
+            p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            p0.record()
+            for _ in range(args.steps):
+                pstep()
+            p1.record()
+            torch.cuda.synchronize()
+            pms = p0.elapsed_time(p1) / args.steps
+            packed_master = {"ms_per_step": pms, "value": batch * 1e3 / pms, "unit": "samples/s", "steps": args.steps,
+                             "launches_per_step": (_ext.launch_count() - l0) // args.steps,
+                             "what": "the same chained step with SpectralConv.enable_packed_master() (opt-in): the trained "
+                                     "parameter is the packed planar tensor the GEMMs read, no re-pack / unpack passes; the "
+                                     "tensor cores truncate the fp32 master to TF32 instead of reading a rounded copy"}
         if not args.no_gpu_baseline:
             from benchlib import torch_gpu
             del grads
@@ -460,7 +488,7 @@ def run_ours(args):
                     "from sfnonet.py with the reference's parameter names (tools/benchlib/sfno_model.py - the reference file "
                     "itself cannot travel to this box).  torch_glue: torch convolutions / norms / GELU around this library's "
                     "spectral path; fused_norm: + fused instance norms; fused: + 1x1-convolution stacks as GEMMs on NCHW "
-                    "(library GEMMs) with this library's bias / GELU kernels")
+                    "(library GEMMs) with this library's bias / GELU kernels; fused_packed_master: + SpectralConv.enable_packed_master()")
                 full_model["spectral_path_share"] = (ms / args.steps) / full_model["fused"]["ms_per_step"]
             except Exception as e:                          # noqa: BLE001
                 full_model = {"error": f"{type(e).__name__}: {e}"[:300]}
@@ -484,7 +512,7 @@ def run_ours(args):
             "e2e": {"value": samples / (ms_e2e * 1e-3), "unit": "samples/s", "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e / args.steps},
             "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
-            "gpu_baseline": gpu_base, "rollout": rollout, "full_model": full_model, "config3": config3, "parity": parity, "spatial": spatial_out,
+            "gpu_baseline": gpu_base, "rollout": rollout, "packed_master": packed_master, "full_model": full_model, "config3": config3, "parity": parity, "spatial": spatial_out,
             "kernels": kernels,
         }
     if distributed:
@@ -509,6 +537,7 @@ def main():
     ap.add_argument("--no-rollout", action="store_true")
     ap.add_argument("--no-config3", action="store_true")
     ap.add_argument("--no-full-model", action="store_true")
+    ap.add_argument("--no-packed-master", action="store_true")
     ap.add_argument("--no-spatial", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":

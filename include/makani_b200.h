@@ -107,6 +107,10 @@ int sfno_legendre_synthesis_win(const sfno_plan* plan, const float* sp, int B, i
  * einsum "bixy,iox->boxy" on complex64) as planar-complex TF32 tcgen05 GEMMs, batched over l.   */
 int sfno_dhconv_pack_weight(const void* w_c64 /*[Cin][Cout][L] complex64*/, int Cin, int Cout, int L,
                             float* wp, void* stream);
+/* round_tf32 = 0: the packed copy keeps the fp32 values (a packed MASTER copy that an optimizer updates in place,
+ * SpectralConv.enable_packed_master(); the tensor cores then truncate instead of rounding to nearest);
+ * round_tf32 = 1 is sfno_dhconv_pack_weight.                                                                    */
+int sfno_dhconv_pack_weight_ex(const void* w_c64, int Cin, int Cout, int L, float* wp, int round_tf32, void* stream);
 int sfno_dhconv_unpack_wgrad(const float* gwp, int Cin, int Cout, int L,
                              void* gw_c64 /*[Cin][Cout][L] complex64*/, void* stream);
 /* l_offset / m_offset: global degree / order of local index 0 (non-zero only for the h/w-sharded

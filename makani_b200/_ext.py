@@ -34,6 +34,7 @@ _PROTOTYPES = {
     "sfno_legendre_analysis_win": (_i, [_vp, _vp, _i, _i, _i, _i, _vp, _i, _i, _vp]),
     "sfno_legendre_synthesis_win": (_i, [_vp, _vp, _i, _i, _i, _i, _vp, _vp]),
     "sfno_dhconv_pack_weight": (_i, [_vp, _i, _i, _i, _vp, _vp]),
+    "sfno_dhconv_pack_weight_ex": (_i, [_vp, _i, _i, _i, _vp, _i, _vp]),
     "sfno_dhconv_unpack_wgrad": (_i, [_vp, _i, _i, _i, _vp, _vp]),
     "sfno_dhconv_fwd": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "sfno_dhconv_fwd_static": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),

@@ -134,7 +134,8 @@ constexpr int kWT = 64;
 __device__ __forceinline__ int wsw(int i, int l) { return l ^ (i >> 2); }
 
 __global__ void __launch_bounds__(256)
-pack_weight_kernel(const float2* __restrict__ w, float* __restrict__ wp, int Cin, int Cout, int L, int o_fastest) {
+pack_weight_kernel(const float2* __restrict__ w, float* __restrict__ wp, int Cin, int Cout, int L, int o_fastest,
+                   int round_out) {
   __shared__ float tr[kWT][kWT], ti[kWT][kWT];
   const int Cinp = (Cin + 3) & ~3, Coutp = (Cout + 3) & ~3;
   const int o = o_fastest ? blockIdx.x : blockIdx.z;
@@ -150,8 +151,9 @@ pack_weight_kernel(const float2* __restrict__ w, float* __restrict__ wp, int Cin
     }
 #pragma unroll
     for (int p = 0; p < 16; ++p) {
-      tr[ib + 4 * p][wsw(ib + 4 * p, ll)] = tf32_rn(v[p].x);   // operands of TF32 GEMMs: pre-rounded (pads are exact zeros)
-      ti[ib + 4 * p][wsw(ib + 4 * p, ll)] = tf32_rn(v[p].y);
+      // operands of TF32 GEMMs: pre-rounded (pads are exact zeros); round_out = 0 keeps the fp32 values (packed master copy)
+      tr[ib + 4 * p][wsw(ib + 4 * p, ll)] = round_out ? tf32_rn(v[p].x) : v[p].x;
+      ti[ib + 4 * p][wsw(ib + 4 * p, ll)] = round_out ? tf32_rn(v[p].y) : v[p].y;
     }
   }
   __syncthreads();
@@ -577,13 +579,17 @@ static dim3 wlayout_grid(int Cin_or_p, int Cout, int L, int order) {
   const int lt = (L + kWT - 1) / kWT, it = (Cin_or_p + kWT - 1) / kWT;
   return order ? dim3(Cout, it, lt) : dim3(lt, it, Cout);
 }
-int sfno_dhconv_pack_weight(const void* w_c64, int Cin, int Cout, int L, float* wp, void* stream) {
+int sfno_dhconv_pack_weight_ex(const void* w_c64, int Cin, int Cout, int L, float* wp, int round_tf32, void* stream) {
+  SFNO_CHECK(w_c64 && wp && Cin > 0 && Cout > 0 && L > 0, "sfno_dhconv_pack_weight: bad arguments");
   const int Cinp = (Cin + 3) & ~3;
   const int order = wlayout_order();
   dim3 grid = wlayout_grid(Cinp, Cout, L, order);
-  pack_weight_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const float2*)w_c64, wp, Cin, Cout, L, order);
+  pack_weight_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const float2*)w_c64, wp, Cin, Cout, L, order, round_tf32);
   SFNO_LAUNCHED();
   return 0;
+}
+int sfno_dhconv_pack_weight(const void* w_c64, int Cin, int Cout, int L, float* wp, void* stream) {
+  return sfno_dhconv_pack_weight_ex(w_c64, Cin, Cout, L, wp, 1, stream);
 }
 int sfno_dhconv_unpack_wgrad(const float* gwp, int Cin, int Cout, int L, void* gw_c64, void* stream) {
   const int order = wlayout_order();

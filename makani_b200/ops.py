@@ -301,13 +301,13 @@ def sp_band_add_(dst: torch.Tensor, src: torch.Tensor, B: int, Cn: int, lmax: in
 
 
 # ------------------------------------------------------------------------------------------ dhconv
-def pack_weight(w: torch.Tensor) -> torch.Tensor:
-    """complex64 [Cin, Cout, L] -> WP."""
+def pack_weight(w: torch.Tensor, round_tf32: bool = True) -> torch.Tensor:
+    """complex64 [Cin, Cout, L] -> WP.  round_tf32=False keeps the fp32 values (packed master copy)."""
     _need_cuda(w, "weight")
     Cin, Cout, L = w.shape
     w = w.detach().contiguous()
     wp = torch.empty(wp_elems(L, Cin, Cout), dtype=torch.float32, device=w.device)
-    _ext.check(_ext.load().sfno_dhconv_pack_weight(_ptr(w), Cin, Cout, L, _ptr(wp), _stream()),
+    _ext.check(_ext.load().sfno_dhconv_pack_weight_ex(_ptr(w), Cin, Cout, L, _ptr(wp), int(round_tf32), _stream()),
                "sfno_dhconv_pack_weight")
     return wp
 

@@ -65,6 +65,7 @@ class _SpectralConvFunction(torch.autograd.Function):
             ops.add_bias_(y, bias)
 
         ctx.mod = mod
+        ctx.packed_master = bool(getattr(mod, "_packed_master", False)) and wp is not None
         ctx.in_dtype = x.dtype
         ctx.shape = (B, Cin, Cout, L, M)
         ctx.has_residual = residual is not None
@@ -93,9 +94,13 @@ class _SpectralConvFunction(torch.autograd.Function):
             dims = (0, 2, 3) if ctx.bias_shape[-1] == 1 else (0,)
             gbias = gy.sum(dim=dims, keepdim=True, dtype=torch.float32).to(ctx.bias_dtype).reshape(ctx.bias_shape)
         gsp2 = ops.sht_to_sp(pi, gy, adj, round_tf32=True)
-        gw = None
+        gw = gwp_out = None
         if mod.operator_type == "dhconv":
-            if ctx.needs_input_grad[1]:
+            if ctx.packed_master:
+                # the trained parameter IS the packed tensor: its gradient is what the GEMM writes, no layout change
+                if ctx.needs_input_grad[4]:
+                    gwp_out = ops.dhconv_bwd_w(sp, gsp2, B, Cin, Cout, L, M).view(wsaved.shape)
+            elif ctx.needs_input_grad[1]:
                 ex = getattr(mod, "_grad_exchange", None)
                 if ex is not None:
                     # data-parallel replicas on one NVLink node: the GEMM writes the packed gradient straight into the
@@ -120,7 +125,7 @@ class _SpectralConvFunction(torch.autograd.Function):
                 # are defined on the same band of SP; no separate add pass)
                 ops.sht_to_sp(pi, gres, adj, round_tf32=True, out=gsp, accumulate=True)
             gx = ops.sp_to_field(pf, gsp, B, Cin, fwd.nlon, fwd._scale(dev, "rfft_adj"), ctx.in_dtype)
-        return gx, gw, gbias, None, None
+        return gx, gw, gbias, None, gwp_out
 
 
 class SpectralConv(nn.Module):
@@ -217,6 +222,7 @@ class SpectralConv(nn.Module):
 
         self._wp_cache = None     # (weight version, data_ptr, packed tensor)
         self._grad_exchange = None   # set by distributed.grad_exchange.PeerGradientAverager
+        self._packed_master = False  # enable_packed_master()
 
     # Packed planar copy of the dhconv weight (the tensor-core GEMMs cannot read the checkpoint layout).
     # While the weight is being trained (grad mode on and weight.requires_grad) it is re-packed on EVERY forward: an
@@ -239,6 +245,56 @@ class SpectralConv(nn.Module):
         """Drop the cached packed weight (inference only; training re-packs every forward)."""
         self._wp_cache = None
 
+    # ---- packed master copy (opt-in) ------------------------------------------------------------------------------
+    # Re-packing the weight on every forward and un-packing its gradient on every backward are two pure layout changes
+    # of 283 MB each way per block (15 % of the training step of the named config).  They exist only because the
+    # parameter lives in the checkpoint layout complex64 [Cin, Cout, L] while the GEMMs read planar [L][2][Cout][Cin].
+    # enable_packed_master() turns it around: the trained parameter becomes `weight_packed` (fp32, the GEMMs' layout),
+    # its gradient is what dhconv_bwd_w writes, and `weight` is re-derived only when a state dict is taken.  Any
+    # elementwise optimizer (SGD, Adam, LAMB: complex parameters are updated as view_as_real, i.e. per real number)
+    # performs the same arithmetic on the packed tensor; state dicts keep the reference's key, shape and dtype
+    # (`weight`, complex64 [Cin, Cout, L]; `weight_packed` never appears in them).
+    # One numerical difference: the GEMMs read the fp32 master directly, so the tensor cores truncate the weight to
+    # TF32 where the re-packed copy is rounded to nearest (what cuBLAS does with fp32 operands when TF32 is allowed).
+    def enable_packed_master(self):
+        if self._packed_master:
+            return self
+        if self.operator_type != "dhconv" or not self._fused_ok():
+            raise NotImplementedError("enable_packed_master: dhconv on single-device transforms only")
+        ops._need_cuda(self.weight, "enable_packed_master: weight")
+        Cin, Cout, L = self.weight.shape
+        wp = ops.pack_weight(self.weight.detach(), round_tf32=False)
+        self.weight_packed = nn.Parameter(wp.view(L, 2, -1, ops._rup(Cin, 4)))
+        self.weight_packed.is_shared_mp = list(self.weight.is_shared_mp)
+        self.weight_packed.sharded_dims_mp = ["h", None, None, None]
+        self.weight.requires_grad_(False)
+        self._packed_master = True
+        self._wp_cache = None
+        self._register_state_dict_hook(SpectralConv._packed_state_dict_hook)
+        self._register_load_state_dict_pre_hook(self._packed_load_pre_hook)
+        return self
+
+    def sync_weight_(self):
+        """Refresh `weight` (checkpoint layout) from the packed master copy."""
+        if self._packed_master:
+            Cin, Cout, L = self.weight.shape
+            with torch.no_grad():
+                self.weight.copy_(ops.unpack_wgrad(self.weight_packed.detach().reshape(-1), Cin, Cout, L))
+        return self.weight
+
+    @staticmethod
+    def _packed_state_dict_hook(module, state_dict, prefix, local_metadata):
+        if module._packed_master:
+            state_dict.pop(prefix + "weight_packed", None)
+            module.sync_weight_()          # in place: the entry `weight` already in state_dict aliases the parameter
+        return state_dict
+
+    def _packed_load_pre_hook(self, state_dict, prefix, local_metadata, strict, missing_keys, unexpected_keys, error_msgs):
+        key = prefix + "weight"
+        if self._packed_master and key in state_dict and prefix + "weight_packed" not in state_dict:
+            w = state_dict[key].to(device=self.weight_packed.device, dtype=torch.complex64)
+            state_dict[prefix + "weight_packed"] = ops.pack_weight(w, round_tf32=False).view(self.weight_packed.shape)
+
     def _fused_ok(self):
         return (isinstance(self.forward_transform, _TransformBase) and isinstance(self.inverse_transform, _TransformBase)
                 and type(self.forward_transform) is RealSHT and type(self.inverse_transform) is InverseRealSHT
@@ -254,7 +310,10 @@ class SpectralConv(nn.Module):
         ops._need_cuda(x, "SpectralConv input")
         ops.dtype_code(dtype)
         if self._fused_ok():
-            wp = self._packed_weight(self.weight) if self.operator_type == "dhconv" else None
+            if self._packed_master:
+                wp = self.weight_packed
+            else:
+                wp = self._packed_weight(self.weight) if self.operator_type == "dhconv" else None
             y, residual = _SpectralConvFunction.apply(x.contiguous(), self.weight, getattr(self, "bias", None), self, wp)
             if residual is None:
                 residual = x

@@ -387,3 +387,73 @@ def test_spectral_conv_matches_reference_module_fixtures(mk, name):
         db = torch.from_numpy(z["dbias"])
         e = float((conv.bias.grad.cpu() - db).norm() / db.norm())
         assert e < 1e-5, ("dbias", e)
+
+
+# ------------------------------------------------------------------------------------------------ packed master copy
+def _small_conv(mk, seed=0):
+    torch.manual_seed(seed)
+    nlat, nlon, L, M, C = 24, 48, 24, 25, 12
+    fwd = mk.RealSHT(nlat, nlon, lmax=L, mmax=M, grid="legendre-gauss").to(DEV)
+    inv = mk.InverseRealSHT(nlat, nlon, lmax=L, mmax=M, grid="legendre-gauss").to(DEV)
+    conv = mk.SpectralConv(fwd, inv, C, C, operator_type="dhconv", bias=False, gain=2.0).to(DEV)
+    x = torch.randn(2, C, nlat, nlon, device=DEV)
+    g = torch.randn(2, C, nlat, nlon, device=DEV)
+    return conv, x, g
+
+
+def test_packed_master_copy_matches_the_repacking_path(mk):
+    """SpectralConv.enable_packed_master(): the trained parameter is the GEMM-layout tensor.  The weight gradient does
+    not depend on the weight's rounding, so it must equal the default path's bit for bit (after the layout change);
+    y and dx see the weight truncated instead of rounded to TF32: 1e-3 relative L2 (TOL_T)."""
+    from makani_b200 import ops
+    conv, x, g = _small_conv(mk)
+    xa = x.clone().requires_grad_(True)
+    ya, _ = conv(xa)
+    ya.backward(g)
+    gw_default = conv.weight.grad.clone()
+    keys_default = {k: (tuple(v.shape), v.dtype) for k, v in conv.state_dict().items()}
+    w0 = conv.weight.detach().clone()
+
+    conv.enable_packed_master()
+    assert conv.enable_packed_master() is conv                                  # idempotent
+    assert not conv.weight.requires_grad and conv.weight_packed.requires_grad
+    xb = x.clone().requires_grad_(True)
+    yb, _ = conv(xb)
+    yb.backward(g)
+    Cin, Cout, L = conv.weight.shape
+    gw_packed = ops.unpack_wgrad(conv.weight_packed.grad.reshape(-1), Cin, Cout, L)
+    assert torch.equal(gw_packed, gw_default)
+    assert O.rel_l2(yb.detach().cpu(), ya.detach().cpu()) < 1e-3
+    assert O.rel_l2(xb.grad.cpu(), xa.grad.cpu()) < 1e-3
+
+    # state dict: the reference's key / shape / dtype, exact values, no packed tensor in it
+    sd = conv.state_dict()
+    assert {k: (tuple(v.shape), v.dtype) for k, v in sd.items()} == keys_default
+    assert torch.equal(sd["weight"], w0)
+
+
+def test_packed_master_copy_optimizer_and_checkpoint_round_trip(mk):
+    """One SGD step on the packed parameter equals the step on the complex parameter (elementwise on real numbers);
+    a default module's state dict loads strictly into a packed module and gives the same forward."""
+    conv_a, x, g = _small_conv(mk, seed=1)
+    conv_b, _, _ = _small_conv(mk, seed=1)
+    conv_b.load_state_dict(conv_a.state_dict(), strict=True)
+    conv_b.enable_packed_master()
+    for conv in (conv_a, conv_b):
+        opt = torch.optim.SGD([p for p in conv.parameters() if p.requires_grad], lr=0.1, momentum=0.9)
+        for _ in range(2):
+            opt.zero_grad(set_to_none=True)
+            y, _ = conv(x)
+            y.backward(g)
+            opt.step()
+    wa, wb = conv_a.state_dict()["weight"], conv_b.state_dict()["weight"]
+    assert O.rel_l2(torch.view_as_real(wb).cpu(), torch.view_as_real(wa).cpu()) < 2e-4   # the second step sees y through truncated weights
+
+    conv_c, _, _ = _small_conv(mk, seed=2)
+    conv_c.enable_packed_master()
+    conv_c.load_state_dict(conv_a.state_dict(), strict=True)                    # default checkpoint -> packed module
+    with torch.no_grad():
+        ya, _ = conv_a(x)
+        yc, _ = conv_c(x)
+    assert O.rel_l2(yc.cpu(), ya.cpu()) < 1e-3
+    assert torch.equal(conv_c.state_dict()["weight"], conv_a.state_dict()["weight"])

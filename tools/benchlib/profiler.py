@@ -70,7 +70,8 @@ CALLS = {
     "sfno_legendre_synthesis": ("legendre_synthesis", _d_leg), "sfno_legendre_synthesis_win": ("legendre_synthesis", _d_leg_win),
     "sfno_dhconv_fwd": ("dhconv_fwd", _d_dh), "sfno_dhconv_bwd_x": ("dhconv_bwd_x", _d_dh),
     "sfno_dhconv_bwd_w": ("dhconv_bwd_w", _d_dh),
-    "sfno_dhconv_pack_weight": ("pack_weight", _d_pack), "sfno_dhconv_unpack_wgrad": ("unpack_wgrad", _d_pack),
+    "sfno_dhconv_pack_weight": ("pack_weight", _d_pack), "sfno_dhconv_pack_weight_ex": ("pack_weight", _d_pack),
+    "sfno_dhconv_unpack_wgrad": ("unpack_wgrad", _d_pack),
     "sfno_dhconv_unpack_wgrad_gather": ("unpack_wgrad_gather", _d_gather), "sfno_slices_average": ("grad_slice_average", _d_avg),
 }
 

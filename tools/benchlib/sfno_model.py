@@ -135,7 +135,7 @@ def measure(dev, steps=5, warmup=2, batch=1):
     geometric L2 loss: one reduction over the output), gradients of all parameters; no optimizer update.  The same
     model instance is timed three times: as built (torch convolutions, norms and GELU around the product's spectral
     path), after fuse_model(pointwise=False) (fused instance norms), after fuse_model() (+ the 1x1-convolution stacks
-    as GEMMs on the NCHW tensor with fused bias / GELU kernels)."""
+    as GEMMs on the NCHW tensor with fused bias / GELU kernels), and with SpectralConv.enable_packed_master() on top."""
     import makani_b200 as mk
     from makani_b200 import _ext
     torch.manual_seed(0)
@@ -167,7 +167,7 @@ def measure(dev, steps=5, warmup=2, batch=1):
         ms = e0.elapsed_time(e1) / steps
         return {"ms_per_step": ms, "value": batch * 1e3 / ms, "unit": "samples/s", "steps": steps, "warmup": warmup,
                 "own_launches_per_step": (_ext.launch_count() - l0) // steps,
-                "peak_mem_gb": torch.cuda.max_memory_allocated() / 1e9, "loss": float(loss),
+                "peak_mem_gb": torch.cuda.max_memory_allocated() / 1e9, "loss": float(loss.detach()),
                 "loss_finite": bool(torch.isfinite(loss).item())}
 
     out = {"batch": batch, "real_parameters": nparams}
@@ -176,6 +176,9 @@ def measure(dev, steps=5, warmup=2, batch=1):
     out["fused_norm"] = timed()
     mk.fuse_model(model)
     out["fused"] = timed()
+    for blk in model.blocks:                                   # opt-in: the spectral weights trained in the GEMMs' layout
+        blk.filter.filter.enable_packed_master()
+    out["fused_packed_master"] = timed()
     del model, x
     torch.cuda.empty_cache()
     return out

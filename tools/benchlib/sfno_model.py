@@ -179,6 +179,47 @@ def measure(dev, steps=5, warmup=2, batch=1):
     for blk in model.blocks:                                   # opt-in: the spectral weights trained in the GEMMs' layout
         blk.filter.filter.enable_packed_master()
     out["fused_packed_master"] = timed()
+    # the same step captured once and replayed as a CUDA graph (the reference's `fwdbwd` capture, trainer.py:84-152):
+    # static input, gradients accumulate into static .grad buffers that are zeroed inside the graph
+    try:
+        for p in model.parameters():
+            if p.requires_grad:
+                p.grad = torch.zeros_like(p)
+
+        def gstep():
+            for p in model.parameters():
+                if p.grad is not None:
+                    p.grad.zero_()
+            with torch.autocast("cuda", dtype=torch.bfloat16):
+                y = model(x)
+                loss = (y.float() ** 2).mean()
+            loss.backward()
+            return loss
+
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(2):
+                gstep()
+        torch.cuda.current_stream().wait_stream(side)
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            gloss = gstep()
+        for _ in range(warmup):
+            graph.replay()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            graph.replay()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / steps
+        out["fused_packed_master_graph"] = {"ms_per_step": ms, "value": batch * 1e3 / ms, "unit": "samples/s", "steps": steps,
+                                            "loss": float(gloss.detach()), "loss_finite": bool(torch.isfinite(gloss).item())}
+        del graph
+    except Exception as e:                                      # noqa: BLE001
+        out["fused_packed_master_graph"] = {"error": f"{type(e).__name__}: {e}"[:300]}
     del model, x
     torch.cuda.empty_cache()
     return out

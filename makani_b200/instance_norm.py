@@ -34,7 +34,6 @@ from .ops import _need_cuda, _ptr, _stream, dtype_code
 
 __all__ = ["FusedInstanceNorm2d", "DistributedFusedInstanceNorm2d", "instance_norm_act", "merge_moments"]
 
-_TOTALS = {}
 _ACTS = {"none": _ext.ACT_NONE, None: _ext.ACT_NONE, "gelu": _ext.ACT_GELU}
 
 
@@ -90,7 +89,7 @@ class _InstanceNormAct(torch.autograd.Function):
 
         sharded = group is not None and dist.get_world_size(group=group) > 1
         stats, mv = _stats(x, eps, want_moments=sharded)
-        hw_total = hw
+        ntot = None
         if sharded:
             # merge the ranks' (mean, var, count): tiny [planes] tensors, one all-gather
             R = dist.get_world_size(group=group)
@@ -100,28 +99,26 @@ class _InstanceNormAct(torch.autograd.Function):
             allm = torch.stack(allm, dim=-1)                                   # [planes, 3, R]
             mean, var, n = merge_moments(allm[:, 0], allm[:, 1], allm[:, 2])
             stats = torch.stack([mean, torch.rsqrt(var + eps)], dim=1).contiguous()
-            # elements of the whole instance: fixed per (group, local shape); read back once, then cached, so that
-            # later calls enqueue no host synchronisation (the reference captures the step in a CUDA graph)
-            key = (id(group), H, W)
-            if key not in _TOTALS:
-                _TOTALS[key] = int(round(float(n[0])))
-            hw_total = _TOTALS[key]
+            # elements of the whole instance, per plane, kept ON THE DEVICE (no host read: the reference captures the
+            # step in a CUDA graph); the backward pass folds it into the per-plane sums
+            ntot = n.contiguous()
         out = torch.empty_like(x)
         _ext.check(_ext.load().sfno_instnorm_apply(_ptr(x), _opt(skip), dt, planes, Cn, hw, _ptr(stats), _opt(w32),
                                                    _opt(b32), act, _ptr(out), _stream()), "sfno_instnorm_apply")
-        tensors = [x, stats] + [t for t in (w32, b32) if t is not None]
+        tensors = [x, stats] + [t for t in (w32, b32, ntot) if t is not None]
         ctx.save_for_backward(*tensors)
-        ctx.cfg = (act, group if sharded else None, hw_total, skip is not None, w32 is not None, b32 is not None,
+        ctx.cfg = (act, group if sharded else None, skip is not None, w32 is not None, b32 is not None,
                    None if weight is None else weight.dtype)
         return out
 
     @staticmethod
     def backward(ctx, g):
-        act, group, hw_total, has_skip, has_w, has_b, wdtype = ctx.cfg
+        act, group, has_skip, has_w, has_b, wdtype = ctx.cfg
         saved = list(ctx.saved_tensors)
         x, stats = saved[0], saved[1]
         w32 = saved[2] if has_w else None
         b32 = saved[2 + int(has_w)] if has_b else None
+        ntot = saved[2 + int(has_w) + int(has_b)] if group is not None else None
         B, Cn, H, W = x.shape
         planes, hw = B * Cn, H * W
         dt = dtype_code(x.dtype)
@@ -135,10 +132,13 @@ class _InstanceNormAct(torch.autograd.Function):
         if group is not None:
             bsum = local.clone()
             dist.all_reduce(bsum, group=group)
+            # the kernel divides the sums by its `hw_total` argument; passing the local size and pre-scaling the sums
+            # by hw / n_total (device arithmetic) gives sums / n_total without reading n_total back to the host
+            bsum = (bsum * (float(hw) / ntot).unsqueeze(1)).contiguous()
         gx = gw = gb = None
         if ctx.needs_input_grad[0]:
             gx = torch.empty_like(x)
-            _ext.check(lib.sfno_instnorm_bwd_apply(_ptr(g), _ptr(x), dt, planes, Cn, hw, hw_total, _ptr(stats),
+            _ext.check(lib.sfno_instnorm_bwd_apply(_ptr(g), _ptr(x), dt, planes, Cn, hw, hw, _ptr(stats),
                                                    _opt(w32), _opt(b32), _ptr(bsum), act, _ptr(gx), _stream()),
                        "sfno_instnorm_bwd_apply")
         # affine-parameter gradients: sums over the batch of this rank's per-plane sums.  For a sharded instance they

@@ -486,10 +486,16 @@ def run_ours(args):
                     "whole SFNO network of the named config (73 -> 384 encoder, 8 blocks with instance norms, MLPs and skips, "
                     "decoder, big skip; 721x1440, batch 1), forward + backward under bf16 autocast, random weights; restated "
                     "from sfnonet.py with the reference's parameter names (tools/benchlib/sfno_model.py - the reference file "
-                    "itself cannot travel to this box).  torch_glue: torch convolutions / norms / GELU around this library's "
+                    "itself cannot travel to this box).  reference_equivalent_torch: all torch (cuDNN convolutions, torch norms / GELU, "
+                    "cuFFT + cuBLAS spectral path with TF32 allowed) = what the reference runs on this GPU; torch_glue: torch convolutions / norms / GELU around this library's "
                     "spectral path; fused_norm: + fused instance norms; fused: + 1x1-convolution stacks as GEMMs on NCHW "
                     "(library GEMMs) with this library's bias / GELU kernels; fused_packed_master: + SpectralConv.enable_packed_master()")
                 full_model["spectral_path_share"] = (ms / args.steps) / full_model["fused"]["ms_per_step"]
+                ref_ms = full_model.get("reference_equivalent_torch", {}).get("ms_per_step")
+                if ref_ms:
+                    full_model["speedup_over_reference_equivalent"] = {
+                        "fused": ref_ms / full_model["fused"]["ms_per_step"],
+                        "fused_packed_master": ref_ms / full_model["fused_packed_master"]["ms_per_step"]}
             except Exception as e:                          # noqa: BLE001
                 full_model = {"error": f"{type(e).__name__}: {e}"[:300]}
         if not args.no_cpu_baseline:

@@ -129,6 +129,29 @@ class SFNO(nn.Module):
         return x + self.residual_transform(residual)
 
 
+class TorchSpectralConv(nn.Module):
+    """The reference's SpectralConv.forward (spectral_convolution.py:124-148) on torch library calls: transforms with
+    autocast disabled on x.float(), complex einsum, cast back - tools/benchlib/torch_gpu.py (cuFFT + cuBLAS)."""
+
+    def __init__(self, weight, fwd, inv):
+        super().__init__()
+        self.weight = nn.Parameter(weight.detach().clone())
+        self.fwd_t, self.inv_t = fwd, inv
+
+    def forward(self, x):
+        dtype = x.dtype
+        residual = x
+        x = x.float()
+        with torch.autocast("cuda", enabled=False):
+            x = self.fwd_t.sht(x).contiguous()
+            if self.fwd_t is not self.inv_t:
+                residual = self.inv_t.isht(x).to(dtype)
+        x = torch.einsum("bixy,iox->boxy", x, self.weight).contiguous()
+        with torch.autocast("cuda", enabled=False):
+            x = self.inv_t.isht(x)
+        return x.to(dtype), residual
+
+
 def measure(dev, steps=5, warmup=2, batch=1):
     """One training step of the whole network at the named size: forward + backward under bf16 autocast
     (amp_mode bf16, trainer.py:516-537 `with amp.autocast(...)`), loss = mean squared output (a stand-in for the
@@ -171,6 +194,27 @@ def measure(dev, steps=5, warmup=2, batch=1):
                 "loss_finite": bool(torch.isfinite(loss).item())}
 
     out = {"batch": batch, "real_parameters": nparams}
+    # the all-torch network first: what the unmodified reference runs on this GPU (cuDNN 1x1 convolutions, torch norms
+    # and GELU, cuFFT + cuBLAS spectral path with TF32 allowed as makani/train.py:109-110 sets it)
+    try:
+        from . import torch_gpu
+        tf32 = (torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.allow_tf32)
+        torch.backends.cuda.matmul.allow_tf32 = torch.backends.cudnn.allow_tf32 = True
+        L, M = model.trans.lmax, model.trans.mmax
+        t_big = torch_gpu.TorchSHT(721, 1440, L, M, "equiangular", dev)
+        t_small = torch_gpu.TorchSHT(model.h, model.w, L, M, "legendre-gauss", dev)
+        own = [blk.filter.filter for blk in model.blocks]
+        last = len(own) - 1
+        for i, blk in enumerate(model.blocks):
+            blk.filter.filter = TorchSpectralConv(own[i].weight, t_big if i == 0 else t_small, t_big if i == last else t_small)
+        out["reference_equivalent_torch"] = timed()
+        for blk, conv in zip(model.blocks, own):
+            blk.filter.filter = conv
+        del t_big, t_small
+        torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.allow_tf32 = tf32
+        torch.cuda.empty_cache()
+    except Exception as e:                                      # noqa: BLE001
+        out["reference_equivalent_torch"] = {"error": f"{type(e).__name__}: {e}"[:300]}
     out["torch_glue"] = timed()
     mk.fuse_model(model, pointwise=False)
     out["fused_norm"] = timed()

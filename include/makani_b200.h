@@ -50,6 +50,11 @@ long long sfno_launch_count(void);
  * (constructed at makani/models/networks/sfnonet.py:536-539).  table_host is fp64, rounded once to
  * fp32 (the reference calls .float() on the module).  m_offset is the first global order m held by
  * this table (azimuth-sharded DistributedRealSHT keeps only its m-slab); 0 otherwise.            */
+/* m_offset of a plan whose table has NO l >= m structure (every (l, m) entry is used): the latitude DFT matrices of
+ * the FFT2 transforms (makani/models/common/layers.py:217-280).  The Legendre kernels then skip nothing; callers pass
+ * l_offset = SFNO_DENSE_L_OFFSET to the SP <-> complex64 conversions so that they skip nothing either.          */
+#define SFNO_M_OFFSET_DENSE (-1)
+#define SFNO_DENSE_L_OFFSET (1 << 20)
 int sfno_plan_create(int nlat, int nlon, int lmax, int mmax, int m_offset,
                      const double* table_host, sfno_plan** out);
 int sfno_plan_destroy(sfno_plan* plan);

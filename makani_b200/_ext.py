@@ -86,6 +86,7 @@ class CopyDesc(C.Structure):
 OP_SHT_FWD, OP_SHT_INV, OP_BLOCK_FWD = 0, 1, 2
 INSTNORM_SEGMENTS = 8
 ACT_NONE, ACT_GELU = 0, 1
+M_OFFSET_DENSE, DENSE_L_OFFSET = -1, 1 << 20          # SFNO_M_OFFSET_DENSE / SFNO_DENSE_L_OFFSET
 ABI_VERSION = 3
 
 EXPORTED_SYMBOLS = tuple(_PROTOTYPES)

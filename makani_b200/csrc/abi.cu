@@ -57,7 +57,7 @@ long long sfno_wp_elems(int lmax, int Cin, int Cout) {
 int sfno_plan_create(int nlat, int nlon, int lmax, int mmax, int m_offset, const double* table_host,
                      sfno_plan** out) {
   SFNO_CHECK(out != nullptr && table_host != nullptr, "null argument");
-  SFNO_CHECK(nlat > 0 && nlon > 0 && lmax > 0 && mmax > 0 && m_offset >= 0, "bad sizes");
+  SFNO_CHECK(nlat > 0 && nlon > 0 && lmax > 0 && mmax > 0 && m_offset >= SFNO_M_OFFSET_DENSE, "bad sizes");
   sfno_plan* p = new sfno_plan();
   p->nlat = nlat;
   p->nlon = nlon;

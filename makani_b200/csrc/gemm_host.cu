@@ -251,7 +251,7 @@ int legendre_analysis(const sfno_plan* plan, const float* xm, int B, int C, int 
   TileKey key{current_device(), LEG_ANA, K, L, M, moff, RS, 0, 0};
   if (get_tiles(key, [&](std::vector<GemmTile>& tiles) {
         for (int m = 0; m < M; ++m) {
-          const int n0 = floor_to(m + moff, 16);
+          const int n0 = moff == SFNO_M_OFFSET_DENSE ? 0 : floor_to(m + moff, 16);   // dense table: no l >= m structure
           for (int c0 = n0; c0 < L; c0 += 256) {
             const int ncols = std::min(256, L - c0);
             for (int r0 = 0; r0 < RS; r0 += 128) {
@@ -308,7 +308,7 @@ int legendre_synthesis(const sfno_plan* plan, const float* sp, int B, int C, int
   TileKey key{current_device(), LEG_SYN, K, L, M, moff, RS, 0, 0};
   if (get_tiles(key, [&](std::vector<GemmTile>& tiles) {
         for (int m = 0; m < M; ++m) {
-          const int l0 = std::min(L, floor_to(m + moff, 8));
+          const int l0 = moff == SFNO_M_OFFSET_DENSE ? 0 : std::min(L, floor_to(m + moff, 8));
           const int nkk = (L - l0 + 7) / 8;        // 0 => this m has no degrees: zeros are written
           for (int c0 = 0; c0 < RS; c0 += 256) {
             const int ncols = std::min(256, RS - c0);

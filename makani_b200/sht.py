@@ -45,6 +45,7 @@ class _TransformBase(nn.Module):
     """Shared plumbing: table precompute (fp64 numpy), lazily created device plan, scale vectors."""
 
     _table_name = "weights"
+    _sp_l_offset = 0          # l_offset handed to the SP <-> complex64 conversions (dense tables: skip nothing)
 
     def __init__(self, nlat, nlon, lmax=None, mmax=None, grid="lobatto", norm="ortho", csphase=True):
         super().__init__()
@@ -127,14 +128,14 @@ class _SHTFunction(torch.autograd.Function):
         B, Cn = x.shape[0], x.shape[1]
         sp = ops.sht_to_sp(plan, x, mod._scale(x.device, "fwd"))
         ctx.mod, ctx.in_dtype = mod, x.dtype
-        return ops.sp_to_c64(sp, B, Cn, mod.lmax, mod.mmax)
+        return ops.sp_to_c64(sp, B, Cn, mod.lmax, mod.mmax, l_offset=mod._sp_l_offset)
 
     @staticmethod
     def backward(ctx, g):
         mod = ctx.mod
         plan = mod._plan(g.device)
         B, Cn = g.shape[0], g.shape[1]
-        gsp = ops.c64_to_sp(g.to(torch.complex64))
+        gsp = ops.c64_to_sp(g.to(torch.complex64), l_offset=mod._sp_l_offset)
         gx = ops.sp_to_field(plan, gsp, B, Cn, mod.nlon, mod._scale(g.device, "rfft_adj"), ctx.in_dtype)
         return gx, None
 
@@ -146,7 +147,7 @@ class _ISHTFunction(torch.autograd.Function):
     def forward(ctx, c, mod):
         plan = mod._plan(c.device)
         B, Cn = c.shape[0], c.shape[1]
-        sp = ops.c64_to_sp(c)
+        sp = ops.c64_to_sp(c, l_offset=mod._sp_l_offset)
         ctx.mod = mod
         return ops.sp_to_field(plan, sp, B, Cn, mod.nlon, mod._scale(c.device, "one"), torch.float32)
 
@@ -156,7 +157,7 @@ class _ISHTFunction(torch.autograd.Function):
         plan = mod._plan(g.device)
         B, Cn = g.shape[0], g.shape[1]
         gsp = ops.sht_to_sp(plan, g, mod._scale(g.device, "irfft_adj"))
-        return ops.sp_to_c64(gsp, B, Cn, mod.lmax, mod.mmax), None
+        return ops.sp_to_c64(gsp, B, Cn, mod.lmax, mod.mmax, l_offset=mod._sp_l_offset), None
 
 
 class RealSHT(_TransformBase):

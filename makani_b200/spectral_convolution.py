@@ -179,6 +179,12 @@ class SpectralConv(nn.Module):
             self.nlon_local = self.inverse_transform.nlon
             self._l_offset = 0
             self._m_offset = 0
+            from .fft2 import InverseRealFFT2
+            if isinstance(self.inverse_transform, InverseRealFFT2):
+                # spectral_transform="fft" (sfnonet.py:541-553): Fourier coefficients have no m <= l structure, the
+                # contraction kernels must not skip anything
+                from . import _ext
+                self._l_offset = _ext.DENSE_L_OFFSET
 
         if self.operator_type == "diagonal":
             weight_shape += [self.modes_lat_local, self.modes_lon_local]

@@ -100,4 +100,28 @@ except RuntimeError as e:
     assert "no CPU path" in str(e), e
 else:
     raise AssertionError("forward on a CPU tensor did not raise")
+
+# spectral_transform="fft" (FourierNeuralOperatorNet, sfnonet.py:541-553,648-650): the reference network on the
+# product's RealFFT2 / InverseRealFFT2 (layers.py:217-280) and SpectralConv; same state-dict names as with its own
+sc.SpectralConv = makani_b200.SpectralConv
+common.SpectralConv = makani_b200.SpectralConv
+net.SpectralConv = makani_b200.SpectralConv
+ref_fft2 = (net.RealFFT2, net.InverseRealFFT2)
+net.RealFFT2, net.InverseRealFFT2 = makani_b200.RealFFT2, makani_b200.InverseRealFFT2
+torch.manual_seed(0)
+fno = net.FourierNeuralOperatorNet(**kw)
+assert type(fno.trans_down) is makani_b200.RealFFT2 and type(fno.itrans) is makani_b200.InverseRealFFT2
+assert (fno.trans.lmax, fno.trans.mmax, fno.trans.truncate) == (30, 31, False)
+assert (fno.trans_down.lmax, fno.trans_down.mmax, fno.trans_down.truncate) == (30, 31, True)
+assert all(type(b.filter.filter) is makani_b200.SpectralConv for b in fno.blocks)
+assert all(b.filter.filter._l_offset == makani_b200._ext.DENSE_L_OFFSET for b in fno.blocks)      # dense contraction
+sc.SpectralConv = ref_spectral_conv
+common.SpectralConv = ref_spectral_conv
+net.SpectralConv = ref_spectral_conv
+net.RealFFT2, net.InverseRealFFT2 = ref_fft2
+torch.manual_seed(0)
+fno_ref = net.FourierNeuralOperatorNet(**kw)
+assert ({k: (tuple(v.shape), v.dtype) for k, v in fno.state_dict().items()}
+        == {k: (tuple(v.shape), v.dtype) for k, v in fno_ref.state_dict().items()})
+fno.load_state_dict(fno_ref.state_dict(), strict=True)
 print("OK reference SFNO built on product modules:", len(names), "state-dict entries")

@@ -29,6 +29,61 @@ using fl::cmul;
 using fl::cconj;
 using fl::cscale;
 
+// Optional (-DSFNO_TW_REGS=1): twiddles e^{-2 pi i k / 480} and e^{-2 pi i k / 1440} at k = lane + 16 k2 formed as
+// (table entry of the lane) x (compile-time constant of k2), and the twiddles of the 16 x 15 exchange as powers of one
+// table entry per lane - two packed instructions each instead of an 8-byte shared-memory load (38 percent of the
+// kernels' shared-memory wavefronts are twiddle loads).  Measured on B200 with the packed arithmetic of fft_lane.cuh
+// (profiles/r2t_dft_f32x2_ab.txt): 240x480 forward / inverse 69.6 -> 67.9 / 63.9 -> 61.9 us, 721x1440 464 -> 472 /
+// 424 -> 423 us: the kernels are bound by neither pipe any more but by latency at 16 warps per SM, so the default
+// stays with the table loads.
+#ifndef SFNO_TW_REGS
+#define SFNO_TW_REGS 0
+#endif
+#ifndef SFNO_TW_REGS_TWIST
+#define SFNO_TW_REGS_TWIST 0
+#endif
+// e^{-2 pi i k2 / 30} = w480^(16 k2)  and  e^{-2 pi i k2 / 90} = w1440^(16 k2),  k2 = 0..14.  Switches, not arrays:
+// every call site has a compile-time k2 after unrolling, so they fold to immediates (an array captured by a lambda or
+// indexed in a large unrolled body ended up in local memory).
+FL_HD cf w30c(int k2) {
+  switch (k2) {
+    case 1: return mk(0.9781476007338057f, -0.20791169081775931f);
+    case 2: return mk(0.9135454576426009f, -0.40673664307580015f);
+    case 3: return mk(0.8090169943749475f, -0.5877852522924731f);
+    case 4: return mk(0.6691306063588582f, -0.7431448254773941f);
+    case 5: return mk(0.5000000000000001f, -0.8660254037844386f);
+    case 6: return mk(0.30901699437494745f, -0.9510565162951535f);
+    case 7: return mk(0.10452846326765346f, -0.9945218953682733f);
+    case 8: return mk(-0.10452846326765333f, -0.9945218953682734f);
+    case 9: return mk(-0.30901699437494734f, -0.9510565162951536f);
+    case 10: return mk(-0.4999999999999998f, -0.8660254037844387f);
+    case 11: return mk(-0.6691306063588579f, -0.7431448254773945f);
+    case 12: return mk(-0.8090169943749473f, -0.5877852522924732f);
+    case 13: return mk(-0.913545457642601f, -0.40673664307580004f);
+    case 14: return mk(-0.9781476007338057f, -0.20791169081775931f);
+    default: return mk(1.f, 0.f);
+  }
+}
+FL_HD cf w90c(int k2) {
+  switch (k2) {
+    case 1: return mk(0.9975640502598242f, -0.0697564737441253f);
+    case 2: return mk(0.9902680687415704f, -0.13917310096006544f);
+    case 3: return mk(0.9781476007338057f, -0.20791169081775931f);
+    case 4: return mk(0.9612616959383189f, -0.27563735581699916f);
+    case 5: return mk(0.9396926207859084f, -0.3420201433256687f);
+    case 6: return mk(0.9135454576426009f, -0.40673664307580015f);
+    case 7: return mk(0.882947592858927f, -0.4694715627858908f);
+    case 8: return mk(0.848048096156426f, -0.5299192642332049f);
+    case 9: return mk(0.8090169943749475f, -0.5877852522924731f);
+    case 10: return mk(0.766044443118978f, -0.6427876096865393f);
+    case 11: return mk(0.7193398003386512f, -0.6946583704589973f);
+    case 12: return mk(0.6691306063588582f, -0.7431448254773941f);
+    case 13: return mk(0.6156614753256583f, -0.788010753606722f);
+    case 14: return mk(0.5591929034707468f, -0.8290375725550417f);
+    default: return mk(1.f, 0.f);
+  }
+}
+
 // 4-point DFT, natural order.  w = e^{SGN i pi/2} = SGN i
 template <int SGN>
 FL_HD void dft4(cf& a0, cf& a1, cf& a2, cf& a3) {
@@ -85,8 +140,18 @@ FL_HD void fft240p_fwd(Warp& w, LoadZ loadz, cf* work, const cf* twA, cf (&Z)[15
     for (int n1 = 0; n1 < 16; ++n1) a[n1] = loadz(15 * n1 + t);
     fft16<-1>(a);
     work[t] = a[0];
+#if SFNO_TW_REGS
+    const cf p = twA[15 + t];                                  // e^{-2 pi i t / 240}; twA[k1*15 + t] = p^k1
+    cf pw = p;
+#pragma unroll
+    for (int k1 = 1; k1 < 16; ++k1) {
+      work[k1 * 15 + t] = cmul(a[k1], pw);
+      if (k1 < 15) pw = cmul(pw, p);
+    }
+#else
 #pragma unroll
     for (int k1 = 1; k1 < 16; ++k1) work[k1 * 15 + t] = cmul(a[k1], twA[k1 * 15 + t]);
+#endif
   }
   w.sync();
 #pragma unroll
@@ -101,8 +166,18 @@ FL_HD void fft240p_inv(Warp& w, cf (&V)[15], cf* work, const cf* twA, StoreZ sto
   const int t = w.lane16();
   fl::dft15<+1>(V);                                          // index is now n2
   work[t * 15] = V[0];
+#if SFNO_TW_REGS
+  const cf q = cconj(twA[t * 15 + 1]);                         // e^{+2 pi i t / 240}; conj(twA[t*15 + n2]) = q^n2
+  cf qw = q;
+#pragma unroll
+  for (int n2 = 1; n2 < 15; ++n2) {
+    work[t * 15 + n2] = cmul(V[n2], qw);
+    if (n2 < 14) qw = cmul(qw, q);
+  }
+#else
 #pragma unroll
   for (int n2 = 1; n2 < 15; ++n2) work[t * 15 + n2] = cmul(V[n2], cconj(twA[t * 15 + n2]));
+#endif
   w.sync();
   if (t < 15) {
     cf a[16];
@@ -124,16 +199,22 @@ template <class Warp, class Emit>
 FL_HD float rfft480_split(Warp& w, const cf (&Z)[15], Emit emit, const cf* tw480) {
   const int k1 = w.lane16();
   const int src = (16 - k1) & 15;
+#if SFNO_TW_REGS
+  const cf base = tw480[k1];
+#endif
 #pragma unroll
   for (int k2 = 0; k2 < 15; ++k2) {
+#if SFNO_TW_REGS
+    const cf c = k2 == 0 ? base : cmul(base, w30c(k2));
+#else
     const cf c = tw480[k1 + 16 * k2];
+#endif
     const cf zs = mk(w.shfl_idx(Z[14 - k2].x, src), w.shfl_idx(Z[14 - k2].y, src));
     const cf z0 = (k2 == 0) ? Z[0] : Z[15 - k2];
     const cf zp = (k1 == 0) ? z0 : zs;
-    const float sx = Z[k2].x + zp.x, sy = Z[k2].y - zp.y;     // Z + conj(Zp)
-    const float dx = Z[k2].x - zp.x, dy = Z[k2].y + zp.y;     // Z - conj(Zp)
-    const float px = c.x * dx - c.y * dy, py = c.x * dy + c.y * dx;
-    emit(k2, mk(sx + py, sy - px));
+    const cf zc = cconj(zp);
+    const cf p = cmul(csub(Z[k2], zc), c);                    // w (Z - conj(Zp))
+    emit(k2, cadd(cadd(Z[k2], zc), fl::mul_i<-1>(p)));        // (Z + conj(Zp)) - i w (Z - conj(Zp))
   }
   return 2.f * (Z[0].x - Z[0].y);
 }
@@ -157,10 +238,19 @@ FL_HD void rfft_row_fwd(Warp& w, LoadZ loadz, cf* work, cf (&X)[15], cf& x240, c
       const float nyq = rfft480_split(w, Z, [&](int k2, cf v) { X[k2] = v; }, tw480);
       x240 = mk(nyq, 0.f);
     } else {
+#if SFNO_TW_REGS
+      const cf b1440 = tw1440[k1];
+      const float nyq = rfft480_split(w, Z, [&](int k2, cf v) {
+        const cf t = k2 == 0 ? b1440 : cmul(b1440, w90c(k2));
+        X[k2] = cadd(v, cmul(t, X[k2]));
+      }, tw480);
+      x240 = cadd(mk(nyq, 0.f), cmul(mk(0.5f, -0.86602540378443865f), x240));      // w1440^240 = e^{-i pi/3}
+#else
       const float nyq = rfft480_split(w, Z, [&](int k2, cf v) {
         X[k2] = cadd(v, cmul(tw1440[k1 + 16 * k2], X[k2]));
       }, tw480);
       x240 = cadd(mk(nyq, 0.f), cmul(tw1440[240], x240));
+#endif
     }
   }
 }
@@ -169,10 +259,9 @@ FL_HD void rfft_row_fwd(Warp& w, LoadZ loadz, cf* work, cf (&X)[15], cf& x240, c
 // length-480 real sequence) build V[k] = A + i conj(w) B,  A = h + conj(hp), B = h - conj(hp),  so that
 // x[2n] + i x[2n+1] = sum_k V[k] e^{+2 pi i k n / 240}.
 FL_HD cf irfft480_prep(cf h, cf hp, cf w480_k) {
-  const float ax = h.x + hp.x, ay = h.y - hp.y;
-  const float bx = h.x - hp.x, by = h.y + hp.y;
-  const float px = w480_k.x * bx + w480_k.y * by, py = w480_k.x * by - w480_k.y * bx;   // conj(w) B
-  return mk(ax - py, ay + px);
+  const cf hc = cconj(hp);
+  const cf p = cmul(csub(h, hc), cconj(w480_k));              // conj(w) B
+  return cadd(cadd(h, hc), fl::mul_i<+1>(p));                 // A + i conj(w) B
 }
 
 // For nlon = 480 R the sub-sequence r of the output needs the spectrum twisted by conj(w1440^k)^r (bin k) and
@@ -195,16 +284,38 @@ template <int R, class Warp, class StoreZ>
 FL_HD void irfft_row(Warp& w, cf (&H)[15], cf (&HP)[15], cf* work, StoreZ storez, const cf* twA, const cf* tw480,
                      const cf* tw1440) {
   const int k1 = w.lane16();
+#if SFNO_TW_REGS
+  const cf b480 = tw480[k1];
+#if SFNO_TW_REGS_TWIST
+  const cf b1440 = R > 1 ? tw1440[k1] : mk(1.f, 0.f);
+#endif
+#endif
 #pragma unroll
   for (int r = 0; r < R; ++r) {
     cf V[15];
 #pragma unroll
     for (int k2 = 0; k2 < 15; ++k2) {
       const int k = k1 + 16 * k2;
+#if SFNO_TW_REGS
+#if SFNO_TW_REGS_TWIST
+      if (r > 0) {
+        // w1440^k = (lane entry) x (constant of k2);  w1440^(240 - k) = e^{-i pi/3} conj(w1440^k)
+        const cf t = k2 == 0 ? b1440 : cmul(b1440, w90c(k2));
+        H[k2] = cmul(H[k2], cconj(t));
+        HP[k2] = cmul(HP[k2], cmul(mk(0.5f, 0.86602540378443865f), t));       // conj(w^(240-k)) = e^{+i pi/3} w^k
+      }
+#else
+      // the twist keeps its table loads: with H, HP and V live (90 registers) the computed variant spills
       if (r > 0) irfft_twist_step(k, H[k2], HP[k2], tw1440);
+#endif
+      const cf c480 = k2 == 0 ? b480 : cmul(b480, w30c(k2));
+#else
+      if (r > 0) irfft_twist_step(k, H[k2], HP[k2], tw1440);
+      const cf c480 = tw480[k];
+#endif
       cf h = H[k2], hp = HP[k2];
       if (k2 == 0) irfft_fix0<R>(k, h, hp);
-      V[k2] = irfft480_prep(h, hp, tw480[k]);
+      V[k2] = irfft480_prep(h, hp, c480);
     }
     fft240p_inv(w, V, work, twA, [&](int n, cf z) { storez(n, r, z); });
   }

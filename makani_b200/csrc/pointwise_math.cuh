@@ -72,4 +72,80 @@ PW_HD float pw_gelu_grad(float z) {
 #endif
 }
 
+#if defined(__CUDA_ARCH__) && (__CUDA_ARCH__ >= 1000) && SFNO_FAST_ERF
+// Two elements at a time with the packed fp32 instructions of sm_100 (FMUL2 / FFMA2): the GELU kernels are bound by
+// issue slots (~12 instructions per bf16 element is what an SM issues at the HBM rate), and the polynomial, the scalings
+// and the final products are the same operation on both elements.  Reciprocal, exp2 and the sign transfer stay scalar.
+// Same arithmetic as pw_erf_fast (the packed forms round like their scalar counterparts).
+#define SFNO_PW_PACKED 1
+namespace pw2 {
+__device__ __forceinline__ unsigned long long pk(float x, float y) {
+  unsigned long long r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(x), "f"(y));
+  return r;
+}
+__device__ __forceinline__ void up(unsigned long long v, float& x, float& y) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(x), "=f"(y) : "l"(v));
+}
+__device__ __forceinline__ unsigned long long mul(unsigned long long a, unsigned long long b) {
+  unsigned long long r;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ unsigned long long fma(unsigned long long a, unsigned long long b, unsigned long long c) {
+  unsigned long long r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+  return r;
+}
+__device__ __forceinline__ unsigned long long bc(float s) { return pk(s, s); }
+__device__ __forceinline__ float ex2(float x) {                      // MUFU.EX2, what __expf uses after its multiply
+  float r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+
+// erf of (u0, u1) -> er; g = exp(-u^2) of both
+__device__ __forceinline__ void erf_pair(float u0, float u1, unsigned long long& er, unsigned long long& g) {
+  const float a0 = fabsf(u0), a1 = fabsf(u1);
+  const unsigned long long ax = pk(a0, a1);
+  float d0, d1;
+  up(fma(ax, bc(0.3275911f), bc(1.0f)), d0, d1);
+  const unsigned long long t = pk(__fdividef(1.0f, d0), __fdividef(1.0f, d1));
+  float m0, m1;
+  up(mul(mul(ax, ax), bc(-1.4426950408889634f)), m0, m1);            // -x^2 log2(e)
+  g = pk(ex2(m0), ex2(m1));
+  unsigned long long poly = bc(1.061405429f);
+  poly = fma(poly, t, bc(-1.453152027f));
+  poly = fma(poly, t, bc(1.421413741f));
+  poly = fma(poly, t, bc(-0.284496736f));
+  poly = fma(poly, t, bc(0.254829592f));
+  float r0, r1;
+  up(fma(mul(mul(poly, t), g), bc(-1.0f), bc(1.0f)), r0, r1);       // 1 - poly t e
+  er = pk(copysignf(r0, u0), copysignf(r1, u1));
+}
+}  // namespace pw2
+
+// z0, z1 -> gelu(z0), gelu(z1)
+__device__ __forceinline__ void pw_gelu_pair(float& z0, float& z1) {
+  const unsigned long long z = pw2::pk(z0, z1);
+  float u0, u1;
+  pw2::up(pw2::mul(z, pw2::bc(0.70710678118654752f)), u0, u1);
+  unsigned long long er, g;
+  pw2::erf_pair(u0, u1, er, g);
+  pw2::up(pw2::mul(z, pw2::fma(er, pw2::bc(0.5f), pw2::bc(0.5f))), z0, z1);
+}
+// z0, z1 -> gelu'(z0), gelu'(z1) = Phi(z) + z phi(z)
+__device__ __forceinline__ void pw_gelu_grad_pair(float& z0, float& z1) {
+  const unsigned long long z = pw2::pk(z0, z1);
+  float u0, u1;
+  pw2::up(pw2::mul(z, pw2::bc(0.70710678118654752f)), u0, u1);
+  unsigned long long er, g;                                            // g = exp(-z^2 / 2)
+  pw2::erf_pair(u0, u1, er, g);
+  const unsigned long long cdf = pw2::fma(er, pw2::bc(0.5f), pw2::bc(0.5f));
+  pw2::up(pw2::fma(pw2::mul(z, pw2::bc(0.3989422804014327f)), g, cdf), z0, z1);
+}
+#else
+#define SFNO_PW_PACKED 0
+#endif
+
 }  // namespace sfno

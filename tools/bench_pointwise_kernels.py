@@ -36,6 +36,8 @@ for (H, W) in ((240, 480), (721, 1440)):
         "bwd_apply gelu (2 reads 1 write)": (3, lambda i: lib.sfno_instnorm_bwd_apply(p(gs[i]), p(xs[i]), _ext.BF16, Cn, Cn, hw, hw, p(stats), p(gam), p(bet), p(bsum), 1, p(out), st)),
         "bias_act gelu (1 read 1 write)": (2, lambda i: lib.sfno_bias_act(p(xs[i]), _ext.BF16, Cn, Cn, hw, p(bet), 1, p(out), st)),
         "bias_act_bwd gelu (2 reads 1 write)": (3, lambda i: lib.sfno_bias_act_bwd(p(gs[i]), p(xs[i]), _ext.BF16, Cn, Cn, hw, p(bet), 1, p(out), p(ws), st)),
+        "bias_act gelu in place (1 read 1 write)": (2, lambda i: lib.sfno_bias_act(p(xs[i]), _ext.BF16, Cn, Cn, hw, p(bet), 1, p(xs[i]), st)),
+        "bias_act none out of place (1 read 1 write)": (2, lambda i: lib.sfno_bias_act(p(xs[i]), _ext.BF16, Cn, Cn, hw, p(bet), 0, p(out), st)),
         "bias_act none in place (1 read 1 write)": (2, lambda i: lib.sfno_bias_act(p(xs[i]), _ext.BF16, Cn, Cn, hw, p(bet), 0, p(xs[i]), st)),
     }
     for name, (passes, fn) in calls.items():

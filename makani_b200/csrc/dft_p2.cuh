@@ -465,7 +465,11 @@ template <int R, typename T, class MAPS>
 static int launch_fwd_p2_maps(const void* x, int B, int C, int Ctot, int K, int pitch, int M, const float* mscale,
                               const MAPS& maps, int round_out, cudaStream_t stream) {
   // 16-bit rows at R = 3: a single row buffer lets two CTAs share an SM (16 warps instead of 8)
-  constexpr int NBUF = (R == 3 && sizeof(T) == 2) ? 1 : 2;
+  // (re-measured after the packed arithmetic, -DSFNO_R3_NBUF=2: 679 us against 464 us - the kernel lives on warps per SM)
+#ifndef SFNO_R3_NBUF
+#define SFNO_R3_NBUF 1
+#endif
+  constexpr int NBUF = (R == 3 && sizeof(T) == 2) ? SFNO_R3_NBUF : 2;
   using S = P2FwdSmem<R, T, NBUF>;
   static_assert(S::kBytes <= 227 * 1024, "forward DFT tile does not fit shared memory");
   constexpr int OCC = S::kCtasPerSm;

@@ -133,13 +133,31 @@ constexpr int kWT = 64;
 // lanes along i in steps of 4 (fixed l)
 __device__ __forceinline__ int wsw(int i, int l) { return l ^ (i >> 2); }
 
+// The unpack kernel is persistent: a CTA walks over tiles t = blockIdx.x, blockIdx.x + gridDim.x, ... (degree tiles
+// fastest, then input-channel tiles, then output channels) and requests the global loads of tile t+1 into registers
+// BEFORE it stores tile t from shared memory.  With one tile per CTA every CTA of a wave first only reads and then only
+// writes, in step with all others (measured: 58 us reading + 56 us writing = 115 us in total); overlapping the two
+// phases and dropping the per-load slice lookup bring the unpack from 132 to 103 us (profiles/r2y_weight_layout_pipelined.txt).
+struct WTile {
+  int l0, i0, o;
+};
+__device__ __forceinline__ WTile wtile(int t, int nlt, int nit) {
+  WTile r;
+  r.l0 = (t % nlt) * kWT;
+  t /= nlt;
+  r.i0 = (t % nit) * kWT;
+  r.o = t / nit;
+  return r;
+}
+
+// One tile per CTA: grid (ceil(L/64), ceil(Cinp/64), Cout).  (A persistent variant with register prefetch like the
+// unpack below needs 116 registers for its 16 + 16 eight-byte loads in flight and was slower: 103 - 113 us against 95.)
 __global__ void __launch_bounds__(256)
-pack_weight_kernel(const float2* __restrict__ w, float* __restrict__ wp, int Cin, int Cout, int L, int o_fastest,
-                   int round_out) {
+pack_weight_kernel(const float2* __restrict__ w, float* __restrict__ wp, int Cin, int Cout, int L, int round_out) {
   __shared__ float tr[kWT][kWT], ti[kWT][kWT];
   const int Cinp = (Cin + 3) & ~3, Coutp = (Cout + 3) & ~3;
-  const int o = o_fastest ? blockIdx.x : blockIdx.z;
-  const int l0 = (o_fastest ? blockIdx.z : blockIdx.x) * kWT, i0 = blockIdx.y * kWT;
+  const int o = blockIdx.z;
+  const int l0 = blockIdx.x * kWT, i0 = blockIdx.y * kWT;
   const int tid = threadIdx.x;
   {
     const int ll = tid & 63, ib = tid >> 6;           // 64 degrees x 4 rows per pass
@@ -185,59 +203,70 @@ struct WpSource {
   }
 };
 
+// GATHER = false: one buffer, addressed through a plain pointer (the per-load slice lookup of `at` - a 64-bit division
+// and an indexed read of the parameter array - cost 16 of 132 us)
+template <bool GATHER>
 __global__ void __launch_bounds__(256)
-unpack_wgrad_kernel(const WpSource src, float2* __restrict__ gw, int Cin, int Cout, int L, int o_fastest) {
+unpack_wgrad_kernel(const WpSource src, float2* __restrict__ gw, int Cin, int Cout, int L, int ntiles) {
+  const float* __restrict__ base0 = src.bases[0];
   __shared__ float tr[kWT][kWT], ti[kWT][kWT];
   const int Cinp = (Cin + 3) & ~3, Coutp = (Cout + 3) & ~3;
-  const int o = o_fastest ? blockIdx.x : blockIdx.z;
-  const int l0 = (o_fastest ? blockIdx.z : blockIdx.x) * kWT, i0 = blockIdx.y * kWT;
+  const int nlt = (L + kWT - 1) / kWT, nit = (Cin + kWT - 1) / kWT;
   const int tid = threadIdx.x;
-  {
-    const int iq = (tid & 15) * 4, lb = tid >> 4;
-    const bool iok = i0 + iq < Cinp;
-    float4 v[8];
+  const int iq = (tid & 15) * 4, lb = tid >> 4;       // loads: 16 lanes x float4 = 64 channels, 16 (l, re/im) rows per pass
+  float4 v[8];
+  auto load = [&](int t) {
+    const WTile c = wtile(t, nlt, nit);
+    const bool iok = c.i0 + iq < Cinp;
 #pragma unroll
     for (int p = 0; p < 8; ++p) {
       const int row = lb + 16 * p;
-      const int l = l0 + (row >> 1), reim = row & 1;
-      v[p] = (iok && l < L)
-                 ? *reinterpret_cast<const float4*>(src.at((((long long)l * 2 + reim) * Coutp + o) * Cinp + i0 + iq))
-                 : make_float4(0.f, 0.f, 0.f, 0.f);
+      const int l = c.l0 + (row >> 1), reim = row & 1;
+      const long long off = (((long long)l * 2 + reim) * Coutp + c.o) * Cinp + c.i0 + iq;
+      v[p] = (iok && l < L) ? *reinterpret_cast<const float4*>(GATHER ? src.at(off) : base0 + off)
+                            : make_float4(0.f, 0.f, 0.f, 0.f);
     }
+  };
+  int t = blockIdx.x;
+  if (t < ntiles) load(t);
+  for (; t < ntiles; t += gridDim.x) {
+    const WTile c = wtile(t, nlt, nit);
 #pragma unroll
     for (int p = 0; p < 8; ++p) {
       const int row = lb + 16 * p;
-      const int ll = row >> 1, reim = row & 1;
-      float (*t)[kWT] = reim ? ti : tr;
-      const int cl = wsw(iq, ll);
-      t[iq][cl] = v[p].x;
-      t[iq + 1][cl] = v[p].y;
-      t[iq + 2][cl] = v[p].z;
-      t[iq + 3][cl] = v[p].w;
+      const int lr = row >> 1, reim = row & 1;
+      float (*tt)[kWT] = reim ? ti : tr;
+      const int cl = wsw(iq, lr);
+      tt[iq][cl] = v[p].x;
+      tt[iq + 1][cl] = v[p].y;
+      tt[iq + 2][cl] = v[p].z;
+      tt[iq + 3][cl] = v[p].w;
     }
-  }
-  __syncthreads();
-  if ((L & 1) == 0) {
-    // two degrees per thread: 16-byte stores, a warp writes 512 contiguous bytes of one (i, o) row
-    const int lp = (tid & 31) * 2, ib = tid >> 5;
+    __syncthreads();
+    if (t + (int)gridDim.x < ntiles) load(t + gridDim.x);         // in flight while this tile is stored
+    if ((L & 1) == 0) {
+      // two degrees per thread: 16-byte stores, a warp writes 512 contiguous bytes of one (i, o) row
+      const int lp = (tid & 31) * 2, ib = tid >> 5;
 #pragma unroll
-    for (int p = 0; p < 8; ++p) {
-      const int il = ib + 8 * p;
-      const int i = i0 + il, l = l0 + lp;
-      if (i < Cin && l < L) {                           // L even and l even: l + 1 < L as well
-        const int c0 = wsw(il, lp), c1 = wsw(il, lp + 1);
-        *reinterpret_cast<float4*>(gw + ((long long)i * Cout + o) * L + l) =
-            make_float4(tr[il][c0], ti[il][c0], tr[il][c1], ti[il][c1]);
+      for (int p = 0; p < 8; ++p) {
+        const int il = ib + 8 * p;
+        const int i = c.i0 + il, l = c.l0 + lp;
+        if (i < Cin && l < L) {                         // L even and l even: l + 1 < L as well
+          const int c0 = wsw(il, lp), c1 = wsw(il, lp + 1);
+          *reinterpret_cast<float4*>(gw + ((long long)i * Cout + c.o) * L + l) =
+              make_float4(tr[il][c0], ti[il][c0], tr[il][c1], ti[il][c1]);
+        }
+      }
+    } else {
+      const int ll = tid & 63, ib = tid >> 6;
+#pragma unroll
+      for (int p = 0; p < 16; ++p) {
+        const int i = c.i0 + ib + 4 * p, l = c.l0 + ll;
+        if (i < Cin && l < L) gw[((long long)i * Cout + c.o) * L + l] =
+              make_float2(tr[ib + 4 * p][wsw(ib + 4 * p, ll)], ti[ib + 4 * p][wsw(ib + 4 * p, ll)]);
       }
     }
-  } else {
-    const int ll = tid & 63, ib = tid >> 6;
-#pragma unroll
-    for (int p = 0; p < 16; ++p) {
-      const int i = i0 + ib + 4 * p, l = l0 + ll;
-      if (i < Cin && l < L) gw[((long long)i * Cout + o) * L + l] =
-            make_float2(tr[ib + 4 * p][wsw(ib + 4 * p, ll)], ti[ib + 4 * p][wsw(ib + 4 * p, ll)]);
-    }
+    __syncthreads();                                  // the tile is overwritten by the next iteration
   }
 }
 
@@ -564,27 +593,20 @@ int sfno_c64_to_xm(const void* in_c64, int B, int C, int nlat, int mmax, float* 
   SFNO_LAUNCHED();
   return 0;
 }
-// CTA order of the weight-layout kernels: which index changes fastest between CTAs that run at the same time.
-// 0: degree tiles (the CTAs of one wave cover whole rows of a few (i, o) pairs), 1: output channels (for a fixed i the
-// rows of consecutive o are adjacent in the complex64 tensor).  SFNO_WLAYOUT_ORDER=0|1 for A/B runs.
-static int wlayout_order() {
-  static int v = -1;
-  if (v < 0) {
-    const char* env = getenv("SFNO_WLAYOUT_ORDER");
-    v = (env && env[0] == '1') ? 1 : 0;
+// persistent grids of the weight-layout kernels: SFNO_WLAYOUT_CTAS CTAs per SM (default 4; A/B runs)
+static int wlayout_grid(int ntiles) {
+  static int per_sm = -1;
+  if (per_sm < 0) {
+    const char* env = getenv("SFNO_WLAYOUT_CTAS");
+    per_sm = env ? std::max(1, atoi(env)) : 4;
   }
-  return v;
-}
-static dim3 wlayout_grid(int Cin_or_p, int Cout, int L, int order) {
-  const int lt = (L + kWT - 1) / kWT, it = (Cin_or_p + kWT - 1) / kWT;
-  return order ? dim3(Cout, it, lt) : dim3(lt, it, Cout);
+  return std::min(ntiles, per_sm * sm_count_current_device());
 }
 int sfno_dhconv_pack_weight_ex(const void* w_c64, int Cin, int Cout, int L, float* wp, int round_tf32, void* stream) {
   SFNO_CHECK(w_c64 && wp && Cin > 0 && Cout > 0 && L > 0, "sfno_dhconv_pack_weight: bad arguments");
   const int Cinp = (Cin + 3) & ~3;
-  const int order = wlayout_order();
-  dim3 grid = wlayout_grid(Cinp, Cout, L, order);
-  pack_weight_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const float2*)w_c64, wp, Cin, Cout, L, order, round_tf32);
+  dim3 grid((L + kWT - 1) / kWT, (Cinp + kWT - 1) / kWT, Cout);
+  pack_weight_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const float2*)w_c64, wp, Cin, Cout, L, round_tf32);
   SFNO_LAUNCHED();
   return 0;
 }
@@ -592,11 +614,13 @@ int sfno_dhconv_pack_weight(const void* w_c64, int Cin, int Cout, int L, float* 
   return sfno_dhconv_pack_weight_ex(w_c64, Cin, Cout, L, wp, 1, stream);
 }
 int sfno_dhconv_unpack_wgrad(const float* gwp, int Cin, int Cout, int L, void* gw_c64, void* stream) {
-  const int order = wlayout_order();
-  dim3 grid = wlayout_grid(Cin, Cout, L, order);
+  SFNO_CHECK(gwp && gw_c64 && Cin > 0 && Cout > 0 && L > 0, "sfno_dhconv_unpack_wgrad: bad arguments");
+  const long long nt = (long long)((L + kWT - 1) / kWT) * ((Cin + kWT - 1) / kWT) * Cout;
+  SFNO_CHECK(nt < (1LL << 31), "sfno_dhconv_unpack_wgrad: too many tiles");
   WpSource src = {};
   src.bases[0] = gwp;
-  unpack_wgrad_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(src, (float2*)gw_c64, Cin, Cout, L, order);
+  unpack_wgrad_kernel<false><<<wlayout_grid((int)nt), 256, 0, (cudaStream_t)stream>>>(src, (float2*)gw_c64, Cin, Cout, L,
+                                                                                      (int)nt);
   SFNO_LAUNCHED();
   return 0;
 }
@@ -608,9 +632,10 @@ int sfno_dhconv_unpack_wgrad_gather(const float* const* gwp_slices_host, int nsl
   WpSource src = {};
   for (int k = 0; k < 8; ++k) src.bases[k] = gwp_slices_host[k < nslices ? k : 0];
   src.slice = slice_floats;
-  const int order = wlayout_order();
-  dim3 grid = wlayout_grid(Cin, Cout, L, order);
-  unpack_wgrad_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(src, (float2*)gw_c64, Cin, Cout, L, order);
+  const long long nt = (long long)((L + kWT - 1) / kWT) * ((Cin + kWT - 1) / kWT) * Cout;
+  SFNO_CHECK(nt < (1LL << 31), "sfno_dhconv_unpack_wgrad_gather: too many tiles");
+  unpack_wgrad_kernel<true><<<wlayout_grid((int)nt), 256, 0, (cudaStream_t)stream>>>(src, (float2*)gw_c64, Cin, Cout, L,
+                                                                                     (int)nt);
   SFNO_LAUNCHED();
   return 0;
 }

@@ -1,5 +1,5 @@
 """pack_weight / unpack_wgrad alone at the named size (Cin = Cout = 384, L = 240: 283 MB each way), CUDA events, inputs
-rotated over three buffers (each 283 MB > 126 MB L2).  Run once per SFNO_WLAYOUT_ORDER value (read once per process)."""
+rotated over three buffers (each 283 MB > 126 MB L2).  SFNO_WLAYOUT_CTAS = CTAs per SM of the persistent unpack kernel."""
 import json
 import os
 import sys
@@ -35,6 +35,6 @@ t_pack = timed(lambda i: ops.pack_weight(ws[i % 3]))
 t_unpack = timed(lambda i: ops.unpack_wgrad(wps[i % 3], Cin, Cout, L))
 ok = bool(torch.equal(ops.unpack_wgrad(wps[0], Cin, Cout, L), torch.view_as_complex(
     (torch.view_as_real(ws[0]).view(torch.int32) + 0x1000 & ~0x1FFF).view(torch.float32))))
-print(json.dumps({"order": os.environ.get("SFNO_WLAYOUT_ORDER", "0"), "pack_us": round(t_pack, 1), "unpack_us": round(t_unpack, 1),
+print(json.dumps({"unpack_ctas_per_sm": os.environ.get("SFNO_WLAYOUT_CTAS", "4"), "pack_us": round(t_pack, 1), "unpack_us": round(t_unpack, 1),
                   "pack_frac": round(nbytes / t_pack / 1e3 / peak, 3), "unpack_frac": round(nbytes / t_unpack / 1e3 / peak, 3),
                   "roundtrip_is_tf32_rounding": ok}))

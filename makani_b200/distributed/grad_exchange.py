@@ -23,6 +23,7 @@ Measured (round 2, profiles/r2f_dp_gradient_exchange.txt): 14.70 ms per step at 
 is therefore not NCCL's SM footprint: whichever way the gradients travel, the exchange shares HBM, L2 and NVLink latency
 with the backward kernels it overlaps with, and those run 15 - 30 % slower while it is in flight.  bench.py keeps NCCL as
 the default and selects this exchange with MAKANI_B200_DP_EXCHANGE=peer.
+(Final tree of round 2, 2 GPUs, tools/run_r2_z.sh: 15.3 ms with this exchange, 14.0 ms with NCCL, identical gradients.)
 
 The averaged gradient is assigned to `weight.grad` in `wait()` (added to it if one is already there), not returned
 through autograd: its contents only exist once the communication stream has run.

@@ -253,10 +253,11 @@ dft_fwd_p2_kernel(const T* __restrict__ x, const __grid_constant__ MAPS xm_map,
 
     if constexpr (R == 1) {
       fl::cf Z[15];
-      fp::fft240p_fwd(warp, [&](int n) { return load_pair<1, T>(myrow, n, 0); }, work + r * 240, tw, Z);
+      fp::fft240p_fwd<fp::tw_regs<1>::value>(warp, [&](int n) { return load_pair<1, T>(myrow, n, 0); },
+                                             work + r * 240, tw, Z);
       __syncthreads();                          // raw[buf] consumed by every row; work no longer read
       if (tid < 32) claim((it + NBUF) & 3, buf);
-      const float nyq = fp::rfft480_split(warp, Z, [&](int k2, fl::cf v) {
+      const float nyq = fp::rfft480_split<fp::tw_regs<1>::value>(warp, Z, [&](int k2, fl::cf v) {
         const float sc = hs[lane + 16 * k2];
         st_re[k2 * 256] = fin(v.x, sc);
         st_im[k2 * 256] = fin(v.y, sc);

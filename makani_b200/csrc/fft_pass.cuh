@@ -29,16 +29,19 @@ using fl::cmul;
 using fl::cconj;
 using fl::cscale;
 
-// Optional (-DSFNO_TW_REGS=1): twiddles e^{-2 pi i k / 480} and e^{-2 pi i k / 1440} at k = lane + 16 k2 formed as
-// (table entry of the lane) x (compile-time constant of k2), and the twiddles of the 16 x 15 exchange as powers of one
-// table entry per lane - two packed instructions each instead of an 8-byte shared-memory load (38 percent of the
-// kernels' shared-memory wavefronts are twiddle loads).  Measured on B200 with the packed arithmetic of fft_lane.cuh
+// Twiddles formed in registers: e^{-2 pi i k / 480} and e^{-2 pi i k / 1440} at k = lane + 16 k2 as (table entry of
+// the lane) x (compile-time constant of k2), and the twiddles of the 16 x 15 exchange as powers of one table entry per
+// lane - two packed instructions each instead of an 8-byte shared-memory load (38 percent of the kernels'
+// shared-memory wavefronts are twiddle loads).  Measured on B200 with the packed arithmetic of fft_lane.cuh
 // (profiles/r2t_dft_f32x2_ab.txt): 240x480 forward / inverse 69.6 -> 67.9 / 63.9 -> 61.9 us, 721x1440 464 -> 472 /
-// 424 -> 423 us: the kernels are bound by neither pipe any more but by latency at 16 warps per SM, so the default
-// stays with the table loads.
+// 424 -> 423 us (bound by latency at 16 warps per SM, not by either pipe).  So the R = 1 rows (nlon = 480) use the
+// register form and the R = 3 rows keep the table loads:  SFNO_TW_REGS  0 = tables everywhere, 1 = registers at
+// R = 1 only (default), 2 = registers everywhere.
 #ifndef SFNO_TW_REGS
-#define SFNO_TW_REGS 0
+#define SFNO_TW_REGS 1
 #endif
+template <int R>
+struct tw_regs { static constexpr bool value = SFNO_TW_REGS == 2 || (SFNO_TW_REGS == 1 && R == 1); };
 #ifndef SFNO_TW_REGS_TWIST
 #define SFNO_TW_REGS_TWIST 0
 #endif
@@ -131,7 +134,7 @@ FL_HD void fft16(cf (&v)[16]) {
 
 // forward complex FFT-240.  loadz(n) returns z[n].  out: Z[k2] = Z[lane + 16 k2].
 // `work` is a 240-element scratch row in shared memory owned by this 16-lane group.
-template <class Warp, class LoadZ>
+template <bool TWR, class Warp, class LoadZ>
 FL_HD void fft240p_fwd(Warp& w, LoadZ loadz, cf* work, const cf* twA, cf (&Z)[15]) {
   const int t = w.lane16();
   if (t < 15) {
@@ -140,18 +143,18 @@ FL_HD void fft240p_fwd(Warp& w, LoadZ loadz, cf* work, const cf* twA, cf (&Z)[15
     for (int n1 = 0; n1 < 16; ++n1) a[n1] = loadz(15 * n1 + t);
     fft16<-1>(a);
     work[t] = a[0];
-#if SFNO_TW_REGS
-    const cf p = twA[15 + t];                                  // e^{-2 pi i t / 240}; twA[k1*15 + t] = p^k1
-    cf pw = p;
+    if constexpr (TWR) {
+      const cf p = twA[15 + t];                                // e^{-2 pi i t / 240}; twA[k1*15 + t] = p^k1
+      cf pw = p;
 #pragma unroll
-    for (int k1 = 1; k1 < 16; ++k1) {
-      work[k1 * 15 + t] = cmul(a[k1], pw);
-      if (k1 < 15) pw = cmul(pw, p);
+      for (int k1 = 1; k1 < 16; ++k1) {
+        work[k1 * 15 + t] = cmul(a[k1], pw);
+        if (k1 < 15) pw = cmul(pw, p);
+      }
+    } else {
+#pragma unroll
+      for (int k1 = 1; k1 < 16; ++k1) work[k1 * 15 + t] = cmul(a[k1], twA[k1 * 15 + t]);
     }
-#else
-#pragma unroll
-    for (int k1 = 1; k1 < 16; ++k1) work[k1 * 15 + t] = cmul(a[k1], twA[k1 * 15 + t]);
-#endif
   }
   w.sync();
 #pragma unroll
@@ -161,23 +164,23 @@ FL_HD void fft240p_fwd(Warp& w, LoadZ loadz, cf* work, const cf* twA, cf (&Z)[15
 }
 
 // inverse (unnormalised, e^{+}) complex FFT-240.  in: V[k2] = V[lane + 16 k2] (destroyed);  storez(n, z[n]).
-template <class Warp, class StoreZ>
+template <bool TWR, class Warp, class StoreZ>
 FL_HD void fft240p_inv(Warp& w, cf (&V)[15], cf* work, const cf* twA, StoreZ storez) {
   const int t = w.lane16();
   fl::dft15<+1>(V);                                          // index is now n2
   work[t * 15] = V[0];
-#if SFNO_TW_REGS
-  const cf q = cconj(twA[t * 15 + 1]);                         // e^{+2 pi i t / 240}; conj(twA[t*15 + n2]) = q^n2
-  cf qw = q;
+  if constexpr (TWR) {
+    const cf q = cconj(twA[t * 15 + 1]);                       // e^{+2 pi i t / 240}; conj(twA[t*15 + n2]) = q^n2
+    cf qw = q;
 #pragma unroll
-  for (int n2 = 1; n2 < 15; ++n2) {
-    work[t * 15 + n2] = cmul(V[n2], qw);
-    if (n2 < 14) qw = cmul(qw, q);
+    for (int n2 = 1; n2 < 15; ++n2) {
+      work[t * 15 + n2] = cmul(V[n2], qw);
+      if (n2 < 14) qw = cmul(qw, q);
+    }
+  } else {
+#pragma unroll
+    for (int n2 = 1; n2 < 15; ++n2) work[t * 15 + n2] = cmul(V[n2], cconj(twA[t * 15 + n2]));
   }
-#else
-#pragma unroll
-  for (int n2 = 1; n2 < 15; ++n2) work[t * 15 + n2] = cmul(V[n2], cconj(twA[t * 15 + n2]));
-#endif
   w.sync();
   if (t < 15) {
     cf a[16];
@@ -195,20 +198,14 @@ FL_HD void fft240p_inv(Warp& w, cf (&V)[15], cf* work, const cf* twA, StoreZ sto
 // returns 2 X[240] (meaningful on lane 0 only).  Bin 240-k of lane k1 > 0 is register 14-k2 of lane 16-k1;
 // lane 0 pairs its own registers (k2 <-> 15-k2, bin 0 with itself).
 //   2 X = (Z + conj(Zp)) - i w (Z - conj(Zp)),   w = e^{-2 pi i k / 480}
-template <class Warp, class Emit>
+template <bool TWR, class Warp, class Emit>
 FL_HD float rfft480_split(Warp& w, const cf (&Z)[15], Emit emit, const cf* tw480) {
   const int k1 = w.lane16();
   const int src = (16 - k1) & 15;
-#if SFNO_TW_REGS
   const cf base = tw480[k1];
-#endif
 #pragma unroll
   for (int k2 = 0; k2 < 15; ++k2) {
-#if SFNO_TW_REGS
-    const cf c = k2 == 0 ? base : cmul(base, w30c(k2));
-#else
-    const cf c = tw480[k1 + 16 * k2];
-#endif
+    const cf c = (!TWR || k2 == 0) ? (k2 == 0 ? base : tw480[k1 + 16 * k2]) : cmul(base, w30c(k2));
     const cf zs = mk(w.shfl_idx(Z[14 - k2].x, src), w.shfl_idx(Z[14 - k2].y, src));
     const cf z0 = (k2 == 0) ? Z[0] : Z[15 - k2];
     const cf zp = (k1 == 0) ? z0 : zs;
@@ -229,28 +226,27 @@ template <int R, class Warp, class LoadZ>
 FL_HD void rfft_row_fwd(Warp& w, LoadZ loadz, cf* work, cf (&X)[15], cf& x240, const cf* twA, const cf* tw480,
                         const cf* tw1440) {
   const int k1 = w.lane16();
+  constexpr bool TWR = tw_regs<R>::value;
   // Horner in the sub-sequence index: X = X_0 + t (X_1 + t X_2),  t = w1440^m  - one complex multiply per bin and r
 #pragma unroll
   for (int r = R - 1; r >= 0; --r) {
     cf Z[15];
-    fft240p_fwd(w, [&](int n) { return loadz(n, r); }, work, twA, Z);
+    fft240p_fwd<TWR>(w, [&](int n) { return loadz(n, r); }, work, twA, Z);
     if (r == R - 1) {
-      const float nyq = rfft480_split(w, Z, [&](int k2, cf v) { X[k2] = v; }, tw480);
+      const float nyq = rfft480_split<TWR>(w, Z, [&](int k2, cf v) { X[k2] = v; }, tw480);
       x240 = mk(nyq, 0.f);
-    } else {
-#if SFNO_TW_REGS
+    } else if constexpr (TWR) {
       const cf b1440 = tw1440[k1];
-      const float nyq = rfft480_split(w, Z, [&](int k2, cf v) {
+      const float nyq = rfft480_split<TWR>(w, Z, [&](int k2, cf v) {
         const cf t = k2 == 0 ? b1440 : cmul(b1440, w90c(k2));
         X[k2] = cadd(v, cmul(t, X[k2]));
       }, tw480);
       x240 = cadd(mk(nyq, 0.f), cmul(mk(0.5f, -0.86602540378443865f), x240));      // w1440^240 = e^{-i pi/3}
-#else
-      const float nyq = rfft480_split(w, Z, [&](int k2, cf v) {
+    } else {
+      const float nyq = rfft480_split<TWR>(w, Z, [&](int k2, cf v) {
         X[k2] = cadd(v, cmul(tw1440[k1 + 16 * k2], X[k2]));
       }, tw480);
       x240 = cadd(mk(nyq, 0.f), cmul(tw1440[240], x240));
-#endif
     }
   }
 }
@@ -284,11 +280,10 @@ template <int R, class Warp, class StoreZ>
 FL_HD void irfft_row(Warp& w, cf (&H)[15], cf (&HP)[15], cf* work, StoreZ storez, const cf* twA, const cf* tw480,
                      const cf* tw1440) {
   const int k1 = w.lane16();
-#if SFNO_TW_REGS
+  constexpr bool TWR = tw_regs<R>::value;
   const cf b480 = tw480[k1];
 #if SFNO_TW_REGS_TWIST
   const cf b1440 = R > 1 ? tw1440[k1] : mk(1.f, 0.f);
-#endif
 #endif
 #pragma unroll
   for (int r = 0; r < R; ++r) {
@@ -296,28 +291,24 @@ FL_HD void irfft_row(Warp& w, cf (&H)[15], cf (&HP)[15], cf* work, StoreZ storez
 #pragma unroll
     for (int k2 = 0; k2 < 15; ++k2) {
       const int k = k1 + 16 * k2;
-#if SFNO_TW_REGS
 #if SFNO_TW_REGS_TWIST
-      if (r > 0) {
+      if (r > 0 && TWR) {
         // w1440^k = (lane entry) x (constant of k2);  w1440^(240 - k) = e^{-i pi/3} conj(w1440^k)
         const cf t = k2 == 0 ? b1440 : cmul(b1440, w90c(k2));
         H[k2] = cmul(H[k2], cconj(t));
         HP[k2] = cmul(HP[k2], cmul(mk(0.5f, 0.86602540378443865f), t));       // conj(w^(240-k)) = e^{+i pi/3} w^k
       }
+      if (r > 0 && !TWR) irfft_twist_step(k, H[k2], HP[k2], tw1440);
 #else
       // the twist keeps its table loads: with H, HP and V live (90 registers) the computed variant spills
       if (r > 0) irfft_twist_step(k, H[k2], HP[k2], tw1440);
 #endif
-      const cf c480 = k2 == 0 ? b480 : cmul(b480, w30c(k2));
-#else
-      if (r > 0) irfft_twist_step(k, H[k2], HP[k2], tw1440);
-      const cf c480 = tw480[k];
-#endif
+      const cf c480 = (!TWR || k2 == 0) ? (k2 == 0 ? b480 : tw480[k]) : cmul(b480, w30c(k2));
       cf h = H[k2], hp = HP[k2];
       if (k2 == 0) irfft_fix0<R>(k, h, hp);
       V[k2] = irfft480_prep(h, hp, c480);
     }
-    fft240p_inv(w, V, work, twA, [&](int n, cf z) { storez(n, r, z); });
+    fft240p_inv<TWR>(w, V, work, twA, [&](int n, cf z) { storez(n, r, z); });
   }
 }
 

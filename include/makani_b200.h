@@ -108,6 +108,24 @@ int sfno_legendre_analysis_win(const sfno_plan* plan, const float* xm_win, int B
 int sfno_legendre_synthesis_win(const sfno_plan* plan, const float* sp, int B, int Ctot, int c0, int C, float* xm_win,
                                 void* stream);
 
+/* nlon = 1440 with more than 241 longitude modes - the transform of the spectral loss, which keeps all 721
+ * (makani/utils/losses.py:291; torch-harmonics RealSHT: rfft over the longitudes, all mmax columns kept).  The tiled
+ * kernels handle 241 bins per launch; three launches with their 1440-point twiddles multiplied by a cube root of unity
+ * cover the spectrum:   band 0: bins k,   band 2: bins 480 + k,   band 1: conj of bins 480 - k   (k = 0 .. 240).
+ *   xm_rows : first bin of the band inside an XM tensor (band 0: xm, band 2: xm + 480 rows) or, for band 1, a scratch
+ *             of 241 rows that sfno_xm_mirror_conj turns around into rows 241 .. 479 (forward) / fills from them
+ *             (inverse).  One row = 2B * round_up(C,4) * Kp floats.
+ *   mscale_dev : mcount per-bin factors of THIS band.  Inverse: the kernel counts its bin 0 once and doubles its bin
+ *             240, so band 2 wants 2 * s[480] first and s[720] / 2 last, and band 1 zeros at both ends; the three
+ *             results are added by the caller (makani_b200/ops.py: _dft_inv_banded).
+ * sfno_xm_mirror_conj: dst row i = conj(src row nrows-1-i) * scale[i] (scale may be NULL); planes alternate re / im. */
+int sfno_dft_fwd_band(const void* x, int x_dtype, int B, int Ctot, int c0, int C, int nlat, int band, int mcount,
+                      const float* mscale_dev, float* xm_rows, int round_tf32, void* stream);
+int sfno_dft_inv_band(const float* xm_rows, int B, int Ctot, int c0, int C, int nlat, int band, int mcount,
+                      const float* mscale_dev, void* y, int y_dtype, void* stream);
+int sfno_xm_mirror_conj(const float* src, float* dst, int nrows, int nplanes, long long plane_floats,
+                        const float* scale_dev, int round_tf32, void* stream);
+
 /* ---- K3 dhconv channel contraction (makani/models/common/contractions.py:131-136,
  * einsum "bixy,iox->boxy" on complex64) as planar-complex TF32 tcgen05 GEMMs, batched over l.   */
 int sfno_dhconv_pack_weight(const void* w_c64 /*[Cin][Cout][L] complex64*/, int Cin, int Cout, int L,
@@ -170,6 +188,17 @@ int sfno_c64_to_xm(const void* in_c64, int B, int C, int nlat, int mmax, float* 
 /* y[b][c][h][w] (+)= bias   (spectral_convolution.py:143-144); bias_kind 0: [C], 1: [C][H][W]    */
 int sfno_add_bias(void* y, int y_dtype, const float* bias, int bias_kind, int B, int C, int H, int W,
                   void* stream);
+
+/* Per-degree energy of an SP tensor and its adjoint - the spectral loss (makani/utils/losses.py:299-303, 327-337:
+ * coeffs.re^2 + coeffs.im^2, then column m = 0 plus twice the sum of the other columns):
+ *   out[b][c][l] = sum_{m + m_offset <= l + l_offset} w_m |SP[l][m][b][c]|^2,   w_m = 1 at m + m_offset == 0, else 2
+ *   gsp[l][m][b][re|im][c] = 2 w_m g[b][c][l] sp[l][m][b][re|im][c]   (exact zeros for m above the diagonal and in
+ *                            pad channels; round_tf32: the consumer is the TF32 Legendre synthesis of the backward)
+ * out / g: fp32 [B][C][lmax].  The complex64 coefficient tensor of the reference API is never formed.          */
+int sfno_sp_degree_power(const float* sp, int B, int C, int lmax, int mmax, int l_offset, int m_offset, float* out,
+                         void* stream);
+int sfno_sp_degree_power_bwd(const float* sp, const float* g, int B, int C, int lmax, int mmax, int l_offset,
+                             int m_offset, int round_tf32, float* gsp, void* stream);
 
 /* dst[i] += src[i], i < n (n % 4 == 0, 16-byte aligned): the sum of two gradients in an internal layout (SP_l of the
  * h-sharded SpectralConv backward: filter branch + re-projected residual, spectral_convolution.py:132-134).   */

@@ -10,6 +10,8 @@ built library, raises.
 from . import quadrature, legendre                      # host-side fp64 precompute (numpy only)
 from .sht import RealSHT, InverseRealSHT
 from .fft2 import RealFFT2, InverseRealFFT2
+from . import losses
+from .losses import GeometricH1Loss
 from .spectral_convolution import SpectralConv, SpectralConvS2
 from .instance_norm import FusedInstanceNorm2d, DistributedFusedInstanceNorm2d
 from .block import fuse_block, fuse_model
@@ -17,8 +19,8 @@ from .pointwise_mlp import pointwise_linear, pointwise_mlp, fuse_pointwise
 from . import distributed
 from .compat import install_torch_harmonics_shim
 
-__all__ = ["RealSHT", "InverseRealSHT", "RealFFT2", "InverseRealFFT2", "SpectralConv", "SpectralConvS2", "FusedInstanceNorm2d",
-           "DistributedFusedInstanceNorm2d", "fuse_block", "fuse_model", "fuse_pointwise",
-           "pointwise_linear", "pointwise_mlp", "distributed", "quadrature", "legendre",
+__all__ = ["RealSHT", "InverseRealSHT", "RealFFT2", "InverseRealFFT2", "GeometricH1Loss", "losses", "SpectralConv",
+           "SpectralConvS2", "FusedInstanceNorm2d", "DistributedFusedInstanceNorm2d", "fuse_block", "fuse_model",
+           "fuse_pointwise", "pointwise_linear", "pointwise_mlp", "distributed", "quadrature", "legendre",
            "install_torch_harmonics_shim"]
 __version__ = "0.1.0"

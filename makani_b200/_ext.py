@@ -50,6 +50,11 @@ _PROTOTYPES = {
     "sfno_peer_copy": (_i, [_vp, _vp, C.c_size_t, _vp]),
     "sfno_slices_average": (_i, [_vp, _vp, _i, _ll, C.c_float, _vp]),
     "sfno_add_inplace": (_i, [_vp, _vp, _ll, _vp]),
+    "sfno_dft_fwd_band": (_i, [_vp, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _vp, _i, _vp]),
+    "sfno_dft_inv_band": (_i, [_vp, _i, _i, _i, _i, _i, _i, _i, _vp, _vp, _i, _vp]),
+    "sfno_xm_mirror_conj": (_i, [_vp, _vp, _i, _i, _ll, _vp, _i, _vp]),
+    "sfno_sp_degree_power": (_i, [_vp, _i, _i, _i, _i, _i, _i, _vp, _vp]),
+    "sfno_sp_degree_power_bwd": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp, _vp]),
     "sfno_xm_add_dc": (_i, [_vp, _i, _i, _i, _vp, _vp]),
     "sfno_workspace_bytes": (C.c_size_t, [_vp, _vp, _i, _i, _i]),
     "sfno_sht_fwd": (_i, [_vp, _vp, _i, _i, _i, _vp, _vp, C.c_size_t, _vp]),

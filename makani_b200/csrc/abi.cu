@@ -138,6 +138,24 @@ int sfno_dft_inv_win(const float* xm_win, int B, int Ctot, int c0, int C, int nl
   char* yw = static_cast<char*>(y) + (size_t)c0 * nlat * nlon * dtype_size(y_dtype);
   return dft_inv(xm_win, B, C, Ctot, nlat, nlon, mmax, m_valid, mscale_dev, yw, y_dtype, (cudaStream_t)stream);
 }
+int sfno_dft_fwd_band(const void* x, int x_dtype, int B, int Ctot, int c0, int C, int nlat, int band, int mcount,
+                      const float* mscale_dev, float* xm_rows, int round_tf32, void* stream) {
+  SFNO_CHECK(x && xm_rows && mscale_dev, "null argument");
+  SFNO_CHECK(c0 >= 0 && C > 0 && c0 + C <= Ctot, "sfno_dft_fwd_band: bad channel window");
+  const char* xw = static_cast<const char*>(x) + (size_t)c0 * nlat * 1440 * dtype_size(x_dtype);
+  return dft_fwd_band(xw, x_dtype, B, C, Ctot, nlat, band, mcount, mscale_dev, xm_rows, round_tf32, (cudaStream_t)stream);
+}
+int sfno_dft_inv_band(const float* xm_rows, int B, int Ctot, int c0, int C, int nlat, int band, int mcount,
+                      const float* mscale_dev, void* y, int y_dtype, void* stream) {
+  SFNO_CHECK(xm_rows && y && mscale_dev, "null argument");
+  SFNO_CHECK(c0 >= 0 && C > 0 && c0 + C <= Ctot, "sfno_dft_inv_band: bad channel window");
+  char* yw = static_cast<char*>(y) + (size_t)c0 * nlat * 1440 * dtype_size(y_dtype);
+  return dft_inv_band(xm_rows, B, C, Ctot, nlat, band, mcount, mscale_dev, yw, y_dtype, (cudaStream_t)stream);
+}
+int sfno_xm_mirror_conj(const float* src, float* dst, int nrows, int nplanes, long long plane_floats,
+                        const float* scale_dev, int round_tf32, void* stream) {
+  return xm_mirror_conj(src, dst, nrows, nplanes, plane_floats, scale_dev, round_tf32, (cudaStream_t)stream);
+}
 int sfno_legendre_analysis_win(const sfno_plan* plan, const float* xm_win, int B, int Ctot, int c0, int C, float* sp,
                                int round_tf32, int accumulate, void* stream) {
   SFNO_CHECK(plan && xm_win && sp, "null argument");

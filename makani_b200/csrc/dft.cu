@@ -66,6 +66,7 @@ template <> __device__ __forceinline__ __nv_bfloat16 from_f32<__nv_bfloat16>(flo
 template <> __device__ __forceinline__ __half from_f32<__half>(float v) { return __float2half_rn(v); }
 
 constexpr int kRows = 16;   // flat positions per CTA tile
+constexpr int kGenericSmemMax = 227 * 1024;   // dynamic shared memory the generic kernels may ask for
 
 // ------------------------------------------------------------------ generic forward
 template <typename T>
@@ -488,8 +489,9 @@ static int launch_fwd_generic(const void* x, int B, int C, int Ctot, int K, int 
   const float2* tw;
   if (get_twiddles(W, &tw)) return 1;
   const size_t smem = (size_t)(kRows * (W + 1) + 2 * W + 2 * M * (kRows + 1)) * 4 + 16;
-  SFNO_CHECK(smem <= 200 * 1024, "generic DFT: nlon too large for the shared-memory kernel");
-  SFNO_CUDA(cudaFuncSetAttribute(dft_fwd_generic_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+  // 227 KB is the sm_100 limit per CTA: nlon = 1440 with all 721 modes (the spectral loss's transform) needs 202 KB
+  SFNO_CHECK(smem <= kGenericSmemMax, "generic DFT: nlon too large for the shared-memory kernel");
+  SFNO_CUDA(cudaFuncSetAttribute(dft_fwd_generic_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGenericSmemMax));
   const int ntiles = ((C * Kp + kRows - 1) / kRows) * B;
   dft_fwd_generic_kernel<T><<<ntiles, 256, smem, stream>>>(static_cast<const T*>(x), xm, tw, mscale, B, C, K, Kp, W, M, round_out, (long long)Ctot * K * W);
   SFNO_LAUNCHED();
@@ -501,8 +503,8 @@ static int launch_inv_generic(const float* xm, int B, int C, int Ctot, int K, in
   const float2* tw;
   if (get_twiddles(W, &tw)) return 1;
   const size_t smem = (size_t)(2 * W + 2 * M * (kRows + 1)) * 4 + 16;
-  SFNO_CHECK(smem <= 200 * 1024, "generic inverse DFT: sizes too large for the shared-memory kernel");
-  SFNO_CUDA(cudaFuncSetAttribute(dft_inv_generic_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+  SFNO_CHECK(smem <= kGenericSmemMax, "generic inverse DFT: sizes too large for the shared-memory kernel");
+  SFNO_CUDA(cudaFuncSetAttribute(dft_inv_generic_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, kGenericSmemMax));
   const int ntiles = ((C * Kp + kRows - 1) / kRows) * B;
   dft_inv_generic_kernel<T><<<ntiles, 256, smem, stream>>>(xm, static_cast<T*>(y), tw, mscale, B, C, K, Kp, W, M, m_valid, (long long)Ctot * K * W);
   SFNO_LAUNCHED();
@@ -572,6 +574,76 @@ int dft_inv(const float* xm, int B, int C, int Ctot, int nlat, int nlon, int mma
     default: SFNO_CHECK(false, "unsupported output dtype");
   }
 #undef SFNO_DISPATCH_INV
+}
+
+// ---- nlon = 1440 with more than 241 modes (the spectral loss keeps all 721, makani/utils/losses.py:291) ----
+// The tiled kernels deliver bins k = 0..240 of a row from three length-480 transforms X_r:  X[k] = sum_r t(k)^r X_r[k],
+// t(k) = e^{-2 pi i k / 1440}.  X_r has period 480 and is Hermitian, so with w = e^{-2 pi i / 3}
+//     X[480 + k] = sum_r (w t)^r X_r[k]                     band 2: the same kernel with its t-table multiplied by w
+//     X[480 - k] = conj( sum_r (conj(w) t)^r X_r[k] )       band 1: table times conj(w), then mirrored and conjugated
+// and, by linearity, the inverse is the sum of three inverse launches on the rows of each band (the caller passes the
+// weights: bin 480 enters band 2 as its k = 0, which the kernel counts once - so twice there - and the Nyquist bin 720
+// as k = 240, which the kernel doubles - so half).  `xm_rows` points at the first bin of the band, `mcount` bins.
+int dft_fwd_band(const void* x, int x_dtype, int B, int C, int Ctot, int nlat, int band, int mcount, const float* mscale,
+                 float* xm_rows, int round_out, cudaStream_t stream) {
+  SFNO_CHECK(band >= 0 && band <= 2 && mcount >= 1 && mcount <= 241, "dft band: band 0..2, 1..241 bins");
+  SFNO_CHECK(Ctot >= C, "channel window larger than the field");
+  SFNO_CHECK(((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(xm_rows)) & 15) == 0, "dft band: alignment");
+  const int Kp = round_up(nlat, 4);
+  switch (x_dtype) {
+    case SFNO_F32: return launch_fwd_p2<3, float>(x, B, C, Ctot, nlat, Kp, mcount, mscale, xm_rows, round_out, stream, band);
+    case SFNO_BF16: return launch_fwd_p2<3, __nv_bfloat16>(x, B, C, Ctot, nlat, Kp, mcount, mscale, xm_rows, round_out, stream, band);
+    case SFNO_F16: return launch_fwd_p2<3, __half>(x, B, C, Ctot, nlat, Kp, mcount, mscale, xm_rows, round_out, stream, band);
+    default: SFNO_CHECK(false, "unsupported input dtype");
+  }
+}
+
+int dft_inv_band(const float* xm_rows, int B, int C, int Ctot, int nlat, int band, int mcount, const float* mscale, void* y,
+                 int y_dtype, cudaStream_t stream) {
+  SFNO_CHECK(band >= 0 && band <= 2 && mcount >= 1 && mcount <= 241, "dft band: band 0..2, 1..241 bins");
+  SFNO_CHECK(Ctot >= C, "channel window larger than the field");
+  SFNO_CHECK(((reinterpret_cast<uintptr_t>(y) | reinterpret_cast<uintptr_t>(xm_rows)) & 15) == 0, "dft band: alignment");
+  const int Kp = round_up(nlat, 4);
+  switch (y_dtype) {
+    case SFNO_F32: return launch_inv_p2<3, float>(xm_rows, B, C, Ctot, nlat, Kp, mcount, mcount, mscale, y, stream, band);
+    case SFNO_BF16: return launch_inv_p2<3, __nv_bfloat16>(xm_rows, B, C, Ctot, nlat, Kp, mcount, mcount, mscale, y, stream, band);
+    case SFNO_F16: return launch_inv_p2<3, __half>(xm_rows, B, C, Ctot, nlat, Kp, mcount, mcount, mscale, y, stream, band);
+    default: SFNO_CHECK(false, "unsupported output dtype");
+  }
+}
+
+// dst row i = conj(src row nrows-1-i) * scale[i]: rows are bins of an XM tensor ([2B planes][plane_floats], odd planes
+// hold the imaginary parts).  grid (chunks, nrows), 256 threads, float4
+__global__ void __launch_bounds__(256) xm_mirror_conj_kernel(const float4* __restrict__ src, float4* __restrict__ dst,
+                                                             int nrows, int nplanes, long long plane4,
+                                                             const float* __restrict__ scale, int round_out) {
+  const int i = blockIdx.y;
+  const long long row4 = plane4 * nplanes;
+  const float s = scale ? scale[i] : 1.f;
+  const float4* sr = src + (long long)(nrows - 1 - i) * row4;
+  float4* dr = dst + (long long)i * row4;
+  for (long long e = blockIdx.x * 256LL + threadIdx.x; e < row4; e += gridDim.x * 256LL) {
+    const float f = ((e / plane4) & 1) ? -s : s;
+    float4 v = sr[e];
+    v.x *= f; v.y *= f; v.z *= f; v.w *= f;
+    if (round_out) { v.x = tf32_rn(v.x); v.y = tf32_rn(v.y); v.z = tf32_rn(v.z); v.w = tf32_rn(v.w); }
+    dr[e] = v;
+  }
+}
+
+int xm_mirror_conj(const float* src, float* dst, int nrows, int nplanes, long long plane_floats, const float* scale,
+                   int round_out, cudaStream_t stream) {
+  SFNO_CHECK(src && dst && nrows >= 0 && nplanes > 0 && plane_floats > 0 && plane_floats % 4 == 0,
+             "xm_mirror_conj: bad arguments (plane_floats % 4 == 0)");
+  SFNO_CHECK(((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) & 15) == 0, "xm_mirror_conj: alignment");
+  if (nrows == 0) return 0;
+  const long long row4 = plane_floats / 4 * nplanes;
+  const int chunks = (int)std::min<long long>((row4 + 255) / 256, 64);
+  xm_mirror_conj_kernel<<<dim3(chunks, nrows), 256, 0, stream>>>(reinterpret_cast<const float4*>(src),
+                                                                 reinterpret_cast<float4*>(dst), nrows, nplanes,
+                                                                 plane_floats / 4, scale, round_out);
+  SFNO_LAUNCHED();
+  return 0;
 }
 
 // ---- h-sharded transforms: the DFT kernels address the channel-sharded XM_ch buffers of all ranks (peer memory)

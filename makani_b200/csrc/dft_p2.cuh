@@ -114,11 +114,15 @@ static int xm_stage_map(CUtensorMap* map, const float* xm, int B, int C, int Kp,
 }
 
 // tables for the p2 kernels: twA[240] | tw480[241] | tw1440[241]
+// band (nlon = 1440 with more than 241 modes, see dft_fwd_band in dft.cu): the kernels combine the three length-480
+// sub-transforms with tw1440[k]^r; with the table multiplied by a cube root of unity the very same kernels produce
+// (consume) bins 480 + k (band 2, factor e^{-2 pi i / 3}) and the conjugates of bins 480 - k (band 1, e^{+2 pi i / 3}).
 static std::map<int, fl::cf*> g_p2_tw_cache;
 
-static int get_p2_tables(const fl::cf** out) {
+static int get_p2_tables(const fl::cf** out, int band = 0) {
   int dev = 0;
   cudaGetDevice(&dev);
+  dev = dev * 4 + band;
   std::lock_guard<std::mutex> lock(g_tw_mutex);
   auto it = g_p2_tw_cache.find(dev);
   if (it != g_p2_tw_cache.end()) {
@@ -134,7 +138,7 @@ static int get_p2_tables(const fl::cf** out) {
   for (int k = 0; k < 241; ++k) {
     double a = -2.0 * M_PI * (double)k / 480.0;
     h[240 + k] = fl::mk((float)cos(a), (float)sin(a));
-    double c = -2.0 * M_PI * (double)k / 1440.0;
+    double c = -2.0 * M_PI * ((double)k / 1440.0 + (band == 2 ? 1.0 / 3.0 : (band == 1 ? -1.0 / 3.0 : 0.0)));
     h[240 + 241 + k] = fl::mk((float)cos(c), (float)sin(c));
   }
   h[240 + 120] = fl::mk(0.f, -1.f);
@@ -464,7 +468,7 @@ static int p2_prepare(Kern kern, int smem_bytes) {
 // pitch = round_up(K, 16): tiles never straddle two channels there)
 template <int R, typename T, class MAPS>
 static int launch_fwd_p2_maps(const void* x, int B, int C, int Ctot, int K, int pitch, int M, const float* mscale,
-                              const MAPS& maps, int round_out, cudaStream_t stream) {
+                              const MAPS& maps, int round_out, cudaStream_t stream, int band = 0) {
   // 16-bit rows at R = 3: a single row buffer lets two CTAs share an SM (16 warps instead of 8)
   // (re-measured after the packed arithmetic, -DSFNO_R3_NBUF=2: 679 us against 464 us - the kernel lives on warps per SM)
 #ifndef SFNO_R3_NBUF
@@ -475,7 +479,7 @@ static int launch_fwd_p2_maps(const void* x, int B, int C, int Ctot, int K, int 
   static_assert(S::kBytes <= 227 * 1024, "forward DFT tile does not fit shared memory");
   constexpr int OCC = S::kCtasPerSm;
   const fl::cf* tables;
-  if (get_p2_tables(&tables)) return 1;
+  if (get_p2_tables(&tables, band)) return 1;
   static PerDeviceOnce attr;
   if (attr.needed()) {
     SFNO_CUDA(cudaFuncSetAttribute(dft_fwd_p2_kernel<R, T, NBUF, true, OCC, MAPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kBytes));
@@ -502,20 +506,20 @@ static int launch_fwd_p2_maps(const void* x, int B, int C, int Ctot, int K, int 
 
 template <int R, typename T>
 static int launch_fwd_p2(const void* x, int B, int C, int Ctot, int K, int Kp, int M, const float* mscale, float* xm,
-                         int round_out, cudaStream_t stream) {
+                         int round_out, cudaStream_t stream, int band = 0) {
   LocalMap lm;
   if (xm_stage_map(&lm.map, xm, B, C, Kp, M)) return 1;
-  return launch_fwd_p2_maps<R, T, LocalMap>(x, B, C, Ctot, K, Kp, M, mscale, lm, round_out, stream);
+  return launch_fwd_p2_maps<R, T, LocalMap>(x, B, C, Ctot, K, Kp, M, mscale, lm, round_out, stream, band);
 }
 
 template <int R, typename T, class MAPS>
 static int launch_inv_p2_maps(const MAPS& maps, int B, int C, int Ctot, int K, int pitch, int m_valid, const float* mscale,
-                              void* y, cudaStream_t stream) {
+                              void* y, cudaStream_t stream, int band = 0) {
   constexpr int NST = P2InvDepth<R, T>::value;
   using S = P2InvSmem<R, T, NST>;
   static_assert(S::kBytes <= 227 * 1024, "inverse DFT tile does not fit shared memory");
   const fl::cf* tables;
-  if (get_p2_tables(&tables)) return 1;
+  if (get_p2_tables(&tables, band)) return 1;
   static PerDeviceOnce attr;
   if (attr.needed()) {
     if (p2_prepare(dft_inv_p2_kernel<R, T, NST, MAPS>, S::kBytes)) return 1;
@@ -536,10 +540,10 @@ static int launch_inv_p2_maps(const MAPS& maps, int B, int C, int Ctot, int K, i
 
 template <int R, typename T>
 static int launch_inv_p2(const float* xm, int B, int C, int Ctot, int K, int Kp, int M, int m_valid, const float* mscale,
-                         void* y, cudaStream_t stream) {
+                         void* y, cudaStream_t stream, int band = 0) {
   LocalMap lm;
   if (xm_stage_map(&lm.map, xm, B, C, Kp, std::max(1, std::min(M, m_valid)))) return 1;
-  return launch_inv_p2_maps<R, T, LocalMap>(lm, B, C, Ctot, K, Kp, std::min(M, m_valid), mscale, y, stream);
+  return launch_inv_p2_maps<R, T, LocalMap>(lm, B, C, Ctot, K, Kp, std::min(M, m_valid), mscale, y, stream, band);
 }
 
 // channel-sharded XM_ch buffers of all ranks as seen from this rank's latitude slab (see PeerMaps)

@@ -289,6 +289,63 @@ __global__ void add_bias_kernel(T* __restrict__ y, const float* __restrict__ bia
   }
 }
 
+// ------------------------------------------------------------------ per-degree energy of an SP tensor (spectral loss)
+// P[b][c][l] = sum_{m <= l} w_m |SP[l][m][b][c]|^2 with w_m = 1 at the global m = 0 and 2 elsewhere: what the
+// reference's GeometricH1Loss forms from the complex64 coefficients (makani/utils/losses.py:299-303, 327-337:
+// coeffs[...,0]^2 + coeffs[...,1]^2, then column 0 + 2 * sum of the others), read here straight from the SP layout.
+// grid (ceil(C/32), L, B), block (32, 8): threadIdx.y strides over m, the eight partial sums meet in shared memory.
+__global__ void __launch_bounds__(256) sp_degree_power_kernel(const float* __restrict__ sp, float* __restrict__ out,
+                                                              int B, int C, int L, int M, int l_off, int m_off) {
+  __shared__ float part[8][33];
+  const int Cp = (C + 3) & ~3;
+  const long long RS = 2LL * B * Cp;
+  const int l = blockIdx.y, b = blockIdx.z, c = blockIdx.x * 32 + threadIdx.x;
+  const int mend = min(M, l + l_off - m_off + 1);              // defined entries: m + m_off <= l + l_off
+  float acc = 0.f;
+  if (c < C) {
+    const float* p = sp + (long long)l * M * RS + (long long)(2 * b) * Cp + c;
+    for (int m = threadIdx.y; m < mend; m += 8) {
+      const float re = p[m * RS], im = p[m * RS + Cp];
+      const float w = (m + m_off == 0) ? 1.f : 2.f;
+      acc = fmaf(w * re, re, acc);
+      acc = fmaf(w * im, im, acc);
+    }
+  }
+  part[threadIdx.y][threadIdx.x] = acc;
+  __syncthreads();
+  if (threadIdx.y == 0 && c < C) {
+    float s = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s += part[j][threadIdx.x];
+    out[((long long)b * C + c) * L + l] = s;
+  }
+}
+
+// its adjoint: gSP[l][m][b][re|im][c] = 2 w_m g[b][c][l] SP[l][m][b][re|im][c] for m <= l and exact zeros in the rest of
+// the tensor (m > l, pad channels), as the SP contract wants.  grid (L, B), block (64, 4)
+__global__ void __launch_bounds__(256) sp_degree_power_bwd_kernel(const float* __restrict__ sp, const float* __restrict__ g,
+                                                                  float* __restrict__ gsp, int B, int C, int L, int M,
+                                                                  int l_off, int m_off, int round_out) {
+  const int Cp = (C + 3) & ~3;
+  const long long RS = 2LL * B * Cp;
+  const int l = blockIdx.x, b = blockIdx.y;
+  const int mend = min(M, l + l_off - m_off + 1);
+  const long long row0 = (long long)l * M * RS + (long long)(2 * b) * Cp;
+  for (int j = threadIdx.x; j < 2 * Cp; j += 64) {
+    const int c = j < Cp ? j : j - Cp;
+    const float gl = c < C ? 2.f * g[((long long)b * C + c) * L + l] : 0.f;
+    for (int m = threadIdx.y; m < M; m += 4) {
+      const long long off = row0 + m * RS + j;
+      float v = 0.f;
+      if (m < mend && c < C) {
+        v = ((m + m_off == 0) ? gl : 2.f * gl) * sp[off];
+        if (round_out) v = tf32_rn(v);
+      }
+      gsp[off] = v;
+    }
+  }
+}
+
 // dst += src over n floats (n % 4 == 0, 16-byte aligned): sum of two SP gradients on the h-sharded path
 __global__ void __launch_bounds__(256) add_inplace_kernel(float4* __restrict__ dst, const float4* __restrict__ src, long long n4) {
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
@@ -650,6 +707,27 @@ int sfno_add_bias(void* y, int y_dtype, const float* bias, int bias_kind, int B,
     case SFNO_F16: add_bias_kernel<__half><<<grid, 256, 0, s>>>((__half*)y, bias, bias_kind, n, C, HW); break;
     default: SFNO_CHECK(false, "unsupported dtype");
   }
+  SFNO_LAUNCHED();
+  return 0;
+}
+
+int sfno_sp_degree_power(const float* sp, int B, int C, int lmax, int mmax, int l_offset, int m_offset, float* out,
+                         void* stream) {
+  SFNO_CHECK(sp && out && B > 0 && C > 0 && lmax > 0 && mmax > 0, "sfno_sp_degree_power: bad arguments");
+  SFNO_CHECK(lmax <= 65535 && B <= 65535, "sfno_sp_degree_power: lmax and B must fit a grid dimension");
+  dim3 grid((C + 31) / 32, lmax, B), block(32, 8);
+  sp_degree_power_kernel<<<grid, block, 0, (cudaStream_t)stream>>>(sp, out, B, C, lmax, mmax, l_offset, m_offset);
+  SFNO_LAUNCHED();
+  return 0;
+}
+
+int sfno_sp_degree_power_bwd(const float* sp, const float* g, int B, int C, int lmax, int mmax, int l_offset, int m_offset,
+                             int round_tf32, float* gsp, void* stream) {
+  SFNO_CHECK(sp && g && gsp && B > 0 && C > 0 && lmax > 0 && mmax > 0, "sfno_sp_degree_power_bwd: bad arguments");
+  SFNO_CHECK(B <= 65535, "sfno_sp_degree_power_bwd: B must fit a grid dimension");
+  dim3 grid(lmax, B), block(64, 4);
+  sp_degree_power_bwd_kernel<<<grid, block, 0, (cudaStream_t)stream>>>(sp, g, gsp, B, C, lmax, mmax, l_offset, m_offset,
+                                                                       round_tf32);
   SFNO_LAUNCHED();
   return 0;
 }

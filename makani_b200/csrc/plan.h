@@ -37,6 +37,14 @@ int dft_fwd(const void* x, int x_dtype, int B, int C, int Ctot, int nlat, int nl
 int dft_inv(const float* xm, int B, int C, int Ctot, int nlat, int nlon, int mmax, int m_valid, const float* mscale,
             void* y, int y_dtype, cudaStream_t stream);
 
+// nlon = 1440 beyond 241 modes: one band (0: bins 0..240, 1: conjugates of bins 480-k, 2: bins 480+k) per launch
+int dft_fwd_band(const void* x, int x_dtype, int B, int C, int Ctot, int nlat, int band, int mcount, const float* mscale,
+                 float* xm_rows, int round_out, cudaStream_t stream);
+int dft_inv_band(const float* xm_rows, int B, int C, int Ctot, int nlat, int band, int mcount, const float* mscale, void* y,
+                 int y_dtype, cudaStream_t stream);
+int xm_mirror_conj(const float* src, float* dst, int nrows, int nplanes, long long plane_floats, const float* scale,
+                   int round_out, cudaStream_t stream);
+
 bool dft_peer_supported(int nlon, int mmax);
 int dft_fwd_peer(const void* x, int x_dtype, int B, int C, int nlat_loc, int nlon, int mmax, const float* mscale,
                  void* const* xm_ch, const int* chan_shapes, int nranks, int Kg, int lat_off, int lat_span,

@@ -12,6 +12,7 @@ from __future__ import annotations
 
 import ctypes as C
 import math
+import os
 
 import numpy as np
 import torch
@@ -109,6 +110,71 @@ def rfft_adjoint_scale(nlon: int, mmax: int) -> torch.Tensor:
     return s * (2.0 * math.pi / nlon)
 
 
+# nlon = 1440 with more than 241 modes (the spectral loss's transform keeps all 721): the tiled kernels produce 241 bins
+# per launch, three launches with modified twiddle tables cover the spectrum (include/makani_b200.h: sfno_dft_fwd_band).
+def _banded(nlon: int, mmax: int) -> bool:
+    return nlon == 1440 and mmax > 241 and os.environ.get("SFNO_FORCE_GENERIC_DFT", "0") != "1"
+
+
+def _fptr(t: torch.Tensor, offset_floats: int = 0):
+    return C.c_void_p(t.data_ptr() + 4 * offset_floats)
+
+
+def _dft_fwd_banded(x: torch.Tensor, Ctot: int, c0: int, c: int, M: int, mscale: torch.Tensor, xm: torch.Tensor,
+                    round_tf32: bool):
+    """Channels [c0, c0 + c) of x [B, Ctot, nlat, 1440] -> compact XM (M rows).  Bins 0..240 and 480.. come straight
+    from the kernel; 241..479 are the mirrored conjugates of a third launch that writes a scratch."""
+    lib, st, dt = _ext.load(), _stream(), dtype_code(x.dtype)
+    B, K = x.shape[0], x.shape[2]
+    plane = _rup(c, 4) * _rup(K, 4)
+    row = 2 * B * plane
+
+    def band(b, count, scale, scale_off, dst, dst_off, rnd):
+        _ext.check(lib.sfno_dft_fwd_band(_ptr(x), dt, B, Ctot, c0, c, K, b, count, _fptr(scale, scale_off),
+                                         _fptr(dst, dst_off), int(rnd), st), "sfno_dft_fwd_band")
+
+    band(0, 241, mscale, 0, xm, 0, round_tf32)
+    n1 = min(M, 480) - 241                                   # bins 241 .. 240 + n1 = 480 - k, k = 239 .. 240 - n1
+    if n1 > 0:
+        tmp = torch.empty(240 * row, dtype=torch.float32, device=x.device)
+        band(1, 240, torch.ones(240, dtype=torch.float32, device=x.device), 0, tmp, 0, False)
+        _ext.check(lib.sfno_xm_mirror_conj(_fptr(tmp, (240 - n1) * row), _fptr(xm, 241 * row), n1, 2 * B, plane,
+                                           _fptr(mscale, 241), int(round_tf32), st), "sfno_xm_mirror_conj")
+    if M > 480:
+        band(2, M - 480, mscale, 480, xm, 480 * row, round_tf32)
+
+
+def _dft_inv_banded(xm: torch.Tensor, B: int, c: int, K: int, M: int, mscale: torch.Tensor) -> torch.Tensor:
+    """Compact XM (M rows, c channels) -> fp32 [B, c, K, 1440]: the sum of one inverse launch per band."""
+    lib, st = _ext.load(), _stream()
+    dev = xm.device
+    plane = _rup(c, 4) * _rup(K, 4)
+    row = 2 * B * plane
+
+    def band(b, count, scale, src, src_off):
+        y = torch.empty((B, c, K, 1440), dtype=torch.float32, device=dev)
+        _ext.check(lib.sfno_dft_inv_band(_fptr(src, src_off), B, c, 0, c, K, b, count, _ptr(scale), _ptr(y),
+                                         dtype_code(torch.float32), st), "sfno_dft_inv_band")
+        return y
+
+    y = band(0, 241, mscale[:241].contiguous(), xm, 0)
+    n1 = min(M, 480) - 241
+    if n1 > 0:
+        # scratch row k = conj(bin 480 - k) * s[480 - k] for k = 240 - n1 .. 239; rows 0 and 240 (and the rest) are zero
+        tmp = torch.zeros(240 * row, dtype=torch.float32, device=dev)
+        _ext.check(lib.sfno_xm_mirror_conj(_fptr(xm, 241 * row), _fptr(tmp, (240 - n1) * row), n1, 2 * B, plane,
+                                           _ptr(mscale[241:241 + n1].flip(0).contiguous()), 0, st),
+                   "sfno_xm_mirror_conj")
+        y.add_(band(1, 240, torch.ones(240, dtype=torch.float32, device=dev), tmp, 0))
+    if M > 480:
+        s2 = mscale[480:M].clone()
+        s2[0] *= 2.0                                         # the kernel counts its bin 0 once (a DC bin) ...
+        if M == 721:
+            s2[240] *= 0.5                                   # ... and doubles its bin 240; 720 is the Nyquist bin
+        y.add_(band(2, M - 480, s2, xm, 480 * row))
+    return y
+
+
 def dft_fwd(x: torch.Tensor, mmax: int, mscale: torch.Tensor, round_tf32: bool = True) -> torch.Tensor:
     """x [B, C, nlat, nlon] (f32/bf16/f16, contiguous) -> XM.  XM always feeds the TF32 Legendre contraction,
     so by default its values are stored round-to-nearest TF32 (see tf32_rn in csrc/common.cuh)."""
@@ -116,6 +182,9 @@ def dft_fwd(x: torch.Tensor, mmax: int, mscale: torch.Tensor, round_tf32: bool =
     B, Cn, K, W = x.shape
     x = x.contiguous()
     xm = torch.empty(xm_elems(K, mmax, B, Cn), dtype=torch.float32, device=x.device)
+    if _banded(W, mmax):
+        _dft_fwd_banded(x, Cn, 0, Cn, mmax, mscale, xm, round_tf32)
+        return xm
     _ext.check(_ext.load().sfno_dft_fwd(_ptr(x), dtype_code(x.dtype), B, Cn, K, W, mmax, _ptr(mscale), _ptr(xm),
                                         int(round_tf32), _stream()), "sfno_dft_fwd")
     return xm
@@ -124,6 +193,8 @@ def dft_fwd(x: torch.Tensor, mmax: int, mscale: torch.Tensor, round_tf32: bool =
 def dft_inv(xm: torch.Tensor, B: int, Cn: int, nlat: int, nlon: int, mmax: int, mscale: torch.Tensor,
             dtype: torch.dtype, m_valid=None) -> torch.Tensor:
     _need_cuda(xm, "xm")
+    if _banded(nlon, mmax if m_valid is None else min(mmax, m_valid)):
+        return _dft_inv_banded(xm, B, Cn, nlat, mmax if m_valid is None else min(mmax, m_valid), mscale).to(dtype)
     y = torch.empty((B, Cn, nlat, nlon), dtype=dtype, device=xm.device)
     _ext.check(_ext.load().sfno_dft_inv(_ptr(xm), B, Cn, nlat, nlon, mmax, mmax if m_valid is None else m_valid,
                                         _ptr(mscale), _ptr(y), dtype_code(dtype), _stream()), "sfno_dft_inv")
@@ -209,8 +280,11 @@ def sht_to_sp(plan: Plan, x: torch.Tensor, mscale: torch.Tensor, round_tf32: boo
     xm = _window_buffer(xm_elems(K, M, B, cc), x.device)
     for c0 in range(0, Cn, cc):
         c = min(cc, Cn - c0)
-        _ext.check(lib.sfno_dft_fwd_win(_ptr(x), dt, B, Cn, c0, c, K, W, M, _ptr(mscale), _ptr(xm), 1, st),
-                   "sfno_dft_fwd_win")
+        if _banded(W, M):
+            _dft_fwd_banded(x, Cn, c0, c, M, mscale, xm, True)
+        else:
+            _ext.check(lib.sfno_dft_fwd_win(_ptr(x), dt, B, Cn, c0, c, K, W, M, _ptr(mscale), _ptr(xm), 1, st),
+                       "sfno_dft_fwd_win")
         _ext.check(lib.sfno_legendre_analysis_win(plan.handle, _ptr(xm), B, Cn, c0, c, _ptr(sp), int(round_tf32),
                                                   int(accumulate), st), "sfno_legendre_analysis_win")
     return sp
@@ -238,8 +312,11 @@ def sp_to_field(plan: Plan, sp: torch.Tensor, B: int, Cn: int, nlon: int, mscale
         if dc_bias is not None:
             _ext.check(lib.sfno_xm_add_dc(_ptr(xm), B, c, K, C.c_void_p(dc_bias.data_ptr() + 4 * c0), st),
                        "sfno_xm_add_dc")
-        _ext.check(lib.sfno_dft_inv_win(_ptr(xm), B, Cn, c0, c, K, nlon, M, mv, _ptr(mscale), _ptr(y), dt, st),
-                   "sfno_dft_inv_win")
+        if _banded(nlon, min(M, mv)):
+            y[:, c0:c0 + c].copy_(_dft_inv_banded(xm, B, c, K, min(M, mv), mscale))
+        else:
+            _ext.check(lib.sfno_dft_inv_win(_ptr(xm), B, Cn, c0, c, K, nlon, M, mv, _ptr(mscale), _ptr(y), dt, st),
+                       "sfno_dft_inv_win")
     return y
 
 
@@ -298,6 +375,27 @@ def sp_band_add_(dst: torch.Tensor, src: torch.Tensor, B: int, Cn: int, lmax: in
     n = sp_elems(lmax, mmax, B, Cn)
     _ext.check(_ext.load().sfno_add_inplace(_ptr(dst), _ptr(src), n, _stream()), "sfno_add_inplace")
     return dst
+
+
+def sp_degree_power(sp: torch.Tensor, B: int, Cn: int, lmax: int, mmax: int, l_offset=0, m_offset=0) -> torch.Tensor:
+    """SP -> fp32 [B, C, lmax]: sum over m <= l of |coefficient|^2, counted once at m = 0 and twice elsewhere
+    (makani/utils/losses.py:299-303)."""
+    out = torch.empty((B, Cn, lmax), dtype=torch.float32, device=sp.device)
+    _ext.check(_ext.load().sfno_sp_degree_power(_ptr(sp), B, Cn, lmax, mmax, l_offset, m_offset, _ptr(out), _stream()),
+               "sfno_sp_degree_power")
+    return out
+
+
+def sp_degree_power_bwd(sp: torch.Tensor, g: torch.Tensor, B: int, Cn: int, lmax: int, mmax: int, l_offset=0,
+                        m_offset=0, round_tf32: bool = True) -> torch.Tensor:
+    """Gradient of sp_degree_power with respect to SP, as an SP tensor (zeros above the diagonal and in pad channels)."""
+    g = g.to(torch.float32).contiguous()
+    if tuple(g.shape) != (B, Cn, lmax):
+        raise ValueError(f"makani_b200: expected a gradient of shape {(B, Cn, lmax)}, got {tuple(g.shape)}")
+    gsp = torch.empty_like(sp)
+    _ext.check(_ext.load().sfno_sp_degree_power_bwd(_ptr(sp), _ptr(g), B, Cn, lmax, mmax, l_offset, m_offset,
+                                                    int(round_tf32), _ptr(gsp), _stream()), "sfno_sp_degree_power_bwd")
+    return gsp
 
 
 # ------------------------------------------------------------------------------------------ dhconv

@@ -8,6 +8,7 @@ What is restated, and from where
 * ``_contract_dhconv`` etc.           makani/models/common/contractions.py:121-154
 * transform construction / sizes      makani/models/networks/sfnonet.py:503-571
 * distributed choreography (twin)     makani/mpu/layers.py:67-102, 134-169
+* ``GeometricH1Loss``                 makani/utils/losses.py:275-370
 * ``RealSHT`` / ``InverseRealSHT`` / ``DistributedRealSHT`` / quadrature / Legendre tables:
   third-party **torch-harmonics** (pyproject.toml:55 ``torch-harmonics>=0.6.5``;
   docker/Dockerfile:78-79 pins v0.6.4).  The package is NOT vendored under /root/reference and not
@@ -20,6 +21,8 @@ Parity pinning status
   ``contractions.py`` (loaded by file path) in the build container (tools/make_golden.py).
 * quadrature: PINNED to the reference's own known-answer test (tests/test_metrics.py:37-45, sum of
   weights) and to numpy's Gauss-Legendre rule.
+* spectral loss: PINNED - tests/golden/h1_loss_ref.npz holds values and gradients of the reference's own, unmodified
+  ``GeometricH1Loss`` run on this oracle's transform (tools/make_golden.py).
 * SHT coefficient / field values: **parity unpinned** - the reference holds no golden vectors for them
   and torch-harmonics cannot be run here.  They are anchored on mathematical invariants instead
   (orthonormality against scipy.special.sph_harm_y, exact round trip, adjointness); see
@@ -299,6 +302,45 @@ def distributed_isht_expected(c_full, isht: InverseRealSHT, h: int, w: int, rank
     lat_shapes = compute_split_shapes(isht.nlat, h)
     lon_shapes = compute_split_shapes(isht.nlon, w)
     return shard(shard(x, -2, lat_shapes, rank_h), -1, lon_shapes, rank_w)
+
+
+# --------------------------------------------------------------------------------------------------
+# spectral loss (makani/utils/losses.py:275-370)
+# --------------------------------------------------------------------------------------------------
+def degree_power(x: torch.Tensor, sht: RealSHT) -> torch.Tensor:
+    """losses.py:299-301 / 327-329: |c|^2 per (l, m), column m = 0 once and every other column twice -> [..., lmax]."""
+    c = sht(x)
+    p = c.real ** 2 + c.imag ** 2
+    return p[..., :, 0] + 2 * torch.sum(p[..., :, 1:], dim=-1)
+
+
+def geometric_h1_loss(prd, tar, sht: RealSHT, mask=None, alpha=0.5, absolute=False, squared=False, reduction=True,
+                      size_average=False):
+    """GeometricH1Loss.forward (losses.py:365-370) with its abs (:296-322) and rel (:324-363) branches."""
+    n = prd.shape[0]
+    h1w = torch.arange(sht.lmax, dtype=prd.dtype)
+    h1w = h1w * (h1w + 1)                                                     # losses.py:293-294
+
+    def norms(x):
+        e = degree_power(x, sht)
+        l2 = e.reshape(n, -1).sum(dim=-1)                                     # :302 / :330
+        h1 = (e * h1w).reshape(n, -1).sum(dim=-1)                             # :303 / :331
+        if not squared:
+            return alpha * torch.sqrt(l2) + (1 - alpha) * torch.sqrt(h1)      # :306 / :340-341
+        return alpha * l2 + (1 - alpha) * h1                                  # :308 / :343-344
+
+    if absolute:
+        val = norms(prd - tar)
+        mask = None                                                           # abs() takes no mask (:365-367)
+    else:
+        val = norms(prd - tar) / norms(tar)                                   # :347
+        if mask is not None:
+            val = val * mask
+    if not reduction:
+        return val
+    if size_average:
+        return torch.mean(val) if mask is None else torch.sum(val) / torch.sum(mask)
+    return torch.sum(val)
 
 
 def rel_l2(a: torch.Tensor, b: torch.Tensor) -> float:

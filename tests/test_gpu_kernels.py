@@ -45,6 +45,13 @@ def _rfft_ref(x64, M, scale):
     (1, 3, 17, 1440, 200, torch.float16),
     (1, 40, 240, 1440, 241, torch.bfloat16),  # 600 tiles: several tiles per CTA (dynamic scheduler, single row buffer)
     (2, 160, 240, 480, 241, torch.bfloat16),  # 4800 tiles at R=1 (double-buffered rows)
+    (1, 3, 17, 1440, 721, torch.float32),     # more than 241 modes at nlon = 1440: three band launches (ops._dft_fwd_banded)
+    (2, 5, 9, 1440, 600, torch.float32),
+    (1, 4, 18, 1440, 400, torch.float32),
+    (1, 2, 8, 1440, 481, torch.float32),
+    (1, 2, 8, 1440, 480, torch.float32),
+    (1, 2, 8, 1440, 242, torch.float32),
+    (1, 4, 16, 1440, 721, torch.bfloat16),
 ])
 def test_dft_fwd(ops, B, C, K, W, M, dtype):
     torch.manual_seed(0)
@@ -72,6 +79,13 @@ def test_dft_fwd(ops, B, C, K, W, M, dtype):
     (1, 40, 240, 1440, 241, torch.bfloat16),  # 600 tiles: several tiles per CTA, single staging tile (NST = 1)
     (2, 160, 240, 480, 241, torch.bfloat16),  # 4800 tiles at R=1
     (1, 4, 18, 1440, 241, torch.float16),
+    (1, 3, 17, 1440, 721, torch.float32),     # more than 241 modes at nlon = 1440: three band launches (ops._dft_inv_banded)
+    (2, 5, 9, 1440, 600, torch.float32),
+    (1, 4, 18, 1440, 400, torch.float32),
+    (1, 2, 8, 1440, 481, torch.float32),
+    (1, 2, 8, 1440, 480, torch.float32),
+    (1, 2, 8, 1440, 242, torch.float32),
+    (1, 4, 16, 1440, 721, torch.bfloat16),
 ])
 def test_dft_inv(ops, B, C, K, W, M, dtype):
     torch.manual_seed(1)

@@ -159,3 +159,41 @@ def test_spectral_conv_matches_reference_module(name):
     if bias:
         db = torch.from_numpy(z["dbias"])
         assert float((b.grad - db).norm() / db.norm()) < 1e-6
+
+
+H1_VARIANTS = {"rel": {}, "abs": {"absolute": True}, "rel_sq": {"squared": True},
+               "abs_sq_mean": {"absolute": True, "squared": True, "size_average": True},
+               "rel_mean": {"size_average": True}, "rel_none": {"reduction": False}, "rel_alpha": {"alpha": 0.2}}
+
+
+@pytest.mark.parametrize("tag,nlat,nlon", [("a", 13, 24), ("b", 25, 48)])
+def test_h1_loss_matches_reference_class(tag, nlat, nlon):
+    """oracle.geometric_h1_loss against values AND gradients recorded from the reference's own GeometricH1Loss
+    (makani/utils/losses.py:275-370, tools/make_golden.py), every switch, with and without the example mask."""
+    z = np.load(os.path.join(GOLD, "h1_loss_ref.npz"))
+    sht = O.RealSHT(nlat, nlon, grid="equiangular", dtype=torch.float32)
+    tar, mask = torch.from_numpy(z[f"{tag}_tar"]), torch.from_numpy(z[f"{tag}_mask"])
+    for name, kw in H1_VARIANTS.items():
+        for mtag, m in (("", None), ("_masked", mask)):
+            prd = torch.from_numpy(z[f"{tag}_prd"]).requires_grad_(True)
+            val = O.geometric_h1_loss(prd, tar, sht, mask=m, **kw)
+            val.sum().backward()
+            np.testing.assert_allclose(val.detach().numpy(), z[f"{tag}_{name}{mtag}"], rtol=1e-5, atol=1e-6)
+            np.testing.assert_allclose(prd.grad.numpy(), z[f"{tag}_{name}{mtag}_dprd"], rtol=1e-4, atol=1e-6)
+
+
+def test_degree_power_is_the_quadrature_of_the_square():
+    """Parseval on the sphere: for a band-limited field the sum over l of the per-degree energy equals the integral of
+    x^2 (Gauss-Legendre quadrature is exact for it) - anchors the 'once at m = 0, twice elsewhere' weighting."""
+    nlat, nlon, L = 24, 48, 12
+    sht = O.RealSHT(nlat, nlon, lmax=L, mmax=L, grid="legendre-gauss")
+    isht = O.InverseRealSHT(nlat, nlon, lmax=L, mmax=L, grid="legendre-gauss")
+    g = torch.Generator().manual_seed(5)
+    c = torch.complex(torch.randn(2, L, L, dtype=torch.float64, generator=g),
+                      torch.randn(2, L, L, dtype=torch.float64, generator=g))
+    c = c * (torch.arange(L)[None, :] <= torch.arange(L)[:, None])            # m <= l
+    c[..., 0] = c[..., 0].real.to(torch.complex128)
+    x = isht(c)
+    _, w, _ = O.grid_nodes_weights(nlat, "legendre-gauss")
+    integral = (x ** 2 * torch.from_numpy(np.ascontiguousarray(w))[:, None]).sum(dim=(-2, -1)) * 2 * np.pi / nlon
+    np.testing.assert_allclose(O.degree_power(x, sht).sum(-1).numpy(), integral.numpy(), rtol=1e-10)

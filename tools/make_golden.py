@@ -12,6 +12,10 @@
    CPU oracle standing in for torch-harmonics (fp32, as ``sfnonet.py:536-539`` builds the transforms with ``.float()``):
    pins the module's orchestration - fp32 forcing, residual re-projection, contraction dispatch, bias, dtype of the
    results - for oracle.spectral_conv_forward (CPU) and makani_b200.SpectralConv (GPU).
+5. h1_loss_ref.npz     - values and gradients of the REFERENCE's own, unmodified ``GeometricH1Loss``
+   (makani/utils/losses.py:275-370, loaded through tests/refharness.py) with the CPU oracle standing in for
+   torch-harmonics, for every combination of its switches: pins oracle.geometric_h1_loss (CPU) and
+   makani_b200.GeometricH1Loss (GPU).  ``python tools/make_golden.py h1`` writes this file only.
 3. sht_small.npz       - oracle outputs on small grids (NOT reference outputs: torch-harmonics is not available;
    recorded so a later change of the oracle or of the kernels is caught as a regression).
 """
@@ -74,8 +78,42 @@ def make_spectral_conv_reference():
         np.savez_compressed(os.path.join(OUT, f"spectral_conv_ref_{name}.npz"), **out)
 
 
+H1_GRIDS = {"a": (13, 24, 2, 3), "b": (25, 48, 3, 4)}          # nlat, nlon, B, C
+H1_VARIANTS = {"rel": {}, "abs": {"absolute": True}, "rel_sq": {"squared": True},
+               "abs_sq_mean": {"absolute": True, "squared": True, "size_average": True},
+               "rel_mean": {"size_average": True}, "rel_none": {"reduction": False}, "rel_alpha": {"alpha": 0.2}}
+
+
+def make_h1_loss_reference():
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import refharness as H
+    H.install("oracle")
+    losses = H.load("makani.utils.losses")
+    assert losses.__file__.startswith("/root/reference/")
+    out = {}
+    for tag, (nlat, nlon, B, Cn) in H1_GRIDS.items():
+        torch.manual_seed(7 + nlat)
+        prd = torch.randn(B, Cn, nlat, nlon, requires_grad=True)
+        tar = torch.randn(B, Cn, nlat, nlon)
+        mask = (torch.arange(B) % 2 == 0).float()
+        out[f"{tag}_prd"], out[f"{tag}_tar"], out[f"{tag}_mask"] = prd.detach().numpy(), tar.numpy(), mask.numpy()
+        for name, kw in H1_VARIANTS.items():
+            mod = losses.GeometricH1Loss((nlat, nlon), **kw)
+            for mtag, m in (("", None), ("_masked", mask)):
+                prd.grad = None
+                val = mod(prd, tar, m)
+                val.sum().backward()
+                out[f"{tag}_{name}{mtag}"] = val.detach().numpy()
+                out[f"{tag}_{name}{mtag}_dprd"] = prd.grad.numpy().copy()
+    np.savez_compressed(os.path.join(OUT, "h1_loss_ref.npz"), **out)
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
+    if sys.argv[1:] == ["h1"]:
+        make_h1_loss_reference()
+        print("wrote h1_loss_ref.npz")
+        return
     ref = load_ref_contractions()
     g = torch.Generator().manual_seed(1234)
     for name, (B, Ci, Co, L, M) in {"a": (2, 6, 10, 12, 13), "b": (1, 16, 16, 20, 21)}.items():
@@ -107,6 +145,7 @@ def main():
         small[f"{tag}_xr"] = isht(c).numpy()
     np.savez_compressed(os.path.join(OUT, "sht_small.npz"), **small)
     make_spectral_conv_reference()
+    make_h1_loss_reference()
     print("wrote", sorted(os.listdir(OUT)))
 
 

@@ -137,7 +137,8 @@ def _dft_fwd_banded(x: torch.Tensor, Ctot: int, c0: int, c: int, M: int, mscale:
     n1 = min(M, 480) - 241                                   # bins 241 .. 240 + n1 = 480 - k, k = 239 .. 240 - n1
     if n1 > 0:
         tmp = torch.empty(240 * row, dtype=torch.float32, device=x.device)
-        band(1, 240, torch.ones(240, dtype=torch.float32, device=x.device), 0, tmp, 0, False)
+        ones = torch.ones(240, dtype=torch.float32, device=x.device)
+        band(1, 240, ones, 0, tmp, 0, False)
         _ext.check(lib.sfno_xm_mirror_conj(_fptr(tmp, (240 - n1) * row), _fptr(xm, 241 * row), n1, 2 * B, plane,
                                            _fptr(mscale, 241), int(round_tf32), st), "sfno_xm_mirror_conj")
     if M > 480:
@@ -157,15 +158,16 @@ def _dft_inv_banded(xm: torch.Tensor, B: int, c: int, K: int, M: int, mscale: to
                                          dtype_code(torch.float32), st), "sfno_dft_inv_band")
         return y
 
-    y = band(0, 241, mscale[:241].contiguous(), xm, 0)
+    y = band(0, 241, mscale, xm, 0)
     n1 = min(M, 480) - 241
     if n1 > 0:
         # scratch row k = conj(bin 480 - k) * s[480 - k] for k = 240 - n1 .. 239; rows 0 and 240 (and the rest) are zero
         tmp = torch.zeros(240 * row, dtype=torch.float32, device=dev)
+        s1 = mscale[241:241 + n1].flip(0).contiguous()       # (named: the buffers must outlive the calls that read them)
+        ones = torch.ones(240, dtype=torch.float32, device=dev)
         _ext.check(lib.sfno_xm_mirror_conj(_fptr(xm, 241 * row), _fptr(tmp, (240 - n1) * row), n1, 2 * B, plane,
-                                           _ptr(mscale[241:241 + n1].flip(0).contiguous()), 0, st),
-                   "sfno_xm_mirror_conj")
-        y.add_(band(1, 240, torch.ones(240, dtype=torch.float32, device=dev), tmp, 0))
+                                           _ptr(s1), 0, st), "sfno_xm_mirror_conj")
+        y.add_(band(1, 240, ones, tmp, 0))
     if M > 480:
         s2 = mscale[480:M].clone()
         s2[0] *= 2.0                                         # the kernel counts its bin 0 once (a DC bin) ...

@@ -6,7 +6,8 @@
   torch      the reference-equivalent path on this GPU: cuFFT rfft + einsum with the fp32 table (TF32 allowed, as
              train.py:109-110 sets it) + the same arithmetic
 
-   python tools/bench_h1_loss.py [iters]         (grids: 240x480 with 240 degrees / 241 modes, 721x1440 with all 721)"""
+   python tools/bench_h1_loss.py [iters [nlat [leg]]]   (grids: 240x480 with 240 degrees / 241 modes, 721x1440 with all
+   721; nlat / leg restrict the run to one grid / one leg, e.g. `1 721 fused` under ncu)"""
 import os
 import sys
 
@@ -16,6 +17,8 @@ import torch
 import makani_b200 as mk
 
 iters = int(sys.argv[1]) if len(sys.argv) > 1 else 5
+only_nlat = int(sys.argv[2]) if len(sys.argv) > 2 else None
+only_leg = sys.argv[3] if len(sys.argv) > 3 else None
 dev = torch.device("cuda:0")
 torch.backends.cuda.matmul.allow_tf32 = True
 torch.backends.cudnn.allow_tf32 = True
@@ -41,6 +44,8 @@ def timed(fn):
 
 
 for nlat, nlon in ((240, 480), (721, 1440)):
+    if only_nlat not in (None, nlat):
+        continue
     Cn = 73
     loss = mk.GeometricH1Loss((nlat, nlon)).to(dev)
     sht = loss.sht
@@ -69,6 +74,8 @@ for nlat, nlon in ((240, 480), (721, 1440)):
             "torch": lambda: run(lambda x: formula(torch_sht(x)))}
     vals = {}
     for name, fn in legs.items():
+        if only_leg not in (None, name):
+            continue
         try:
             vals[name] = float(fn().detach())
             print(f"h1_loss {nlat}x{nlon} C={Cn} lmax={sht.lmax} mmax={sht.mmax} {name:8s} {timed(fn):8.2f} ms  "
